@@ -1,0 +1,165 @@
+/* mcpt.h — C ABI of the B200-native Monte Carlo path-tracing core.
+ *
+ * This library replaces ONE hot path of ksaintmarc/Montecarlo-PathTracing: the
+ * per-pixel path tracer the reference runs as an OpenGL fragment program
+ * (shaders/raytracer_func.frag + tp/montecarlo.frag + shaders/main.frag), the
+ * additive progressive accumulation (MontecarloGPU/montecarlo.cpp:450-467) and
+ * the resolve pass (montecarlo.cpp:59-70,470-476 / shaders/average.frag).
+ *
+ * The reference has no FFI; the seam is two host call sites, and every entry
+ * point below names the reference code it stands in for:
+ *   (1) BVH_GPU_Scene::finalize()            bvh_gpu/gpu_bvh_scene.cpp:121-187
+ *   (2) RTViewer::draw_ogl(), RT branch      MontecarloGPU/montecarlo.cpp:408-477
+ *       RTViewer::resize_ogl()               MontecarloGPU/montecarlo.cpp:616-626
+ *
+ * Conventions: plain C types only; every function returns 0 (MCPT_OK) or a
+ * negative MCPT_E_* code and never throws or exits; mcpt_last_error(ctx) gives
+ * a human-readable message for the last failure on that context. A context is
+ * owned by one caller thread at a time (the reference's "GL thread" rule);
+ * several contexts (one per GPU) may be driven from several threads/processes.
+ * There is NO CPU fallback: without a CUDA device mcpt_create fails.
+ */
+#ifndef MCPT_H_
+#define MCPT_H_
+
+#include <stddef.h>
+#include <stdint.h>
+#include "mcpt_scene.h"
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define MCPT_OK 0
+#define MCPT_E_INVALID -1   /* bad argument / bad state                    */
+#define MCPT_E_CUDA -2      /* a CUDA runtime call failed                  */
+#define MCPT_E_NODEVICE -3  /* no CUDA device / device index out of range  */
+#define MCPT_E_NOMEM -4     /* host or device allocation failed            */
+#define MCPT_E_NCCL -5      /* NCCL unavailable or a collective failed     */
+#define MCPT_E_UNSUPPORTED -6
+
+#define MCPT_ABI_VERSION 1
+
+typedef struct mcpt_ctx mcpt_ctx;
+
+/* Viewer-facing parameter block = the uniforms RTViewer::draw_ogl sets
+ * (montecarlo.cpp:441-448,453; declared at raytracer_func.frag:23-27 and
+ * tp/montecarlo.frag:1-3). numero_pass is an argument of mcpt_render. */
+typedef struct mcpt_params {
+    int32_t nb_bounces;   /* uniform 21 NB_BOUNCES   (UI 0..9, any >=0 accepted) */
+    float refract_ind;    /* uniform 24 refract_ind  (UI 1.0..2.5)              */
+    float date;           /* uniform 5  date: seconds since previous frame      */
+    int32_t flat_face;    /* uniform 3  flat_face (never set by the host => 0)  */
+    int32_t mode;         /* tp shader: 0 montecarlo.frag, 1 montecarlo_mat.frag,
+                             2 montecarlo_mat_tr.frag (keys O/P, montecarlo.cpp:292-304) */
+    int32_t nb_prims;     /* uniform 1  (uploaded, unused by montecarlo.frag)   */
+    int32_t nb_emissives; /* uniform 20 (uploaded, unused by montecarlo.frag)   */
+} mcpt_params;
+
+/* closest-hit record = struct sInter, raytracer_func.frag:257-267 */
+typedef struct mcpt_hit {
+    int32_t index;     /* primitive index, -1 on miss                        */
+    int32_t tri_index; /* triangle index inside the mesh, -1 if not a mesh   */
+    int32_t shape;     /* type code of the hit primitive, -1 on miss         */
+    int32_t dir;       /* face id (cube 0..5, cylinder/cone 0/1/2), else 0   */
+    float dist;        /* world-space distance |O - pg| (FLT_MAX on miss)    */
+    float pl[3];       /* hit point in primitive-local space                 */
+    float pg[3];       /* hit point in world space                           */
+} mcpt_hit;
+
+/* destination kinds for mcpt_resolve */
+enum {
+    MCPT_DST_HOST_RGB32F = 0,   /* float[3*w*h], unclamped (what fs_frag computes)      */
+    MCPT_DST_HOST_RGBA8 = 1,    /* uint8[4*w*h], clamped to [0,1], no gamma (back buffer) */
+    MCPT_DST_DEVICE_RGB32F = 2, /* device pointer, float[3*w*h]                          */
+    MCPT_DST_DEVICE_RGBA8 = 3   /* device pointer, uint8[4*w*h]                          */
+};
+
+/* tuning knobs for mcpt_set_option */
+enum {
+    MCPT_OPT_PASSES_PER_BATCH = 0, /* passes traced together in one wavefront (default auto) */
+    MCPT_OPT_SMEM_STAGING = 1,     /* 1 = stage top BVH levels in shared memory (default 1)  */
+    MCPT_OPT_FAST_MATH = 2,        /* 1 = MUFU sin/cos/log/pow in the bounce sampler         */
+    MCPT_OPT_SORT_QUEUES = 3       /* reserved                                               */
+};
+
+/* counters filled by the wavefront since the last mcpt_clear / mcpt_reset_stats */
+typedef struct mcpt_stats {
+    uint64_t paths;      /* camera paths started (pixels x passes)              */
+    uint64_t rays;       /* traverse_all_bvh calls (primary + bounce + interior) */
+    uint64_t segments;   /* shaded hits                                         */
+    uint64_t launches;   /* kernels launched by this library                    */
+} mcpt_stats;
+
+int mcpt_abi_version(void);
+const char* mcpt_last_error(const mcpt_ctx* ctx);
+const char* mcpt_error_string(int code);
+
+/* GL context + program creation, montecarlo.cpp:342-348. device = CUDA ordinal. */
+int mcpt_create(int device, mcpt_ctx** out);
+int mcpt_destroy(mcpt_ctx* ctx);
+
+/* Launch on an existing cudaStream_t (e.g. torch's current stream) instead of
+ * the context's own stream; pass NULL to go back to the private stream. */
+int mcpt_set_stream(mcpt_ctx* ctx, void* cuda_stream);
+int mcpt_synchronize(mcpt_ctx* ctx);
+int mcpt_set_option(mcpt_ctx* ctx, int option, int value);
+
+/* finalize() uploads, gpu_bvh_scene.cpp:143-175: tables are copied to the
+ * device and re-packed into the library's compact node / record layout. */
+int mcpt_upload_scene(mcpt_ctx* ctx, const mcpt_scene_desc* desc);
+
+/* resize_ogl -> fbo->resize, montecarlo.cpp:616-626: reallocates the
+ * accumulation buffer (zeroed) and resets the pass counter. */
+int mcpt_resize(mcpt_ctx* ctx, int width, int height);
+
+/* uniforms 6 and 10, montecarlo.cpp:439-440: column-major view.inverse() and
+ * (proj*view).inverse(), consumed as in shaders/raytracer.vert:9-22. */
+int mcpt_set_camera(mcpt_ctx* ctx, const float inv_v[16], const float inv_pv[16]);
+
+int mcpt_set_params(mcpt_ctx* ctx, const mcpt_params* p);
+
+/* glClear of the FBO when not locked, montecarlo.cpp:423-424. */
+int mcpt_clear(mcpt_ctx* ctx);
+
+/* The draw loop, montecarlo.cpp:454-466: pass k of this call uses
+ * numero_pass = first_pass + k and is blended additively (ONE,ONE) into the
+ * accumulation buffer. Asynchronous on the context's stream. */
+int mcpt_render(mcpt_ctx* ctx, int first_pass, int n_passes);
+
+/* The prg_fs draw, montecarlo.cpp:470-476 (frag = accum / nb), with the
+ * optional nearest-neighbour sub-sampling upscale of shaders/average.frag:9
+ * (dst is (w*subsampling) x (h*subsampling); subsampling >= 1). Host
+ * destinations synchronise; device destinations stay asynchronous. */
+int mcpt_resolve(mcpt_ctx* ctx, float divisor, int subsampling, void* dst, int dst_kind);
+
+/* Accumulation buffer access (new; multi-GPU spp split and checkpoint/resume).
+ * Layout: float4 per pixel (rgb sum, w unused), row-major, row 0 = bottom row
+ * (gl_FragCoord convention). mcpt_bind_accum makes the library accumulate
+ * straight into a caller-owned device buffer (e.g. an NCCL/torch send buffer). */
+int mcpt_get_accum(mcpt_ctx* ctx, float** dev_ptr, size_t* bytes);
+int mcpt_bind_accum(mcpt_ctx* ctx, float* dev_ptr, size_t bytes);
+int mcpt_read_accum(mcpt_ctx* ctx, float* host_rgba, size_t bytes);
+int mcpt_write_accum(mcpt_ctx* ctx, const float* host_rgba, size_t bytes);
+
+/* One ncclReduce(sum, fp32) of the accumulation buffer to `root` on the
+ * context's stream. `nccl_comm` is an ncclComm_t; NCCL symbols are resolved at
+ * run time from the libnccl already loaded in the process. */
+int mcpt_reduce_nccl(mcpt_ctx* ctx, void* nccl_comm, int root);
+
+/* traverse_all_bvh as a callable, raytracer_func.frag:777-781 (any_hit != 0:
+ * just_hit_bvh, :771-775 — only `index >= 0` is meaningful then). Host arrays:
+ * o and d are float[3*n]. d need not be unit length. */
+int mcpt_trace_rays(mcpt_ctx* ctx, int64_t n, const float* o, const float* d,
+                    mcpt_hit* out, int any_hit);
+/* same, with device-resident inputs/outputs (float4 o[n], float4 d[n]); asynchronous. */
+int mcpt_trace_rays_device(mcpt_ctx* ctx, int64_t n, const float* o4, const float* d4,
+                           mcpt_hit* out_dev, int any_hit);
+
+int mcpt_get_stats(mcpt_ctx* ctx, mcpt_stats* out);
+int mcpt_reset_stats(mcpt_ctx* ctx);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* MCPT_H_ */

@@ -1,0 +1,117 @@
+// layout.cuh — device-side data layout of the scene and of the wavefront state.
+//
+// The reference keeps its tables in six 1024-wide OpenGL textures
+// (bvh_gpu/gpu_bvh_scene.cpp:121-187) and pays 5-9 dependent texel fetches per
+// candidate primitive. Here the same information is re-packed once at upload:
+//
+//  * BVH nodes: 32 bytes = two float4 {min.xyz, aux0} {max.xyz, aux1}, in the
+//    reference's implicit heap order (node k has children 2k+1, 2k+2) so the tree
+//    needs no child pointers and traversal needs no stack in memory: a 32-bit
+//    trail of "sibling still pending" bits plus the heap index is the whole state.
+//    Boxes are inflated by a few ulps so the (FMA, non-exact) slab test stays
+//    conservative. Leaf-level nodes of the top-level tree carry the primitive id
+//    in aux0.
+//  * primitive records: 128 bytes = inverse transform (3 rows), forward transform
+//    (3 rows), {type, mesh id, leaf slot}, instead of the 256-byte PrimData.
+//  * triangles: 48 bytes per LEAF SLOT (three float4: A,B,C with the triangle id
+//    in A.w), stored in leaf-slot order so that the leaf level needs neither the
+//    index table nor the three scattered vertex fetches of read_triangle_pos
+//    (shaders/raytracer_func.frag:144-152).
+//  * shading tables: colour + material float4 per primitive; per-mesh vertex
+//    positions/normals/indices for the smooth-normal reconstruction.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "vecmath.cuh"
+
+namespace mcpt {
+
+struct DevNode {
+    float4 lo;  // min.xyz, aux0
+    float4 hi;  // max.xyz, aux1
+};
+
+struct DevPrim {
+    Aff inv;      // world -> local            (PrimData.inv_transfo)
+    Aff fwd;      // local -> world: primitives PrimData.transfo, meshes PrimData.mesh_transfo
+    int32_t type; // MCPT_PRIM_*
+    int32_t mesh; // mesh id for type 0, else -1
+    int32_t slot; // leaf slot of this primitive in the top-level tree (visit rank)
+    int32_t pad;
+    float4 pad2;
+};
+static_assert(sizeof(DevPrim) == 128, "DevPrim must be 128 bytes");
+
+struct DevTri {
+    float4 a;  // A.xyz, w = triangle id as int bits (-1: empty slot)
+    float4 b;  // B.xyz
+    float4 c;  // C.xyz
+};
+
+struct DevMesh {
+    const DevNode* nodes;   // 2^depth - 1 interior nodes, heap order
+    const DevTri* tris;     // 2^depth leaf slots
+    const uint32_t* idx;    // 3 * n_tris vertex ids (shading)
+    const float* pos;       // 3 * n_verts
+    const float* nrm;       // 3 * n_verts
+    int32_t depth;
+    int32_t n_tris;
+    int32_t smem_off;       // offset (in nodes) of this mesh's staged top levels, -1 if none
+    int32_t smem_nodes;     // number of staged nodes (2^L - 1)
+};
+
+struct DevScene {
+    const DevNode* top_nodes;  // 2^(depth+1) - 1 nodes, heap order
+    const DevPrim* prims;
+    const float4* color;       // PrimData.color_
+    const float4* mat;         // PrimData.mat_info
+    const DevMesh* meshes;
+    int32_t top_depth;
+    int32_t n_prims;
+    int32_t n_meshes;
+    // shared-memory staging plan (in units of DevNode / DevPrim)
+    int32_t smem_top_nodes;    // first N top-level nodes staged
+    int32_t smem_prims;        // first N primitive records staged
+    int32_t smem_mesh_nodes;   // total staged mesh nodes (sum over meshes)
+    int32_t smem_bytes;
+};
+
+// closest-hit registers of one ray (the live part of struct sInter,
+// raytracer_func.frag:257-267; pg is recomputed from pl where needed)
+struct Hit {
+    float dist;
+    f3 pl;
+    int32_t prim;
+    int32_t sub;   // triangle id for meshes, face id `dir` otherwise
+    int32_t rank;  // visit rank inside the winning primitive's mesh (tie-break only)
+};
+
+// uniforms of the traced path
+struct DevParams {
+    float inv_v[16];
+    float inv_pv[16];
+    int32_t width, height;
+    int32_t nb_bounces;
+    float refract_ind;
+    float date;
+    int32_t flat_face;
+    int32_t mode;
+};
+
+// SoA wavefront state, one entry per path slot
+struct Wavefront {
+    float4* ray_o;     // origin.xyz
+    float4* ray_d;     // direction.xyz
+    float4* hit_a;     // pl.xyz, dist
+    int2* hit_b;       // prim, sub
+    float4* attenu;    // attenuation.xyz
+    float4* total;     // radiance gathered so far .xyz
+    uint4* seed;       // xxhash32 state .xyz
+    float4* keep_n;    // N of the entry hit (interior rays)
+    float4* keep_p;    // P of the entry hit (interior rays)
+    float4* result;    // value returned by random_path
+    uint8_t* flag;     // per queue position: 0 dead, 1 continue, 2 continue + interior ray
+};
+
+}  // namespace mcpt

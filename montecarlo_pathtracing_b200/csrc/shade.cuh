@@ -1,0 +1,231 @@
+// shade.cuh — per-hit work of the bounce loop: RNG, geometric normal, material
+// fetch, bounce sampling and the four material cases.
+//
+// Follows tp/montecarlo.frag:49-179 (sample_hemisphere, random_ray, rSchlick,
+// random_path) and shaders/raytracer_func.frag:90-124 (xxhash32 RNG), :783-907
+// (normal reconstruction, colour / material fetch). The RNG is integer and
+// bit-exact; sin/cos/log/pow go through CUDA's libm (or MUFU with
+// MCPT_OPT_FAST_MATH), so radiance agrees with a CPU evaluation to rounding, not
+// bit for bit.
+#pragma once
+#include "intersect.cuh"
+
+namespace mcpt {
+
+// ---- RNG, raytracer_func.frag:90-124 ---------------------------------------
+MCPT_DEV uint32_t xxhash32(uint3 p) {
+    const uint32_t PRIME32_2 = 2246822519U, PRIME32_3 = 3266489917U;
+    const uint32_t PRIME32_4 = 668265263U, PRIME32_5 = 374761393U;
+    uint32_t h32 = p.z + PRIME32_5 + p.x * PRIME32_3;
+    h32 = PRIME32_4 * ((h32 << 17) | (h32 >> (32 - 17)));
+    h32 += p.y * PRIME32_3;
+    h32 = PRIME32_4 * ((h32 << 17) | (h32 >> (32 - 17)));
+    h32 = PRIME32_2 * (h32 ^ (h32 >> 15));
+    h32 = PRIME32_3 * (h32 ^ (h32 >> 13));
+    return h32 ^ (h32 >> 16);
+}
+
+// srand(): seed from screen_tc, numero_pass and date (:105-110)
+MCPT_DEV uint3 rng_seed(float tcx, float tcy, int numero_pass, float date) {
+    float k = float(1 + numero_pass);
+    float wx = tcx * k * 1.125f;
+    float wy = (float(numero_pass) * 3.14f + date) * k * 1.125f;
+    float wz = tcy * k * 1.125f;
+    return make_uint3(__float_as_uint(wx), __float_as_uint(wy), __float_as_uint(wz));
+}
+
+MCPT_DEV float random_float(uint3& s) {
+    uint32_t m = xxhash32(s);
+    m &= 0x007FFFFFu;
+    m |= 0x3F800000u;
+    float f = __uint_as_float(m);
+    s.x += 11u;
+    s.y += 43u;
+    s.z += 67u;
+    return f - 1.0f;
+}
+
+// ---- transcendental back-ends ---------------------------------------------
+template <bool FAST>
+struct Tm {
+    static MCPT_DEV float sin_(float x) { return FAST ? __sinf(x) : sinf(x); }
+    static MCPT_DEV float cos_(float x) { return FAST ? __cosf(x) : cosf(x); }
+    static MCPT_DEV float log_(float x) { return FAST ? __logf(x) : logf(x); }
+    static MCPT_DEV float pow_(float x, float y) { return FAST ? __powf(x, y) : powf(x, y); }
+};
+
+#define MCPT_PI 3.14159274101257324f /* float(2*acos(0)) */
+
+// sample_hemisphere, tp/montecarlo.frag:49-70
+template <bool FAST>
+MCPT_DEV f3 sample_hemisphere(float roughness, uint3& seed) {
+    float alpha = roughness * roughness;
+    float beta = 2.0f * MCPT_PI * random_float(seed);
+    float tanTheta2 = -alpha * alpha * Tm<FAST>::log_(1.0f - random_float(seed));
+    float cosTheta = 1.0f / sqrtf(1.0f + tanTheta2);
+    float sinTheta = sqrtf(fmaxf(0.0f, 1.0f - cosTheta * cosTheta));
+    f3 localDir = mk3(Tm<FAST>::cos_(beta) * sinTheta, Tm<FAST>::sin_(beta) * sinTheta, cosTheta);
+    return normalize3(localDir);
+}
+
+// random_ray, tp/montecarlo.frag:72-89: frame (U,V,D) around D, M * sample
+template <bool FAST>
+MCPT_DEV f3 random_ray(f3 D, float roughness, uint3& seed) {
+    f3 W = normalize3(mk3(D.x, D.y + 5.0f, D.z + 3.0f));
+    f3 U = normalize3(cross3(D, W));
+    f3 V = normalize3(cross3(D, U));
+    f3 s = sample_hemisphere<FAST>(roughness, seed);
+    // mat3(U,V,D) * s = U*s.x + V*s.y + D*s.z
+    f3 r = mk3(U.x * s.x + V.x * s.y + D.x * s.z, U.y * s.x + V.y * s.y + D.y * s.z, U.z * s.x + V.z * s.y + D.z * s.z);
+    return normalize3(r);
+}
+
+// rSchlick, tp/montecarlo.frag:91-98 (I is the incoming direction, as written)
+MCPT_DEV float r_schlick(f3 I, f3 N, float refract_ind) {
+    float r0 = (refract_ind - 1.0f) / (refract_ind + 1.0f);
+    r0 *= r0;
+    float x = 1.0f - dot3(N, I);
+    float v = r0 + (1.0f - r0) * x * x * x * x * x;
+    return fminf(fmaxf(v, 0.0f), 1.0f);
+}
+
+// ---- geometric info of a hit, raytracer_func.frag:783-897 -------------------
+// Returns false when the shape writes nothing (shape < 0): N, P keep their values.
+MCPT_DEV bool intersection_info(const DevScene& S, int prim, int sub, f3 pl, int flat_face, f3& N, f3& Pg) {
+    if (prim < 0) return false;
+    const DevPrim* pp = S.prims + prim;
+    Aff fwd;
+    fwd.r0 = __ldg(&pp->fwd.r0);
+    fwd.r1 = __ldg(&pp->fwd.r1);
+    fwd.r2 = __ldg(&pp->fwd.r2);
+    const int type = __ldg(&pp->type);
+    f3 P = xform_point(fwd, pl);  // closest_intersection.pg
+    f3 tip;                        // local point whose image gives the normal
+    switch (type) {
+        case MCPT_PRIM_MESH: {
+            const DevMesh& M = S.meshes[__ldg(&pp->mesh)];
+            uint32_t i0 = __ldg(M.idx + 3 * sub), i1 = __ldg(M.idx + 3 * sub + 1), i2 = __ldg(M.idx + 3 * sub + 2);
+            f3 A = mk3(__ldg(M.pos + 3 * i0), __ldg(M.pos + 3 * i0 + 1), __ldg(M.pos + 3 * i0 + 2));
+            f3 B = mk3(__ldg(M.pos + 3 * i1), __ldg(M.pos + 3 * i1 + 1), __ldg(M.pos + 3 * i1 + 2));
+            f3 C = mk3(__ldg(M.pos + 3 * i2), __ldg(M.pos + 3 * i2 + 1), __ldg(M.pos + 3 * i2 + 2));
+            if (flat_face) {
+                tip = pl + cross3(B - A, C - A);
+            } else {
+                f3 nA = mk3(__ldg(M.nrm + 3 * i0), __ldg(M.nrm + 3 * i0 + 1), __ldg(M.nrm + 3 * i0 + 2));
+                f3 nB = mk3(__ldg(M.nrm + 3 * i1), __ldg(M.nrm + 3 * i1 + 1), __ldg(M.nrm + 3 * i1 + 2));
+                f3 nC = mk3(__ldg(M.nrm + 3 * i2), __ldg(M.nrm + 3 * i2 + 1), __ldg(M.nrm + 3 * i2 + 2));
+                f3 PA = A - pl, PB = B - pl, PC = C - pl;
+                float tA = length3(cross3(PB, PC));
+                float tB = length3(cross3(PA, PC));
+                float tC = length3(cross3(PA, PB));
+                f3 No = nA * tA + nB * tB + nC * tC;
+                tip = pl + No;
+            }
+            break;
+        }
+        case MCPT_PRIM_SPHERE: tip = pl * 2.0f; break;
+        case MCPT_PRIM_CUBE: {
+            f3 No = mk3(0.0f, 0.0f, 0.0f);
+            float s = (sub % 2 != 0) ? 1.0f : -1.0f;
+            int ax = sub / 2;
+            if (ax == 0) No.x = s; else if (ax == 1) No.y = s; else No.z = s;
+            tip = pl + No;
+            break;
+        }
+        case MCPT_PRIM_CYLINDER: {
+            f3 No = mk3(0.0f, 0.0f, 0.0f);
+            if (sub < 2) No.z = (sub % 2 != 0) ? 1.0f : -1.0f;
+            else No = mk3(pl.x, pl.y, 0.0f);
+            tip = pl + No;
+            break;
+        }
+        case MCPT_PRIM_CONE: {
+            if (sub == 0) {
+                tip = mk3(pl.x, pl.y, pl.z - 1.0f);
+            } else if (sub == 2) {
+                f3 No = mk3(pl.x, pl.y, sqrtf(pl.x * pl.x + pl.y * pl.y) / 2.0f);
+                tip = pl + No;
+            } else {
+                Pg = P;
+                if (sub == 1) N = mk3(0.0f, 0.0f, 0.0f);
+                return true;
+            }
+            break;
+        }
+        case MCPT_PRIM_ORIENTED_QUAD: tip = pl + mk3(0.0f, 0.0f, 1.0f); break;
+        default: return false;
+    }
+    Pg = P;
+    N = normalize3(xform_point(fwd, tip) - P);
+    return true;
+}
+
+// ---- one iteration of random_path's loop body after a confirmed hit ---------
+// tp/montecarlo.frag:121-175. Outputs:
+//   kind 0: path ends, `total` is the value returned            (:174-175)
+//   kind 1: continue with ray (nO, nD) and attenuation new_att   (:141-144,156-159,169-172)
+//   kind 2: interior ray (nO, nD) must be traced first; the exit ray is derived
+//           from that hit by finish_interior()                   (:146-153,160-166)
+struct BounceOut {
+    int kind;
+    f3 nO, nD, new_att;
+};
+
+template <bool FAST>
+MCPT_DEV BounceOut bounce(f3 O, f3 D, f3 N, f3 P, float4 mat, float4 col, f3 attenu, f3& total, uint3& seed, float refract_ind) {
+    BounceOut out;
+    f3 c3 = mk3(col.x, col.y, col.z);
+    f3 ray = random_ray<FAST>(N, 1.0f - mat.y, seed);
+    float rs = r_schlick(D, N, refract_ind);
+    f3 R = reflect3(-ray, N);
+    f3 E = normalize3(O - P);
+    float se = mixf(100.0f, 2.0f, mat.y);
+    float spec = Tm<FAST>::pow_(fmaxf(0.0f, dot3(E, R)), se);
+
+    // total += col.xyz * 0.1 + attenu * mat.b * (1.0-mat.r) * col.a
+    total = total + (c3 * 0.1f + attenu * mat.z * (1.0f - mat.x) * col.w);
+
+    if (!(mat.z <= 0.5f)) {
+        out.kind = 0;
+        return out;
+    }
+    f3 mixed = mix3(attenu, c3, mat.x);
+    if (mat.x > 0.0f && col.w == 1.0f) {
+        out.new_att = c3 * attenu + attenu * col.w * rs * spec * mixed;
+        out.nO = P + N * MCPT_BIAS;
+        out.nD = random_ray<FAST>(reflect3(D, N), 1.0f - mat.x * mat.y, seed);
+        out.kind = 1;
+    } else if (col.w < 1.0f && mat.x == 0.0f) {
+        out.new_att = c3 * attenu + attenu * (1.0f - col.w) * (1.0f - rs) * spec * mixed;
+        out.nO = P - N * MCPT_BIAS;
+        out.nD = refract3(D, N, refract_ind);
+        out.kind = 2;
+    } else if (col.w < 1.0f && mat.x > 0.0f) {
+        float r = random_float(seed);
+        if (r > 0.5f) {
+            out.new_att = c3 * attenu + attenu * col.w * rs * spec * mixed;
+            out.nO = P + N * MCPT_BIAS;
+            out.nD = random_ray<FAST>(reflect3(D, N), 1.0f - mat.x * mat.y, seed);
+            out.kind = 1;
+        } else {
+            out.new_att = c3 * attenu + attenu * (1.0f - col.w) * (1.0f - rs) * spec * mixed;
+            out.nO = P - N * MCPT_BIAS;
+            out.nD = D;
+            out.kind = 2;
+        }
+    } else {
+        out.new_att = c3 * attenu + attenu * spec * mixed;
+        out.nO = P + N * MCPT_BIAS;
+        out.nD = ray;
+        out.kind = 1;
+    }
+    return out;
+}
+
+// fake sky, tp/montecarlo.frag:118-119
+MCPT_DEV f3 sky(f3 total, f3 attenu, f3 D) {
+    f3 c = mix3(mk3(0.5f, 0.5f, 0.9f), mk3(1.0f, 1.0f, 0.8f), fmaxf(0.0f, D.z));
+    return total + attenu * c;
+}
+
+}  // namespace mcpt

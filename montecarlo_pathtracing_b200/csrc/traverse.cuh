@@ -1,0 +1,199 @@
+// traverse.cuh — closest-hit traversal of the two-level scene
+// (replaces intersect_bvh / Mesh_intersect, shaders/raytracer_func.frag:642-678,
+// 734-781, and the AABB tests intersect_bv / intersect_bvm, :273-352).
+//
+// Design (B200): the reference walks the tree with an int[29] stack in local
+// memory, visits children in fixed left/right order and pays two dependent texel
+// fetches plus three vector divides per box. Here
+//   * the tree keeps the reference's implicit heap order, so the walk needs no
+//     stack at all: the node's heap index plus a 32-bit trail ("a sibling is still
+//     pending at this level") live in two registers per thread — nothing to spill,
+//     nothing to diverge on in memory;
+//   * children are visited near-first using the split axis that the builder cycles
+//     per level (bvh_gpu/bvh.cpp:45-51), and the far sibling is tested only when
+//     it is popped, against the by-then shorter ray;
+//   * a node is 32 bytes, fetched as two 16-byte vector loads; both children of a
+//     node share one 64-byte segment; the top levels come from shared memory;
+//   * the slab test runs on precomputed reciprocals with FMAs. It only culls:
+//     boxes are inflated at upload so it never rejects a box the exact arithmetic
+//     of the reference would accept, and candidates are ranked by the exact
+//     world-space distance (intersect.cuh).
+#pragma once
+#include "intersect.cuh"
+
+namespace mcpt {
+
+struct SmemScene {
+    const DevNode* top_nodes;   // staged top-level nodes, index 1-based like global
+    const DevPrim* prims;       // staged primitive records
+    const DevNode* mesh_nodes;  // staged per-mesh top levels, concatenated
+};
+
+MCPT_DEV DevNode load_node(const DevNode* p) {
+    DevNode n;
+    n.lo = __ldg(&p->lo);
+    n.hi = __ldg(&p->hi);
+    return n;
+}
+MCPT_DEV DevNode load_node_smem(const DevNode* p) { return *p; }
+
+// conservative slab test on [0, tmax]; idir = 1/dir, od = -origin*idir
+MCPT_DEV bool slab(const DevNode& n, f3 idir, f3 od, float tmax) {
+    float tx0 = __fmaf_rn(n.lo.x, idir.x, od.x), tx1 = __fmaf_rn(n.hi.x, idir.x, od.x);
+    float ty0 = __fmaf_rn(n.lo.y, idir.y, od.y), ty1 = __fmaf_rn(n.hi.y, idir.y, od.y);
+    float tz0 = __fmaf_rn(n.lo.z, idir.z, od.z), tz1 = __fmaf_rn(n.hi.z, idir.z, od.z);
+    float tn = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), 0.0f));
+    float tf = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), tmax));
+    return tn <= tf;
+}
+
+MCPT_DEV f3 safe_rcp3(f3 d) {
+    // 1/0 = inf is fine for slabs; keep the sign of zero out of it
+    return mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+}
+
+// Walk one mesh (second level). Oi/Di: ray in mesh-local space (Di normalised by
+// intersect_prim, raytracer_func.frag:688); Ow: world origin; fwd: mesh -> world.
+MCPT_DEV void mesh_walk(const DevMesh& M, const DevNode* smem_mesh_nodes, f3 Oi, f3 Di, f3 Ow, const Aff& fwd, int prim,
+                        int tslot, float slack, Best& best) {
+    // world length of one unit of local parameter: dist ~= a * scale
+    f3 wd = mk3(fwd.r0.x * Di.x + fwd.r0.y * Di.y + fwd.r0.z * Di.z, fwd.r1.x * Di.x + fwd.r1.y * Di.y + fwd.r1.z * Di.z,
+                fwd.r2.x * Di.x + fwd.r2.y * Di.y + fwd.r2.z * Di.z);
+    float scale = sqrtf(wd.x * wd.x + wd.y * wd.y + wd.z * wd.z);
+    if (!(scale > 0.0f)) return;  // zero or NaN direction: the shader finds nothing either
+    const float inv_scale = 1.0f / scale;
+    const f3 idir = safe_rcp3(Di);
+    const f3 od = mk3(-Oi.x * idir.x, -Oi.y * idir.y, -Oi.z * idir.z);
+    float tmax = (best.h.dist * 1.0001f + slack) * inv_scale;
+
+    const int depth = M.depth;
+    const uint32_t first_leaf = 1u << depth;
+    const uint32_t staged = uint32_t(M.smem_nodes);  // nodes with heap index <= staged live in smem
+    const DevNode* snodes = smem_mesh_nodes + M.smem_off - 1;  // 1-based
+    const DevNode* gnodes = M.nodes;                           // 1-based (entry 0 unused)
+    // near-first: level l splits along axis l % 3 with the smaller centres on the left
+    const uint32_t neg = (Di.x < 0.0f ? 1u : 0u) | (Di.y < 0.0f ? 2u : 0u) | (Di.z < 0.0f ? 4u : 0u);
+
+    uint32_t k = 1, trail = 0;
+    int level = 0, axis = 0;
+    while (true) {
+        bool descend = false;
+        if (k < first_leaf) {
+            DevNode n = (k <= staged) ? load_node_smem(snodes + k) : load_node(gnodes + k);
+            descend = slab(n, idir, od, tmax);
+        } else {
+            const DevTri* tp = M.tris + (k - first_leaf);
+            float4 ta = __ldg(&tp->a);
+            int tri = __float_as_int(ta.w);
+            if (tri >= 0) {
+                float4 tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+                float a;
+                if (triangle_test(best, fwd, mk3(ta.x, ta.y, ta.z), mk3(tb.x, tb.y, tb.z), mk3(tc.x, tc.y, tc.z), Oi, Di, Ow,
+                                  prim, tri, tslot, int(k - first_leaf), a))
+                    tmax = (best.h.dist * 1.0001f + slack) * inv_scale;
+            }
+        }
+        if (descend) {
+            k = 2u * k + ((neg >> axis) & 1u);
+            trail = (trail << 1) | 1u;
+            ++level;
+            axis = (axis == 2) ? 0 : axis + 1;
+            continue;
+        }
+        // pop: climb while no sibling is pending
+        while (level > 0 && !(trail & 1u)) {
+            trail >>= 1;
+            k >>= 1;
+            --level;
+            axis = (axis == 0) ? 2 : axis - 1;
+        }
+        if (level == 0) break;
+        k ^= 1u;
+        trail &= ~1u;
+    }
+}
+
+// intersect_prim, raytracer_func.frag:681-705
+MCPT_DEV void prim_test(const DevScene& S, const SmemScene& sm, int p, f3 O, f3 D, float slack, Best& best) {
+    const DevPrim* pp = (p < S.smem_prims) ? (sm.prims + p) : (S.prims + p);
+    const int type = pp->type;
+    if (type < 0) return;
+    Aff inv, fwd;
+    inv.r0 = pp->inv.r0;
+    inv.r1 = pp->inv.r1;
+    inv.r2 = pp->inv.r2;
+    fwd.r0 = pp->fwd.r0;
+    fwd.r1 = pp->fwd.r1;
+    fwd.r2 = pp->fwd.r2;
+    const int tslot = pp->slot;
+    f3 Oi = xform_point(inv, O);
+    f3 Di = normalize3(xform_vector(inv, D));
+    switch (type) {
+        case MCPT_PRIM_MESH:
+            mesh_walk(S.meshes[pp->mesh], sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
+            break;
+        case MCPT_PRIM_SPHERE: sphere_test(best, fwd, Oi, Di, O, p, tslot); break;
+        case MCPT_PRIM_CUBE: cube_test(best, fwd, Oi, Di, O, p, tslot); break;
+        case MCPT_PRIM_CYLINDER: cylinder_test(best, fwd, Oi, Di, O, p, tslot); break;
+        case MCPT_PRIM_CONE: cone_test(best, fwd, Oi, Di, O, p, tslot); break;
+        case MCPT_PRIM_ORIENTED_QUAD: quad_test(best, fwd, Oi, Di, O, p, tslot); break;
+        default: break;
+    }
+}
+
+// traverse_all_bvh, raytracer_func.frag:777-781. D need not be unit length.
+// any_hit: just_hit_bvh (:771-775) — stop at the first accepted candidate.
+MCPT_DEV void scene_walk(const DevScene& S, const SmemScene& sm, f3 O, f3 D, bool any_hit, Best& best) {
+    best_reset(best);
+    const float len = sqrtf(D.x * D.x + D.y * D.y + D.z * D.z);
+    if (!(len > 0.0f) || !(len < FLT_MAX)) return;  // zero / NaN / inf direction: nothing is hit
+    const float rl = 1.0f / len;
+    const f3 dn = mk3(D.x * rl, D.y * rl, D.z * rl);  // culling only
+    const f3 idir = safe_rcp3(dn);
+    const f3 od = mk3(-O.x * idir.x, -O.y * idir.y, -O.z * idir.z);
+    const float slack = 1e-4f * (fabsf(O.x) + fabsf(O.y) + fabsf(O.z)) + 1e-3f;
+    float tmax = FLT_MAX;
+
+    const int depth = S.top_depth;
+    const uint32_t first_leaf = 1u << depth;
+    const uint32_t staged = uint32_t(S.smem_top_nodes);
+    const DevNode* snodes = sm.top_nodes;  // 1-based
+    const DevNode* gnodes = S.top_nodes;   // 1-based
+    const uint32_t neg = (dn.x < 0.0f ? 1u : 0u) | (dn.y < 0.0f ? 2u : 0u) | (dn.z < 0.0f ? 4u : 0u);
+
+    uint32_t k = 1, trail = 0;
+    int level = 0, axis = 0;
+    while (true) {
+        DevNode n = (k <= staged) ? load_node_smem(snodes + k) : load_node(gnodes + k);
+        bool inside = slab(n, idir, od, tmax);
+        if (inside && k >= first_leaf) {
+            int p = __float_as_int(n.lo.w);
+            if (p >= 0) {
+                prim_test(S, sm, p, O, D, slack, best);
+                if (best.h.prim >= 0) {
+                    if (any_hit) return;
+                    tmax = best.h.dist * 1.0001f + slack;
+                }
+            }
+            inside = false;
+        }
+        if (inside) {
+            k = 2u * k + ((neg >> axis) & 1u);
+            trail = (trail << 1) | 1u;
+            ++level;
+            axis = (axis == 2) ? 0 : axis + 1;
+            continue;
+        }
+        while (level > 0 && !(trail & 1u)) {
+            trail >>= 1;
+            k >>= 1;
+            --level;
+            axis = (axis == 0) ? 2 : axis - 1;
+        }
+        if (level == 0) break;
+        k ^= 1u;
+        trail &= ~1u;
+    }
+}
+
+}  // namespace mcpt
