@@ -1,0 +1,250 @@
+// api.cu — context management and the C ABI of include/mcpt.h.
+//
+// Owns all device memory of a context: the re-packed scene (layout.cuh), the
+// accumulation buffer, and the SoA wavefront state sized for a batch of passes.
+// mcpt_render() drives the wavefront: for each batch of passes
+//   raygen -> { traverse -> shade -> compact -> [traverse -> shade_exit] } x bounces -> accumulate
+// with queue lengths kept on the device.
+#include <cuda_runtime.h>
+#include <dlfcn.h>
+
+#include <algorithm>
+#include <cfloat>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "kernels.cuh"
+#include "mcpt.h"
+
+using namespace mcpt;
+
+struct mcpt_ctx {
+    int device = 0;
+    int sm_count = 148;
+    cudaStream_t own_stream = nullptr;
+    cudaStream_t stream = nullptr;
+    std::string err;
+
+    // scene
+    std::vector<void*> scene_allocs;
+    DevScene scene{};
+    bool have_scene = false;
+
+    // viewer state
+    DevParams prm{};
+    CameraRays cam{};
+    mcpt_params user_params{};
+    bool have_camera = false;
+
+    // accumulation target
+    float4* accum = nullptr;
+    bool accum_owned = false;
+    size_t accum_bytes = 0;
+
+    // wavefront
+    Wavefront wf{};
+    std::vector<void*> wf_allocs;
+    uint64_t wf_capacity = 0;  // path slots
+    uint32_t* queue[3] = {nullptr, nullptr, nullptr};
+    uint32_t* counters = nullptr;  // 2 * max_bounces entries
+    int counters_len = 0;
+    unsigned long long* dev_stats = nullptr;  // [0] rays, [1] segments
+
+    // options
+    int opt_passes_per_batch = 0;  // 0 = auto
+    int opt_smem_staging = 1;
+    int opt_fast_math = 0;
+
+    uint64_t paths_started = 0;
+    unsigned long long launches_base = 0;
+};
+
+namespace {
+
+int fail(mcpt_ctx* c, int code, const char* fmt, ...) {
+    if (c) {
+        char buf[512];
+        va_list ap;
+        va_start(ap, fmt);
+        vsnprintf(buf, sizeof buf, fmt, ap);
+        va_end(ap);
+        c->err = buf;
+    }
+    return code;
+}
+
+#define CK(ctx, call)                                                                                   \
+    do {                                                                                                \
+        cudaError_t e_ = (call);                                                                        \
+        if (e_ != cudaSuccess)                                                                          \
+            return fail(ctx, e_ == cudaErrorMemoryAllocation ? MCPT_E_NOMEM : MCPT_E_CUDA, "%s: %s", #call, \
+                        cudaGetErrorString(e_));                                                        \
+    } while (0)
+
+template <class T>
+int dev_alloc(mcpt_ctx* c, std::vector<void*>& owner, T** out, size_t count) {
+    void* p = nullptr;
+    size_t bytes = std::max<size_t>(count, 1) * sizeof(T);
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return fail(c, MCPT_E_NOMEM, "cudaMalloc(%zu bytes): %s", bytes, cudaGetErrorString(e));
+    owner.push_back(p);
+    *out = static_cast<T*>(p);
+    return MCPT_OK;
+}
+
+void free_all(std::vector<void*>& v) {
+    for (void* p : v) cudaFree(p);
+    v.clear();
+}
+
+LaunchCfg lcfg(const mcpt_ctx* c) { return LaunchCfg{c->sm_count, c->stream}; }
+
+// rows of the affine part of a column-major mat4
+Aff rows_of(const float m[16]) {
+    Aff a;
+    a.r0 = make_float4(m[0], m[4], m[8], m[12]);
+    a.r1 = make_float4(m[1], m[5], m[9], m[13]);
+    a.r2 = make_float4(m[2], m[6], m[10], m[14]);
+    return a;
+}
+
+// Inflate a box so the FMA slab test (traverse.cuh) never rejects what the exact
+// arithmetic would accept. Empty boxes (min > max) stay empty.
+DevNode pack_node(const mcpt_bb& b, int aux) {
+    DevNode n;
+    float lo[3], hi[3];
+    for (int k = 0; k < 3; ++k) {
+        lo[k] = b.min[k];
+        hi[k] = b.max[k];
+        if (lo[k] <= hi[k]) {
+            float mag = std::max(std::fabs(lo[k]), std::fabs(hi[k]));
+            float pad = 1e-5f * std::max(mag, hi[k] - lo[k]) + 1e-7f;
+            lo[k] -= pad;
+            hi[k] += pad;
+        }
+    }
+    n.lo = make_float4(lo[0], lo[1], lo[2], 0.0f);
+    n.hi = make_float4(hi[0], hi[1], hi[2], 0.0f);
+    std::memcpy(&n.lo.w, &aux, sizeof aux);
+    return n;
+}
+
+DevNode empty_node() {
+    DevNode n;
+    int aux = -1;
+    n.lo = make_float4(FLT_MAX, FLT_MAX, FLT_MAX, 0.0f);
+    n.hi = make_float4(-FLT_MAX, -FLT_MAX, -FLT_MAX, 0.0f);
+    std::memcpy(&n.lo.w, &aux, sizeof aux);
+    return n;
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcpt_abi_version(void) { return MCPT_ABI_VERSION; }
+
+const char* mcpt_last_error(const mcpt_ctx* ctx) { return ctx ? ctx->err.c_str() : "null context"; }
+
+const char* mcpt_error_string(int code) {
+    switch (code) {
+        case MCPT_OK: return "ok";
+        case MCPT_E_INVALID: return "invalid argument or state";
+        case MCPT_E_CUDA: return "CUDA error";
+        case MCPT_E_NODEVICE: return "no CUDA device";
+        case MCPT_E_NOMEM: return "out of memory";
+        case MCPT_E_NCCL: return "NCCL error";
+        case MCPT_E_UNSUPPORTED: return "unsupported";
+    }
+    return "unknown error";
+}
+
+int mcpt_create(int device, mcpt_ctx** out) {
+    if (!out) return MCPT_E_INVALID;
+    *out = nullptr;
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess || n <= 0) return MCPT_E_NODEVICE;
+    if (device < 0 || device >= n) return MCPT_E_NODEVICE;
+    mcpt_ctx* c = new (std::nothrow) mcpt_ctx();
+    if (!c) return MCPT_E_NOMEM;
+    c->device = device;
+    if (cudaSetDevice(device) != cudaSuccess) {
+        delete c;
+        return MCPT_E_CUDA;
+    }
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) c->sm_count = prop.multiProcessorCount;
+    if (cudaStreamCreateWithFlags(&c->own_stream, cudaStreamNonBlocking) != cudaSuccess) {
+        delete c;
+        return MCPT_E_CUDA;
+    }
+    c->stream = c->own_stream;
+    void* p = nullptr;
+    if (cudaMalloc(&p, 2 * sizeof(unsigned long long)) != cudaSuccess) {
+        cudaStreamDestroy(c->own_stream);
+        delete c;
+        return MCPT_E_NOMEM;
+    }
+    c->dev_stats = static_cast<unsigned long long*>(p);
+    cudaMemset(c->dev_stats, 0, 2 * sizeof(unsigned long long));
+    c->prm.nb_bounces = 3;       // RTViewer defaults, montecarlo.cpp:126-141
+    c->prm.refract_ind = 1.0f;
+    c->user_params.nb_bounces = 3;
+    c->user_params.refract_ind = 1.0f;
+    c->launches_base = launches_issued();
+    *out = c;
+    return MCPT_OK;
+}
+
+int mcpt_destroy(mcpt_ctx* c) {
+    if (!c) return MCPT_E_INVALID;
+    cudaSetDevice(c->device);
+    cudaStreamSynchronize(c->stream);
+    free_all(c->scene_allocs);
+    free_all(c->wf_allocs);
+    if (c->accum_owned && c->accum) cudaFree(c->accum);
+    if (c->dev_stats) cudaFree(c->dev_stats);
+    if (c->own_stream) cudaStreamDestroy(c->own_stream);
+    delete c;
+    return MCPT_OK;
+}
+
+int mcpt_set_stream(mcpt_ctx* c, void* s) {
+    if (!c) return MCPT_E_INVALID;
+    c->stream = s ? static_cast<cudaStream_t>(s) : c->own_stream;
+    return MCPT_OK;
+}
+
+int mcpt_synchronize(mcpt_ctx* c) {
+    if (!c) return MCPT_E_INVALID;
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return MCPT_OK;
+}
+
+int mcpt_set_option(mcpt_ctx* c, int option, int value) {
+    if (!c) return MCPT_E_INVALID;
+    switch (option) {
+        case MCPT_OPT_PASSES_PER_BATCH:
+            if (value < 0) return fail(c, MCPT_E_INVALID, "passes per batch must be >= 0");
+            c->opt_passes_per_batch = value;
+            return MCPT_OK;
+        case MCPT_OPT_SMEM_STAGING:
+            c->opt_smem_staging = value ? 1 : 0;
+            if (c->have_scene) return fail(c, MCPT_E_INVALID, "set MCPT_OPT_SMEM_STAGING before mcpt_upload_scene");
+            return MCPT_OK;
+        case MCPT_OPT_FAST_MATH: c->opt_fast_math = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_SORT_QUEUES: return MCPT_OK;
+    }
+    return fail(c, MCPT_E_INVALID, "unknown option %d", option);
+}
+
+}  // extern "C"
+
+#include "api_scene.inl"
+#include "api_render.inl"

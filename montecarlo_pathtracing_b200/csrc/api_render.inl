@@ -1,0 +1,320 @@
+// api_render.inl — viewer-facing half of the C ABI: resize / camera / params /
+// clear / render / resolve / accumulation access / NCCL reduce / ray batches.
+// Included by api.cu.
+
+namespace {
+
+// wavefront buffers for `slots` path slots and up to `bounces` bounces
+int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
+    if (slots > 0x7fffff00ull) return fail(c, MCPT_E_INVALID, "batch of %llu paths is too large", (unsigned long long)slots);
+    if (slots > c->wf_capacity) {
+        CK(c, cudaStreamSynchronize(c->stream));
+        free_all(c->wf_allocs);
+        c->wf_capacity = 0;
+        c->counters = nullptr;
+        c->counters_len = 0;
+        Wavefront& w = c->wf;
+        int rc;
+        if ((rc = dev_alloc(c, c->wf_allocs, &w.ray_o, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.ray_d, slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &w.hit_a, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.hit_b, slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &w.attenu, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.total, slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &w.seed, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.keep_n, slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &w.keep_p, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.result, slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &w.flag, slots)) || (rc = dev_alloc(c, c->wf_allocs, &c->queue[0], slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &c->queue[1], slots)) || (rc = dev_alloc(c, c->wf_allocs, &c->queue[2], slots))) {
+            free_all(c->wf_allocs);
+            return rc;
+        }
+        c->wf_capacity = slots;
+    }
+    const int need = 2 * std::max(bounces, 1);
+    if (need > c->counters_len) {
+        int rc = dev_alloc(c, c->wf_allocs, &c->counters, size_t(need));
+        if (rc) return rc;
+        c->counters_len = need;
+    }
+    return MCPT_OK;
+}
+
+int passes_per_batch(const mcpt_ctx* c, uint32_t npix) {
+    if (c->opt_passes_per_batch > 0) return c->opt_passes_per_batch;
+    uint64_t target = 8ull << 20;  // ~8M paths in flight
+    uint64_t ppb = target / std::max<uint32_t>(npix, 1);
+    return int(std::min<uint64_t>(std::max<uint64_t>(ppb, 1), 64));
+}
+
+// raytracer.vert:9-22 evaluated for the four strip vertices, in fp32
+void camera_rays(const float iv[16], const float ipv[16], CameraRays& out) {
+    // P4 = invV * vec4(0,0,0,1)
+    float P[3];
+    for (int r = 0; r < 3; ++r) P[r] = iv[0 + r] * 0.0f + iv[4 + r] * 0.0f + iv[8 + r] * 0.0f + iv[12 + r] * 1.0f;
+    for (int r = 0; r < 3; ++r) out.ori[r] = P[r];
+    for (int vid = 0; vid < 4; ++vid) {
+        float tcx = float(vid % 2), tcy = float(vid / 2);
+        float cx = 2.0f * tcx - 1.0f, cy = 2.0f * tcy - 1.0f;
+        float Q[4];
+        for (int r = 0; r < 4; ++r) Q[r] = ipv[0 + r] * cx + ipv[4 + r] * cy + ipv[8 + r] * 1.0f + ipv[12 + r] * 1.0f;
+        float d[3];
+        for (int r = 0; r < 3; ++r) d[r] = Q[r] / Q[3] - P[r];
+        float inv = 1.0f / sqrtf(d[0] * d[0] + d[1] * d[1] + d[2] * d[2]);
+        for (int r = 0; r < 3; ++r) out.dir[vid][r] = d[r] * inv;
+    }
+}
+
+}  // namespace
+
+extern "C" {
+
+int mcpt_resize(mcpt_ctx* c, int w, int h) {
+    if (!c) return MCPT_E_INVALID;
+    if (w <= 0 || h <= 0 || int64_t(w) * h > (int64_t(1) << 28)) return fail(c, MCPT_E_INVALID, "bad size %dx%d", w, h);
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaStreamSynchronize(c->stream));
+    if (c->accum_owned && c->accum) cudaFree(c->accum);
+    c->accum = nullptr;
+    c->accum_owned = false;
+    c->accum_bytes = size_t(w) * h * sizeof(float4);
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, c->accum_bytes);
+    if (e != cudaSuccess) return fail(c, MCPT_E_NOMEM, "accumulation buffer: %s", cudaGetErrorString(e));
+    c->accum = static_cast<float4*>(p);
+    c->accum_owned = true;
+    c->prm.width = w;
+    c->prm.height = h;
+    CK(c, cudaMemsetAsync(c->accum, 0, c->accum_bytes, c->stream));
+    return MCPT_OK;
+}
+
+int mcpt_set_camera(mcpt_ctx* c, const float inv_v[16], const float inv_pv[16]) {
+    if (!c || !inv_v || !inv_pv) return MCPT_E_INVALID;
+    std::memcpy(c->prm.inv_v, inv_v, sizeof c->prm.inv_v);
+    std::memcpy(c->prm.inv_pv, inv_pv, sizeof c->prm.inv_pv);
+    camera_rays(inv_v, inv_pv, c->cam);
+    c->have_camera = true;
+    return MCPT_OK;
+}
+
+int mcpt_set_params(mcpt_ctx* c, const mcpt_params* p) {
+    if (!c || !p) return MCPT_E_INVALID;
+    if (p->nb_bounces < 0 || p->nb_bounces > 4096) return fail(c, MCPT_E_INVALID, "nb_bounces %d out of range", p->nb_bounces);
+    if (p->mode < 0 || p->mode > 2) return fail(c, MCPT_E_INVALID, "mode %d out of range", p->mode);
+    c->user_params = *p;
+    c->prm.nb_bounces = p->nb_bounces;
+    c->prm.refract_ind = p->refract_ind;
+    c->prm.date = p->date;
+    c->prm.flat_face = p->flat_face;
+    c->prm.mode = p->mode;
+    return MCPT_OK;
+}
+
+int mcpt_clear(mcpt_ctx* c) {
+    if (!c) return MCPT_E_INVALID;
+    if (!c->accum) return fail(c, MCPT_E_INVALID, "mcpt_clear before mcpt_resize");
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMemsetAsync(c->accum, 0, c->accum_bytes, c->stream));
+    return MCPT_OK;
+}
+
+int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
+    if (!c) return MCPT_E_INVALID;
+    if (!c->have_scene) return fail(c, MCPT_E_INVALID, "mcpt_render before mcpt_upload_scene");
+    if (!c->accum) return fail(c, MCPT_E_INVALID, "mcpt_render before mcpt_resize");
+    if (!c->have_camera) return fail(c, MCPT_E_INVALID, "mcpt_render before mcpt_set_camera");
+    if (n_passes < 0) return fail(c, MCPT_E_INVALID, "n_passes < 0");
+    if (n_passes == 0) return MCPT_OK;
+    CK(c, cudaSetDevice(c->device));
+    const uint32_t npix = uint32_t(c->prm.width) * uint32_t(c->prm.height);
+    const int ppb = std::min(passes_per_batch(c, npix), n_passes);
+    // mode 1/2 are single-traversal debug shaders; mode 0 loops NB_BOUNCES times
+    const int iters = (c->prm.mode != 0) ? 1 : c->prm.nb_bounces;
+    int rc = ensure_wavefront(c, uint64_t(npix) * ppb, iters);
+    if (rc) return rc;
+    const LaunchCfg lc = lcfg(c);
+    const DevScene& S = c->scene;
+
+    for (int b0 = 0; b0 < n_passes; b0 += ppb) {
+        const int nb = std::min(ppb, n_passes - b0);
+        const uint32_t slots = npix * uint32_t(nb);
+        CK(c, cudaMemsetAsync(c->counters, 0, sizeof(uint32_t) * c->counters_len, c->stream));
+        launch_raygen(lc, c->prm, c->cam, c->wf, first_pass + b0, nb, npix);
+        uint32_t* q_cur = nullptr;  // identity queue for the first bounce
+        const uint32_t* n_cur = nullptr;
+        int spare = 0;  // queue[spare] receives survivors
+        for (int it = 0; it < iters; ++it) {
+            const bool last = (it == iters - 1);
+            launch_traverse(lc, S, c->wf, q_cur, n_cur, slots, c->dev_stats + 0);
+            QueueSet q{};
+            q.cur = q_cur;
+            q.n_cur = n_cur;
+            q.n_cur_host = slots;
+            q.next = c->queue[spare];
+            q.interior = c->queue[2];
+            q.n_next = c->counters + 2 * it;
+            q.n_interior = c->counters + 2 * it + 1;
+            q.seg_counter = c->dev_stats + 1;
+            launch_shade(lc, S, c->prm, c->wf, q, last, c->opt_fast_math != 0);
+            if (last) break;
+            launch_compact(lc, c->wf, q);
+            launch_traverse(lc, S, c->wf, q.interior, q.n_interior, 0, c->dev_stats + 0);
+            launch_shade_exit(lc, S, c->prm, c->wf, q.interior, q.n_interior);
+            q_cur = q.next;
+            n_cur = q.n_next;
+            spare ^= 1;
+        }
+        launch_accumulate(lc, c->wf, c->accum, npix, nb);
+        c->paths_started += slots;
+    }
+    CK(c, cudaGetLastError());
+    return MCPT_OK;
+}
+
+int mcpt_resolve(mcpt_ctx* c, float divisor, int subsampling, void* dst, int dst_kind) {
+    if (!c || !dst) return MCPT_E_INVALID;
+    if (!c->accum) return fail(c, MCPT_E_INVALID, "mcpt_resolve before mcpt_resize");
+    if (subsampling < 1 || subsampling > 64) return fail(c, MCPT_E_INVALID, "subsampling %d out of range", subsampling);
+    if (dst_kind < 0 || dst_kind > 3) return fail(c, MCPT_E_INVALID, "bad dst_kind %d", dst_kind);
+    CK(c, cudaSetDevice(c->device));
+    const bool rgba8 = (dst_kind == MCPT_DST_HOST_RGBA8 || dst_kind == MCPT_DST_DEVICE_RGBA8);
+    const bool host = (dst_kind == MCPT_DST_HOST_RGB32F || dst_kind == MCPT_DST_HOST_RGBA8);
+    const size_t n = size_t(c->prm.width) * subsampling * size_t(c->prm.height) * subsampling;
+    const size_t bytes = n * (rgba8 ? 4 : 3 * sizeof(float));
+    const LaunchCfg lc = lcfg(c);
+    if (!host) {
+        launch_resolve(lc, c->accum, c->prm.width, c->prm.height, divisor, subsampling, dst, rgba8);
+        CK(c, cudaGetLastError());
+        return MCPT_OK;
+    }
+    void* tmp = nullptr;
+    CK(c, cudaMalloc(&tmp, bytes));
+    launch_resolve(lc, c->accum, c->prm.width, c->prm.height, divisor, subsampling, tmp, rgba8);
+    cudaError_t e = cudaMemcpyAsync(dst, tmp, bytes, cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(tmp);
+    if (e != cudaSuccess) return fail(c, MCPT_E_CUDA, "resolve readback: %s", cudaGetErrorString(e));
+    return MCPT_OK;
+}
+
+int mcpt_get_accum(mcpt_ctx* c, float** dev_ptr, size_t* bytes) {
+    if (!c || !dev_ptr || !bytes) return MCPT_E_INVALID;
+    if (!c->accum) return fail(c, MCPT_E_INVALID, "no accumulation buffer (call mcpt_resize)");
+    *dev_ptr = reinterpret_cast<float*>(c->accum);
+    *bytes = c->accum_bytes;
+    return MCPT_OK;
+}
+
+int mcpt_bind_accum(mcpt_ctx* c, float* dev_ptr, size_t bytes) {
+    if (!c || !dev_ptr) return MCPT_E_INVALID;
+    if (c->prm.width <= 0) return fail(c, MCPT_E_INVALID, "mcpt_bind_accum before mcpt_resize");
+    if (bytes < c->accum_bytes) return fail(c, MCPT_E_INVALID, "buffer of %zu bytes < %zu needed", bytes, c->accum_bytes);
+    if ((reinterpret_cast<uintptr_t>(dev_ptr) & 15u) != 0) return fail(c, MCPT_E_INVALID, "buffer must be 16-byte aligned");
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaStreamSynchronize(c->stream));
+    if (c->accum_owned && c->accum) cudaFree(c->accum);
+    c->accum = reinterpret_cast<float4*>(dev_ptr);
+    c->accum_owned = false;
+    return MCPT_OK;
+}
+
+int mcpt_read_accum(mcpt_ctx* c, float* host_rgba, size_t bytes) {
+    if (!c || !host_rgba) return MCPT_E_INVALID;
+    if (!c->accum || bytes < c->accum_bytes) return fail(c, MCPT_E_INVALID, "bad accumulation read");
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMemcpyAsync(host_rgba, c->accum, c->accum_bytes, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return MCPT_OK;
+}
+
+int mcpt_write_accum(mcpt_ctx* c, const float* host_rgba, size_t bytes) {
+    if (!c || !host_rgba) return MCPT_E_INVALID;
+    if (!c->accum || bytes < c->accum_bytes) return fail(c, MCPT_E_INVALID, "bad accumulation write");
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMemcpyAsync(c->accum, host_rgba, c->accum_bytes, cudaMemcpyHostToDevice, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    return MCPT_OK;
+}
+
+int mcpt_reduce_nccl(mcpt_ctx* c, void* nccl_comm, int root) {
+    if (!c || !nccl_comm) return MCPT_E_INVALID;
+    if (!c->accum) return fail(c, MCPT_E_INVALID, "no accumulation buffer");
+    // ncclResult_t ncclReduce(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, int, ncclComm_t, cudaStream_t)
+    typedef int (*reduce_fn)(const void*, void*, size_t, int, int, int, void*, cudaStream_t);
+    static reduce_fn fn = nullptr;
+    if (!fn) {
+        fn = reinterpret_cast<reduce_fn>(dlsym(RTLD_DEFAULT, "ncclReduce"));
+        if (!fn) {
+            void* h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+            if (h) fn = reinterpret_cast<reduce_fn>(dlsym(h, "ncclReduce"));
+        }
+        if (!fn) return fail(c, MCPT_E_NCCL, "ncclReduce not found (no libnccl loaded)");
+    }
+    CK(c, cudaSetDevice(c->device));
+    const int nccl_float32 = 7, nccl_sum = 0;
+    int r = fn(c->accum, c->accum, c->accum_bytes / sizeof(float), nccl_float32, nccl_sum, root, nccl_comm, c->stream);
+    if (r != 0) return fail(c, MCPT_E_NCCL, "ncclReduce failed with %d", r);
+    return MCPT_OK;
+}
+
+int mcpt_trace_rays_device(mcpt_ctx* c, int64_t n, const float* o4, const float* d4, mcpt_hit* out_dev, int any_hit) {
+    if (!c || n < 0 || (n > 0 && (!o4 || !d4 || !out_dev))) return MCPT_E_INVALID;
+    if (!c->have_scene) return fail(c, MCPT_E_INVALID, "mcpt_trace_rays before mcpt_upload_scene");
+    if (n == 0) return MCPT_OK;
+    CK(c, cudaSetDevice(c->device));
+    launch_trace(lcfg(c), c->scene, n, reinterpret_cast<const float4*>(o4), reinterpret_cast<const float4*>(d4), out_dev,
+                 any_hit != 0);
+    CK(c, cudaGetLastError());
+    return MCPT_OK;
+}
+
+int mcpt_trace_rays(mcpt_ctx* c, int64_t n, const float* o, const float* d, mcpt_hit* out, int any_hit) {
+    if (!c || n < 0 || (n > 0 && (!o || !d || !out))) return MCPT_E_INVALID;
+    if (!c->have_scene) return fail(c, MCPT_E_INVALID, "mcpt_trace_rays before mcpt_upload_scene");
+    if (n == 0) return MCPT_OK;
+    CK(c, cudaSetDevice(c->device));
+    std::vector<float4> ho(n), hd(n);
+    for (int64_t i = 0; i < n; ++i) {
+        ho[i] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], 0.0f);
+        hd[i] = make_float4(d[3 * i], d[3 * i + 1], d[3 * i + 2], 0.0f);
+    }
+    float4 *dev_o = nullptr, *dev_d = nullptr;
+    mcpt_hit* dev_h = nullptr;
+    cudaError_t e = cudaMalloc(&dev_o, n * sizeof(float4));
+    if (e == cudaSuccess) e = cudaMalloc(&dev_d, n * sizeof(float4));
+    if (e == cudaSuccess) e = cudaMalloc(&dev_h, n * sizeof(mcpt_hit));
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dev_o, ho.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(dev_d, hd.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
+    if (e == cudaSuccess) {
+        launch_trace(lcfg(c), c->scene, n, dev_o, dev_d, dev_h, any_hit != 0);
+        e = cudaGetLastError();
+    }
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dev_h, n * sizeof(mcpt_hit), cudaMemcpyDeviceToHost, c->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    cudaFree(dev_o);
+    cudaFree(dev_d);
+    cudaFree(dev_h);
+    if (e != cudaSuccess) return fail(c, MCPT_E_CUDA, "trace_rays: %s", cudaGetErrorString(e));
+    return MCPT_OK;
+}
+
+int mcpt_get_stats(mcpt_ctx* c, mcpt_stats* out) {
+    if (!c || !out) return MCPT_E_INVALID;
+    CK(c, cudaSetDevice(c->device));
+    unsigned long long h[2] = {0, 0};
+    CK(c, cudaMemcpyAsync(h, c->dev_stats, sizeof h, cudaMemcpyDeviceToHost, c->stream));
+    CK(c, cudaStreamSynchronize(c->stream));
+    out->paths = c->paths_started;
+    out->rays = h[0];
+    out->segments = h[1];
+    out->launches = launches_issued() - c->launches_base;
+    return MCPT_OK;
+}
+
+int mcpt_reset_stats(mcpt_ctx* c) {
+    if (!c) return MCPT_E_INVALID;
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaMemsetAsync(c->dev_stats, 0, 2 * sizeof(unsigned long long), c->stream));
+    c->paths_started = 0;
+    c->launches_base = launches_issued();
+    return MCPT_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,174 @@
+// api_scene.inl — mcpt_upload_scene: validate the reference-layout tables and
+// re-pack them into the device layout of layout.cuh. Included by api.cu.
+
+namespace {
+
+template <class T>
+int upload_vec(mcpt_ctx* c, const std::vector<T>& h, T** out) {
+    int rc = dev_alloc(c, c->scene_allocs, out, h.size());
+    if (rc) return rc;
+    if (!h.empty()) CK(c, cudaMemcpy(*out, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+    return MCPT_OK;
+}
+
+int validate_bvh(mcpt_ctx* c, const mcpt_bvh_desc& b, int n_items, const char* what) {
+    if (!b.bb || !b.ind) return fail(c, MCPT_E_INVALID, "%s: null BVH arrays", what);
+    if (b.depth < 1 || b.depth > 29) return fail(c, MCPT_E_INVALID, "%s: BVH depth %d out of range [1,29]", what, b.depth);
+    const int64_t n_leaves = int64_t(1) << b.depth;
+    for (int64_t s = 0; s < n_leaves; ++s)
+        if (b.ind[s] < -1 || b.ind[s] >= n_items)
+            return fail(c, MCPT_E_INVALID, "%s: leaf slot %lld holds index %d (have %d items)", what, (long long)s, b.ind[s],
+                        n_items);
+    return MCPT_OK;
+}
+
+}  // namespace
+
+extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
+    if (!c || !d) return MCPT_E_INVALID;
+    CK(c, cudaSetDevice(c->device));
+    if (d->n_prims < 0 || (d->n_prims > 0 && !d->prim_data)) return fail(c, MCPT_E_INVALID, "bad primitive table");
+    if (d->n_meshes < 0 || (d->n_meshes > 0 && !d->meshes)) return fail(c, MCPT_E_INVALID, "bad mesh table");
+    int rc = validate_bvh(c, d->root, d->n_prims, "root");
+    if (rc) return rc;
+    for (int m = 0; m < d->n_meshes; ++m) {
+        const mcpt_mesh_desc& md = d->meshes[m];
+        if (!md.tri_idx || !md.pos || !md.nrm) return fail(c, MCPT_E_INVALID, "mesh %d: null arrays", m);
+        rc = validate_bvh(c, md.bvh, int(md.n_tris), "mesh");
+        if (rc) return rc;
+        for (uint64_t i = 0; i < 3ull * md.n_tris; ++i)
+            if (md.tri_idx[i] >= md.n_verts) return fail(c, MCPT_E_INVALID, "mesh %d: vertex index out of range", m);
+    }
+
+    CK(c, cudaStreamSynchronize(c->stream));
+    free_all(c->scene_allocs);
+    c->have_scene = false;
+    DevScene S{};
+
+    // ---- primitive records + shading tables
+    std::vector<DevPrim> prims(d->n_prims);
+    std::vector<float4> color(d->n_prims), mat(d->n_prims);
+    for (int i = 0; i < d->n_prims; ++i) {
+        const mcpt_prim_data& pd = d->prim_data[i];
+        DevPrim& p = prims[i];
+        std::memset(&p, 0, sizeof p);
+        p.type = int(pd.type[0]);  // int(texel.x), raytracer_func.frag:171-178
+        p.mesh = -1;
+        p.slot = -1;
+        p.inv = rows_of(pd.inv_transfo);
+        if (p.type == MCPT_PRIM_MESH) {
+            p.fwd = rows_of(pd.mesh_transfo);
+            const int line = int(pd.type[1]);
+            for (int m = 0; m < d->n_meshes; ++m)
+                if (d->meshes[m].mesh_line == line) p.mesh = m;
+            if (p.mesh < 0) return fail(c, MCPT_E_INVALID, "primitive %d: no mesh with mesh_line %d", i, line);
+        } else {
+            p.fwd = rows_of(pd.transfo);
+            if (p.type > MCPT_PRIM_ORIENTED_QUAD) p.type = -1;  // the shader's switch has no such case
+        }
+        color[i] = make_float4(pd.color[0], pd.color[1], pd.color[2], pd.color[3]);
+        mat[i] = make_float4(pd.mat_info[0], pd.mat_info[1], pd.mat_info[2], pd.mat_info[3]);
+    }
+
+    // ---- top-level tree: 1-based heap array, leaf level carries the primitive id
+    const int td = d->root.depth;
+    const uint32_t t_first_leaf = 1u << td, t_nodes = 2u << td;  // indices 1 .. t_nodes-1
+    std::vector<DevNode> top(t_nodes, empty_node());
+    for (uint32_t k = 1; k < t_nodes; ++k) {
+        int aux = -1;
+        bool empty = false;
+        if (k >= t_first_leaf) {
+            aux = d->root.ind[k - t_first_leaf];
+            empty = aux < 0;
+            if (!empty && prims[aux].slot < 0) prims[aux].slot = int(k - t_first_leaf);
+        }
+        if (!empty) top[k] = pack_node(d->root.bb[k - 1], aux);
+    }
+
+    // ---- meshes
+    std::vector<DevMesh> meshes(d->n_meshes);
+    for (int m = 0; m < d->n_meshes; ++m) {
+        const mcpt_mesh_desc& md = d->meshes[m];
+        const int depth = md.bvh.depth;
+        const uint32_t first_leaf = 1u << depth;
+        std::vector<DevNode> nodes(first_leaf, empty_node());  // interior nodes 1 .. first_leaf-1
+        for (uint32_t k = 1; k < first_leaf; ++k) nodes[k] = pack_node(md.bvh.bb[k - 1], -1);
+        std::vector<DevTri> tris(first_leaf);
+        for (uint32_t s = 0; s < first_leaf; ++s) {
+            int t = md.bvh.ind[s];
+            DevTri& T = tris[s];
+            T.a = T.b = T.c = make_float4(0, 0, 0, 0);
+            if (t >= 0) {
+                const uint32_t* ix = md.tri_idx + 3 * size_t(t);
+                const float *A = md.pos + 3 * size_t(ix[0]), *B = md.pos + 3 * size_t(ix[1]), *C = md.pos + 3 * size_t(ix[2]);
+                T.a = make_float4(A[0], A[1], A[2], 0);
+                T.b = make_float4(B[0], B[1], B[2], 0);
+                T.c = make_float4(C[0], C[1], C[2], 0);
+            }
+            std::memcpy(&T.a.w, &t, sizeof t);
+        }
+        std::vector<uint32_t> idx(md.tri_idx, md.tri_idx + 3 * size_t(md.n_tris));
+        std::vector<float> pos(md.pos, md.pos + 3 * size_t(md.n_verts)), nrm(md.nrm, md.nrm + 3 * size_t(md.n_verts));
+        DevMesh& M = meshes[m];
+        DevNode* dn = nullptr;
+        DevTri* dt = nullptr;
+        uint32_t* di = nullptr;
+        float *dp = nullptr, *dnr = nullptr;
+        if ((rc = upload_vec(c, nodes, &dn)) || (rc = upload_vec(c, tris, &dt)) || (rc = upload_vec(c, idx, &di)) ||
+            (rc = upload_vec(c, pos, &dp)) || (rc = upload_vec(c, nrm, &dnr)))
+            return rc;
+        M.nodes = dn;
+        M.tris = dt;
+        M.idx = di;
+        M.pos = dp;
+        M.nrm = dnr;
+        M.depth = depth;
+        M.n_tris = int(md.n_tris);
+        M.smem_off = 0;
+        M.smem_nodes = 0;
+    }
+
+    // ---- shared-memory staging plan (<= 40 KB so no opt-in is needed and
+    // several CTAs stay resident per SM)
+    S.smem_top_nodes = 0;
+    S.smem_prims = 0;
+    S.smem_mesh_nodes = 0;
+    if (c->opt_smem_staging) {
+        uint32_t keep = t_nodes - 1;            // all top-level nodes ...
+        while (keep > 511) keep >>= 1;          // ... or the top levels that fit 16 KB
+        S.smem_top_nodes = int(keep);
+        S.smem_prims = std::min(d->n_prims, 64);
+        if (d->n_meshes > 0) {
+            int share = 512 / d->n_meshes;  // nodes per mesh out of a 16 KB budget
+            int off = 0;
+            for (DevMesh& M : meshes) {
+                int cnt = (1 << M.depth) - 1;
+                while (cnt > share) cnt >>= 1;  // 2^L - 1 stays of that form
+                M.smem_off = off;
+                M.smem_nodes = cnt;
+                off += cnt;
+            }
+            S.smem_mesh_nodes = off;
+        }
+    }
+    S.smem_bytes = int(sizeof(DevNode)) * (S.smem_top_nodes + 1 + S.smem_mesh_nodes) + int(sizeof(DevPrim)) * S.smem_prims;
+
+    DevNode* d_top = nullptr;
+    DevPrim* d_prims = nullptr;
+    float4 *d_color = nullptr, *d_mat = nullptr;
+    DevMesh* d_meshes = nullptr;
+    if ((rc = upload_vec(c, top, &d_top)) || (rc = upload_vec(c, prims, &d_prims)) || (rc = upload_vec(c, color, &d_color)) ||
+        (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)))
+        return rc;
+    S.top_nodes = d_top;
+    S.prims = d_prims;
+    S.color = d_color;
+    S.mat = d_mat;
+    S.meshes = d_meshes;
+    S.top_depth = td;
+    S.n_prims = d->n_prims;
+    S.n_meshes = d->n_meshes;
+    c->scene = S;
+    c->have_scene = true;
+    return MCPT_OK;
+}

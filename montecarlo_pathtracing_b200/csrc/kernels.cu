@@ -1,0 +1,185 @@
+// kernels.cu — the wavefront stages as sm_100a kernels.
+//
+// Compiled with -fmad=false (see vecmath.cuh). All kernels are grid-stride over a
+// device-resident work count, launched with a fixed grid that is a multiple of
+// the SM count, so a bounce never needs a host round trip to size its launches.
+#include <cfloat>
+#include <cstdio>
+
+#include "kernels.cuh"
+#include "mcpt.h"
+#include "shade.cuh"
+#include "traverse.cuh"
+
+namespace mcpt {
+
+static unsigned long long g_launches = 0;
+unsigned long long launches_issued() { return g_launches; }
+
+constexpr int kBlock = 256;
+
+static inline int grid_for(const LaunchCfg& lc, uint64_t n, int blocks_per_sm) {
+    uint64_t want = (n + kBlock - 1) / kBlock;
+    uint64_t cap = uint64_t(lc.sm_count) * uint64_t(blocks_per_sm);
+    if (want > cap) want = cap;
+    if (want < 1) want = 1;
+    return int(want);
+}
+
+// ------------------------------------------------------------------ staging
+// Copy the staged part of the scene (top-level nodes, primitive records, top
+// levels of every mesh tree) into dynamic shared memory. Layout:
+//   [top nodes: 1 + smem_top_nodes][mesh nodes: smem_mesh_nodes][prims: smem_prims]
+// Index 0 of the top-node block is unused so heap indices stay 1-based.
+__device__ __forceinline__ SmemScene stage_scene(const DevScene& S, unsigned char* smem) {
+    DevNode* top = reinterpret_cast<DevNode*>(smem);
+    DevNode* mesh = top + (S.smem_top_nodes + 1);
+    DevPrim* prims = reinterpret_cast<DevPrim*>(mesh + S.smem_mesh_nodes);
+    {
+        const float4* src = reinterpret_cast<const float4*>(S.top_nodes);
+        float4* dst = reinterpret_cast<float4*>(top);
+        const int n4 = (S.smem_top_nodes + 1) * 2;
+        for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    for (int m = 0; m < S.n_meshes; ++m) {
+        const DevMesh& M = S.meshes[m];
+        if (M.smem_nodes <= 0) continue;
+        const float4* src = reinterpret_cast<const float4*>(M.nodes + 1);
+        float4* dst = reinterpret_cast<float4*>(mesh + M.smem_off);
+        const int n4 = M.smem_nodes * 2;
+        for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    {
+        const float4* src = reinterpret_cast<const float4*>(S.prims);
+        float4* dst = reinterpret_cast<float4*>(prims);
+        const int n4 = S.smem_prims * int(sizeof(DevPrim) / sizeof(float4));
+        for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
+    __syncthreads();
+    SmemScene sm;
+    sm.top_nodes = top;
+    sm.prims = prims;
+    sm.mesh_nodes = mesh;
+    return sm;
+}
+
+// ------------------------------------------------------------------- raygen
+// raytracer.vert:9-22 + main.frag + raytrace()/srand() (tp/montecarlo.frag:182-188):
+// Dir_in is the barycentric interpolation, over the two triangles of the
+// full-screen strip, of the per-corner normalised directions; it is normalised
+// again; the path starts with attenuation 0.8 and total 0 (:105-107).
+__global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam, Wavefront wf, int first_pass, int n_passes,
+                                                    uint32_t npix) {
+    const uint64_t total = uint64_t(npix) * uint64_t(n_passes);
+    for (uint64_t p = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; p < total; p += uint64_t(gridDim.x) * blockDim.x) {
+        const uint32_t k = uint32_t(p / npix);
+        const uint32_t pix = uint32_t(p - uint64_t(k) * npix);
+        const int x = int(pix % uint32_t(prm.width));
+        const int y = int(pix / uint32_t(prm.width));
+        const float u = (float(x) + 0.5f) / float(prm.width);
+        const float v = (float(y) + 0.5f) / float(prm.height);
+        f3 d0 = mk3(cam.dir[0][0], cam.dir[0][1], cam.dir[0][2]);
+        f3 d1 = mk3(cam.dir[1][0], cam.dir[1][1], cam.dir[1][2]);
+        f3 d2 = mk3(cam.dir[2][0], cam.dir[2][1], cam.dir[2][2]);
+        f3 d3 = mk3(cam.dir[3][0], cam.dir[3][1], cam.dir[3][2]);
+        f3 dir;
+        if (u + v <= 1.0f)
+            dir = d0 * ((1.0f - u) - v) + d1 * u + d2 * v;
+        else
+            dir = d1 * (1.0f - v) + d2 * (1.0f - u) + d3 * ((u + v) - 1.0f);
+        dir = normalize3(dir);
+        const int numero_pass = first_pass + int(k);
+        uint3 seed = rng_seed(u, v, numero_pass, prm.date);
+        wf.ray_o[p] = make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f);
+        wf.ray_d[p] = make_float4(dir.x, dir.y, dir.z, 0.0f);
+        wf.attenu[p] = make_float4(0.8f, 0.8f, 0.8f, 0.0f);
+        wf.total[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        wf.seed[p] = make_uint4(seed.x, seed.y, seed.z, 0u);
+        wf.result[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+    }
+}
+
+void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,
+                   int n_passes, uint32_t npix) {
+    uint64_t total = uint64_t(npix) * uint64_t(n_passes);
+    k_raygen<<<grid_for(lc, total, 16), kBlock, 0, lc.stream>>>(prm, cam, wf, first_pass, n_passes, npix);
+    ++g_launches;
+}
+
+// ----------------------------------------------------------------- traverse
+__global__ void __launch_bounds__(kBlock) k_traverse(DevScene S, Wavefront wf, const uint32_t* __restrict__ queue,
+                                                      const uint32_t* __restrict__ n_dev, uint32_t n_host,
+                                                      unsigned long long* ray_counter) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const uint32_t n = n_dev ? *n_dev : n_host;
+    if (uint64_t(blockIdx.x) * blockDim.x >= n) return;
+    if (blockIdx.x == 0 && threadIdx.x == 0 && ray_counter) atomicAdd(ray_counter, (unsigned long long)n);
+    SmemScene sm = stage_scene(S, smem_raw);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t p = queue ? queue[i] : i;
+        float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
+        Best best;
+        scene_walk(S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
+        wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
+        wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
+    }
+}
+
+void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const uint32_t* queue, const uint32_t* n_dev,
+                     uint32_t n_host, unsigned long long* ray_counter) {
+    uint64_t n = n_dev ? 0xffffffffull : n_host;
+    k_traverse<<<grid_for(lc, n, 8), kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter);
+    ++g_launches;
+}
+
+// traverse_all_bvh as a callable on caller-provided rays (mcpt_trace_rays)
+__global__ void __launch_bounds__(kBlock) k_trace(DevScene S, int64_t n, const float4* __restrict__ o,
+                                                   const float4* __restrict__ d, mcpt_hit* __restrict__ out, int any_hit) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    if (int64_t(blockIdx.x) * blockDim.x >= n) return;
+    SmemScene sm = stage_scene(S, smem_raw);
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        float4 o4 = o[i], d4 = d[i];
+        Best best;
+        f3 O = mk3(o4.x, o4.y, o4.z);
+        scene_walk(S, sm, O, mk3(d4.x, d4.y, d4.z), any_hit != 0, best);
+        mcpt_hit h;
+        h.index = best.h.prim;
+        h.dist = best.h.dist;
+        h.pl[0] = best.h.pl.x;
+        h.pl[1] = best.h.pl.y;
+        h.pl[2] = best.h.pl.z;
+        if (best.h.prim >= 0) {
+            const DevPrim* pp = S.prims + best.h.prim;
+            Aff fwd;
+            fwd.r0 = pp->fwd.r0;
+            fwd.r1 = pp->fwd.r1;
+            fwd.r2 = pp->fwd.r2;
+            f3 pg = xform_point(fwd, best.h.pl);
+            h.pg[0] = pg.x;
+            h.pg[1] = pg.y;
+            h.pg[2] = pg.z;
+            h.shape = pp->type;
+            h.tri_index = (pp->type == MCPT_PRIM_MESH) ? best.h.sub : -1;
+            h.dir = (pp->type == MCPT_PRIM_MESH) ? 0 : best.h.sub;
+        } else {
+            h.pg[0] = h.pg[1] = h.pg[2] = 0.0f;
+            h.shape = -1;
+            h.tri_index = -1;
+            h.dir = -1;
+        }
+        out[i] = h;
+    }
+}
+
+void launch_trace(const LaunchCfg& lc, const DevScene& S, int64_t n, const float4* o, const float4* d, void* hits_out,
+                  bool any_hit) {
+    k_trace<<<grid_for(lc, uint64_t(n), 8), kBlock, S.smem_bytes, lc.stream>>>(S, n, o, d, static_cast<mcpt_hit*>(hits_out),
+                                                                               any_hit ? 1 : 0);
+    ++g_launches;
+}
+
+// (shade / compact / accumulate / resolve follow in kernels_shade.inl)
+#include "kernels_shade.inl"
+
+}  // namespace mcpt

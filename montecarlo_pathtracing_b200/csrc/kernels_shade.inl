@@ -1,0 +1,240 @@
+// kernels_shade.inl — included by kernels.cu inside namespace mcpt.
+// shade / compact / shade_exit / accumulate / resolve stages.
+
+// -------------------------------------------------------------------- shade
+// One iteration of random_path's loop after traverse_all_bvh
+// (tp/montecarlo.frag:117-175), or one of the two debug shaders
+// (tp/montecarlo_mat.frag:5-20, tp/montecarlo_mat_tr.frag:5-20) when mode != 0.
+// Writes flag[i] for queue position i: 0 ended, 1 continue, 2 continue after an
+// interior traversal.
+template <bool FAST>
+__global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wavefront wf, const uint32_t* __restrict__ queue,
+                                                   const uint32_t* __restrict__ n_dev, uint32_t n_host, int last_bounce,
+                                                   unsigned long long* seg_counter) {
+    const uint32_t n = n_dev ? *n_dev : n_host;
+    unsigned int my_segments = 0;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t p = queue ? queue[i] : i;
+        const float4 ha = wf.hit_a[p];
+        const int2 hb = wf.hit_b[p];
+        const float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
+        const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
+        float4 t4 = wf.total[p];
+        f3 total = mk3(t4.x, t4.y, t4.z);
+        uint8_t flag = 0;
+        if (prm.mode != 0) {
+            // debug shaders: a single traversal, no bounce
+            f3 res = mk3(0.0f, 0.0f, 0.2f);
+            if (hb.x >= 0) {
+                uint4 s4 = wf.seed[p];
+                uint3 seed = make_uint3(s4.x, s4.y, s4.z);
+                f3 N = mk3(0, 0, 0), P = mk3(0, 0, 0);
+                intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
+                if (prm.mode == 1) {
+                    float r0 = random_float(seed), r1 = random_float(seed), r2 = random_float(seed);
+                    res = mk3(fabsf(N.x) * r0, fabsf(N.y) * r1, fabsf(N.z) * r2);
+                } else {
+                    float4 col = __ldg(S.color + hb.x);
+                    float r = random_float(seed);
+                    res = mk3(col.x * r, col.y * r, col.z * r);
+                }
+            }
+            wf.result[p] = make_float4(res.x, res.y, res.z, 0.0f);
+        } else if (hb.x < 0) {
+            float4 a4 = wf.attenu[p];
+            f3 res = sky(total, mk3(a4.x, a4.y, a4.z), D);
+            wf.result[p] = make_float4(res.x, res.y, res.z, 0.0f);
+        } else {
+            ++my_segments;
+            float4 a4 = wf.attenu[p];
+            uint4 s4 = wf.seed[p];
+            uint3 seed = make_uint3(s4.x, s4.y, s4.z);
+            f3 N = mk3(0, 0, 0), P = mk3(0, 0, 0);
+            intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
+            const float4 mat = __ldg(S.mat + hb.x);
+            const float4 col = __ldg(S.color + hb.x);
+            BounceOut bo = bounce<FAST>(O, D, N, P, mat, col, mk3(a4.x, a4.y, a4.z), total, seed, prm.refract_ind);
+            if (bo.kind == 0) {
+                wf.result[p] = make_float4(total.x, total.y, total.z, 0.0f);
+            } else if (!last_bounce) {
+                // a path still alive after the last iteration returns vec3(0)
+                // (tp/montecarlo.frag:178): result stays at its initial zero.
+                wf.ray_o[p] = make_float4(bo.nO.x, bo.nO.y, bo.nO.z, 0.0f);
+                wf.ray_d[p] = make_float4(bo.nD.x, bo.nD.y, bo.nD.z, 0.0f);
+                wf.attenu[p] = make_float4(bo.new_att.x, bo.new_att.y, bo.new_att.z, 0.0f);
+                wf.total[p] = make_float4(total.x, total.y, total.z, 0.0f);
+                wf.seed[p] = make_uint4(seed.x, seed.y, seed.z, 0u);
+                if (bo.kind == 2) {
+                    wf.keep_n[p] = make_float4(N.x, N.y, N.z, 0.0f);
+                    wf.keep_p[p] = make_float4(P.x, P.y, P.z, 0.0f);
+                }
+                flag = uint8_t(bo.kind);
+            }
+        }
+        wf.flag[i] = flag;
+    }
+    if (seg_counter) {
+        // one atomic per warp
+        for (int off = 16; off > 0; off >>= 1) my_segments += __shfl_down_sync(0xffffffffu, my_segments, off);
+        if ((threadIdx.x & 31) == 0 && my_segments) atomicAdd(seg_counter, (unsigned long long)my_segments);
+    }
+}
+
+void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueSet& q,
+                  bool last_bounce, bool fast_math) {
+    uint64_t n = q.n_cur ? 0xffffffffull : q.n_cur_host;
+    int grid = grid_for(lc, n, 8);
+    if (fast_math)
+        k_shade<true><<<grid, kBlock, 0, lc.stream>>>(S, prm, wf, q.cur, q.n_cur, q.n_cur_host, last_bounce ? 1 : 0,
+                                                      q.seg_counter);
+    else
+        k_shade<false><<<grid, kBlock, 0, lc.stream>>>(S, prm, wf, q.cur, q.n_cur, q.n_cur_host, last_bounce ? 1 : 0,
+                                                       q.seg_counter);
+    ++g_launches;
+}
+
+// ------------------------------------------------------------------ compact
+// Warp-ballot stream compaction of the current queue into (a) the queue of
+// paths entering the next bounce and (b) the queue of interior rays. Each warp
+// ballots its flags, warps of a block combine their counts in shared memory, one
+// thread reserves the block's output range with a single atomic per queue, and
+// every surviving lane writes at base + (survivors before it). Order is kept
+// inside a block's tile, which keeps neighbouring pixels neighbours.
+__global__ void __launch_bounds__(kBlock) k_compact(Wavefront wf, const uint32_t* __restrict__ queue,
+                                                     const uint32_t* __restrict__ n_dev, uint32_t n_host,
+                                                     uint32_t* __restrict__ next, uint32_t* __restrict__ n_next,
+                                                     uint32_t* __restrict__ interior, uint32_t* __restrict__ n_interior) {
+    __shared__ uint32_t warp_alive[kBlock / 32], warp_int[kBlock / 32];
+    __shared__ uint32_t base_alive, base_int;
+    const uint32_t n = n_dev ? *n_dev : n_host;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t n_tiles = (n + kBlock - 1) / kBlock;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const uint32_t i = tile * kBlock + threadIdx.x;
+        uint8_t f = 0;
+        uint32_t p = 0;
+        if (i < n) {
+            f = wf.flag[i];
+            p = queue ? queue[i] : i;
+        }
+        const uint32_t m_alive = __ballot_sync(0xffffffffu, f != 0);
+        const uint32_t m_int = __ballot_sync(0xffffffffu, f == 2);
+        if (lane == 0) {
+            warp_alive[warp] = __popc(m_alive);
+            warp_int[warp] = __popc(m_int);
+        }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint32_t sa = 0, si = 0;
+            for (int w = 0; w < kBlock / 32; ++w) {
+                uint32_t a = warp_alive[w], b = warp_int[w];
+                warp_alive[w] = sa;
+                warp_int[w] = si;
+                sa += a;
+                si += b;
+            }
+            base_alive = sa ? atomicAdd(n_next, sa) : 0u;
+            base_int = si ? atomicAdd(n_interior, si) : 0u;
+        }
+        __syncthreads();
+        const uint32_t below = (1u << lane) - 1u;
+        if (f != 0) next[base_alive + warp_alive[warp] + __popc(m_alive & below)] = p;
+        if (f == 2) interior[base_int + warp_int[warp] + __popc(m_int & below)] = p;
+        __syncthreads();
+    }
+}
+
+void launch_compact(const LaunchCfg& lc, Wavefront wf, const QueueSet& q) {
+    uint64_t n = q.n_cur ? 0xffffffffull : q.n_cur_host;
+    k_compact<<<grid_for(lc, n, 8), kBlock, 0, lc.stream>>>(wf, q.cur, q.n_cur, q.n_cur_host, q.next, q.n_next, q.interior,
+                                                            q.n_interior);
+    ++g_launches;
+}
+
+// --------------------------------------------------------------- shade_exit
+// Second half of the transparent cases (tp/montecarlo.frag:150-152,163-165): the
+// interior ray has been traced; take N,P of that hit (or keep the entry hit's
+// N,P when nothing was hit: intersection_info writes nothing for shape -1) and
+// leave through refract(D, -N, 1/refract_ind).
+__global__ void __launch_bounds__(kBlock) k_shade_exit(DevScene S, DevParams prm, Wavefront wf,
+                                                        const uint32_t* __restrict__ queue,
+                                                        const uint32_t* __restrict__ n_dev) {
+    const uint32_t n = *n_dev;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t p = queue[i];
+        const float4 ha = wf.hit_a[p];
+        const int2 hb = wf.hit_b[p];
+        const float4 d4 = wf.ray_d[p];
+        const float4 n4 = wf.keep_n[p], p4 = wf.keep_p[p];
+        f3 N = mk3(n4.x, n4.y, n4.z), P = mk3(p4.x, p4.y, p4.z);
+        intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
+        f3 nO = P + N * MCPT_BIAS;
+        f3 nD = refract3(mk3(d4.x, d4.y, d4.z), -N, 1.0f / prm.refract_ind);
+        wf.ray_o[p] = make_float4(nO.x, nO.y, nO.z, 0.0f);
+        wf.ray_d[p] = make_float4(nD.x, nD.y, nD.z, 0.0f);
+    }
+}
+
+void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const uint32_t* queue,
+                       const uint32_t* n_dev) {
+    k_shade_exit<<<grid_for(lc, 0xffffffffull, 8), kBlock, 0, lc.stream>>>(S, prm, wf, queue, n_dev);
+    ++g_launches;
+}
+
+// --------------------------------------------------------------- accumulate
+// glBlendFunc(GL_ONE, GL_ONE) into the RGB32F target, one draw per pass in pass
+// order (montecarlo.cpp:450-466): accum = ((accum + r0) + r1) + ...
+__global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __restrict__ accum, uint32_t npix,
+                                                        int n_passes) {
+    for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
+        float4 a = accum[pix];
+        for (int k = 0; k < n_passes; ++k) {
+            float4 r = wf.result[uint64_t(k) * npix + pix];
+            a.x += r.x;
+            a.y += r.y;
+            a.z += r.z;
+        }
+        accum[pix] = a;
+    }
+}
+
+void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes) {
+    k_accumulate<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(wf, accum, npix, n_passes);
+    ++g_launches;
+}
+
+// ------------------------------------------------------------------ resolve
+// fs_frag (montecarlo.cpp:59-70): frag = texture(TU, tc).rgb / nb with NEAREST
+// filtering, and shaders/average.frag:7-10: texelFetch(gl_FragCoord.xy /
+// subsampling) * k. Destination is (w*sub) x (h*sub); RGBA8 clamps like the
+// 8-bit back buffer (round to nearest, no gamma).
+__global__ void __launch_bounds__(kBlock) k_resolve(const float4* __restrict__ accum, int w, int h, float divisor, int sub,
+                                                     float* __restrict__ dst_f, uchar4* __restrict__ dst_u8) {
+    const int W = w * sub, H = h * sub;
+    const uint32_t total = uint32_t(W) * uint32_t(H);
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+        const int X = int(i % uint32_t(W)), Y = int(i / uint32_t(W));
+        const float4 a = accum[uint32_t(Y / sub) * uint32_t(w) + uint32_t(X / sub)];
+        const float r = a.x / divisor, g = a.y / divisor, b = a.z / divisor;
+        if (dst_f) {
+            dst_f[3 * size_t(i) + 0] = r;
+            dst_f[3 * size_t(i) + 1] = g;
+            dst_f[3 * size_t(i) + 2] = b;
+        } else {
+            auto q = [](float v) -> unsigned char {
+                v = fminf(fmaxf(v, 0.0f), 1.0f);  // NaN -> 0
+                return (unsigned char)(__float2int_rn(v * 255.0f));
+            };
+            dst_u8[i] = make_uchar4(q(r), q(g), q(b), 255);
+        }
+    }
+}
+
+void launch_resolve(const LaunchCfg& lc, const float4* accum, int w, int h, float divisor, int subsampling, void* dst,
+                    bool rgba8) {
+    uint64_t total = uint64_t(w) * subsampling * uint64_t(h) * subsampling;
+    k_resolve<<<grid_for(lc, total, 16), kBlock, 0, lc.stream>>>(accum, w, h, divisor, subsampling,
+                                                                 rgba8 ? nullptr : static_cast<float*>(dst),
+                                                                 rgba8 ? static_cast<uchar4*>(dst) : nullptr);
+    ++g_launches;
+}
