@@ -62,7 +62,7 @@ typedef struct mcpt_hit {
     int32_t tri_index; /* triangle index inside the mesh, -1 if not a mesh   */
     int32_t shape;     /* type code of the hit primitive, -1 on miss         */
     int32_t dir;       /* face id (cube 0..5, cylinder/cone 0/1/2), else 0   */
-    float dist;        /* world-space distance |O - pg| (FLT_MAX on miss)    */
+    float dist;        /* world-space distance |O - pg| (3.402823e38f on miss, the shader's FLT_MAX)    */
     float pl[3];       /* hit point in primitive-local space                 */
     float pg[3];       /* hit point in world space                           */
 } mcpt_hit;

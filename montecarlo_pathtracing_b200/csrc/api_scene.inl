@@ -74,13 +74,17 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     const int td = d->root.depth;
     const uint32_t t_first_leaf = 1u << td, t_nodes = 2u << td;  // indices 1 .. t_nodes-1
     std::vector<DevNode> top(t_nodes, empty_node());
+    std::vector<float> leaf_bb(6 * size_t(std::max(d->n_prims, 1)), 0.0f);
     for (uint32_t k = 1; k < t_nodes; ++k) {
         int aux = -1;
         bool empty = false;
         if (k >= t_first_leaf) {
             aux = d->root.ind[k - t_first_leaf];
             empty = aux < 0;
-            if (!empty && prims[aux].slot < 0) prims[aux].slot = int(k - t_first_leaf);
+            if (!empty && prims[aux].slot < 0) {
+                prims[aux].slot = int(k - t_first_leaf);
+                std::memcpy(&leaf_bb[6 * size_t(aux)], &d->root.bb[k - 1], 6 * sizeof(float));
+            }
         }
         if (!empty) top[k] = pack_node(d->root.bb[k - 1], aux);
     }
@@ -157,14 +161,16 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     DevPrim* d_prims = nullptr;
     float4 *d_color = nullptr, *d_mat = nullptr;
     DevMesh* d_meshes = nullptr;
+    float* d_leaf_bb = nullptr;
     if ((rc = upload_vec(c, top, &d_top)) || (rc = upload_vec(c, prims, &d_prims)) || (rc = upload_vec(c, color, &d_color)) ||
-        (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)))
+        (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)) || (rc = upload_vec(c, leaf_bb, &d_leaf_bb)))
         return rc;
     S.top_nodes = d_top;
     S.prims = d_prims;
     S.color = d_color;
     S.mat = d_mat;
     S.meshes = d_meshes;
+    S.leaf_bb = d_leaf_bb;
     S.top_depth = td;
     S.n_prims = d->n_prims;
     S.n_meshes = d->n_meshes;

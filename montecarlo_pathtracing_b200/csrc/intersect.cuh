@@ -17,6 +17,8 @@
 
 namespace mcpt {
 
+// the shader's own constants (raytracer_func.frag:8,13-14); its FLT_MAX is 3.402823e38, not the IEEE one
+#define MCPT_FLT_MAX 3.402823e38f
 #define MCPT_EPSILON 1e-10f
 #define MCPT_BIAS 1e-2f
 
@@ -31,7 +33,7 @@ struct Best {
 };
 
 MCPT_DEV void best_reset(Best& b) {
-    b.h.dist = FLT_MAX;
+    b.h.dist = MCPT_FLT_MAX;
     b.h.pl = mk3(0.0f, 0.0f, 0.0f);
     b.h.prim = -1;
     b.h.sub = -1;
@@ -63,6 +65,22 @@ MCPT_DEV bool offer_at(Best& b, const Aff& fwd, f3 O, f3 D, float a, f3 Ow, int 
     return offer(b, dist, Pl, prim, sub, tslot, rank);
 }
 
+// The reference only reaches a primitive whose leaf box passes intersect_bv
+// (raytracer_func.frag:314-352): origin strictly inside the box, or the box entered
+// from the front. For every intersector that demands a > EPSILON a valid hit implies
+// that, so the conservative slab test upstream is enough. The quad and the cone
+// quadric accept hits BEHIND the origin (no a > 0 test); those are reachable in the
+// reference only when the origin is inside the leaf box, which is evaluated here
+// with the shader's own arithmetic on the un-inflated box.
+MCPT_DEV bool origin_inside_leaf_box(const float* __restrict__ bb, f3 O) {
+    f3 mn = mk3(__ldg(bb + 0), __ldg(bb + 1), __ldg(bb + 2));
+    f3 mx = mk3(__ldg(bb + 3), __ldg(bb + 4), __ldg(bb + 5));
+    f3 center = (mn + mx) / 2.0f;
+    f3 width = (mx - mn) * 0.5f;
+    f3 Oi = mk3((O.x - center.x) / width.x, (O.y - center.y) / width.y, (O.z - center.z) / width.z);
+    return fabsf(Oi.x) < 1.0f && fabsf(Oi.y) < 1.0f && fabsf(Oi.z) < 1.0f;
+}
+
 // raytracer_func.frag:398-441
 MCPT_DEV void sphere_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot) {
     float OO = dot3(O, O);
@@ -80,9 +98,10 @@ MCPT_DEV void sphere_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, 
 
 // raytracer_func.frag:443-470. One-sided (D.z < -EPSILON); note there is no
 // a > 0 test in the shader, so there is none here.
-MCPT_DEV void quad_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot) {
+MCPT_DEV void quad_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot, const float* leaf_bb) {
     if (D.z > -MCPT_EPSILON) return;
     float a = -O.z / D.z;
+    if (!(a > 0.0f) && !origin_inside_leaf_box(leaf_bb, Ow)) return;  // hit behind the origin
     f3 Pl = O + D * a;
     if (fabsf(Pl.x) > 1.0f || fabsf(Pl.y) > 1.0f) return;
     f3 Pg = xform_point(fwd, Pl);
@@ -92,7 +111,7 @@ MCPT_DEV void quad_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, in
 
 // raytracer_func.frag:472-512: nearest of the six faces, face id -> dir
 MCPT_DEV void cube_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot) {
-    float al = FLT_MAX;
+    float al = MCPT_FLT_MAX;
     int cl = 0;
 #pragma unroll
     for (int c = 0; c < 6; ++c) {
@@ -110,13 +129,13 @@ MCPT_DEV void cube_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, in
             }
         }
     }
-    if (al < FLT_MAX) offer_at(b, fwd, O, D, al, Ow, prim, cl, tslot, 0);
+    if (al < MCPT_FLT_MAX) offer_at(b, fwd, O, D, al, Ow, prim, cl, tslot, 0);
 }
 
 // raytracer_func.frag:515-577: caps z = -1 (dir 0), z = +1 (dir 1), side (dir 2)
 MCPT_DEV void cylinder_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot) {
     int cl = -1;
-    float al = FLT_MAX;
+    float al = MCPT_FLT_MAX;
     if (fabsf(D.z) > MCPT_EPSILON) {
         float a = (-1.0f - O.z) / D.z;
         if (a > MCPT_EPSILON) {
@@ -149,15 +168,15 @@ MCPT_DEV void cylinder_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim
             }
         }
     }
-    if (al < FLT_MAX) offer_at(b, fwd, O, D, al, Ow, prim, cl, tslot, 0);
+    if (al < MCPT_FLT_MAX) offer_at(b, fwd, O, D, al, Ow, prim, cl, tslot, 0);
 }
 
 // raytracer_func.frag:579-640: cap z = -1 (dir 0) and the quadric with k = 0.8,
 // apex at z = +1 (dir 2); as in the shader the quadric roots are not tested for
 // positivity.
-MCPT_DEV void cone_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot) {
+MCPT_DEV void cone_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot, const float* leaf_bb) {
     int cl = -1;
-    float tl = FLT_MAX;
+    float tl = MCPT_FLT_MAX;
     if (fabsf(D.z) > MCPT_EPSILON) {
         float t0 = (-1.0f - O.z) / D.z;
         if (t0 > MCPT_EPSILON) {
@@ -177,16 +196,19 @@ MCPT_DEV void cone_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, in
     if (det > 0.0f) {
         det = sqrtf(det);
         float t1 = (-qb - det) / (2.0f * qa);
-        if (fabsf(O.z + t1 * D.z) > 1.0f) t1 = FLT_MAX;
+        if (fabsf(O.z + t1 * D.z) > 1.0f) t1 = MCPT_FLT_MAX;
         float t2 = (-qb + det) / (2.0f * qa);
-        if (fabsf(O.z + t2 * D.z) > 1.0f) t2 = FLT_MAX;
+        if (fabsf(O.z + t2 * D.z) > 1.0f) t2 = MCPT_FLT_MAX;
         float t = (t2 < t1) ? t2 : t1;  // GLSL min(t1,t2)
         if (t < tl) {
             cl = 2;
             tl = t;
         }
     }
-    if (tl < FLT_MAX) offer_at(b, fwd, O, D, tl, Ow, prim, cl, tslot, 0);
+    if (tl < MCPT_FLT_MAX) {
+        if (!(tl > 0.0f) && !origin_inside_leaf_box(leaf_bb, Ow)) return;  // hit behind the origin
+        offer_at(b, fwd, O, D, tl, Ow, prim, cl, tslot, 0);
+    }
 }
 
 // raytracer_func.frag:354-396 (Moeller-Trumbore, u,v in [0,1], a > EPSILON)

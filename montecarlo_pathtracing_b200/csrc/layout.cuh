@@ -67,6 +67,7 @@ struct DevScene {
     const float4* color;       // PrimData.color_
     const float4* mat;         // PrimData.mat_info
     const DevMesh* meshes;
+    const float* leaf_bb;      // 6 floats per primitive: its un-inflated top-level leaf box
     int32_t top_depth;
     int32_t n_prims;
     int32_t n_meshes;

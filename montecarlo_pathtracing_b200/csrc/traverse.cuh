@@ -47,10 +47,13 @@ MCPT_DEV bool slab(const DevNode& n, f3 idir, f3 od, float tmax) {
     return tn <= tf;
 }
 
-MCPT_DEV f3 safe_rcp3(f3 d) {
-    // 1/0 = inf is fine for slabs; keep the sign of zero out of it
-    return mk3(1.0f / d.x, 1.0f / d.y, 1.0f / d.z);
+MCPT_DEV float safe_rcp(float d) {
+    // A zero component would give 1/0 = inf and inf - inf = NaN inside the FMA slab
+    // test; 1e-30 keeps the products finite and the ray "parallel" for any box.
+    if (fabsf(d) < 1e-30f) d = copysignf(1e-30f, d);
+    return 1.0f / d;
 }
+MCPT_DEV f3 safe_rcp3(f3 d) { return mk3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(d.z)); }
 
 // Walk one mesh (second level). Oi/Di: ray in mesh-local space (Di normalised by
 // intersect_prim, raytracer_func.frag:688); Ow: world origin; fwd: mesh -> world.
@@ -135,8 +138,8 @@ MCPT_DEV void prim_test(const DevScene& S, const SmemScene& sm, int p, f3 O, f3 
         case MCPT_PRIM_SPHERE: sphere_test(best, fwd, Oi, Di, O, p, tslot); break;
         case MCPT_PRIM_CUBE: cube_test(best, fwd, Oi, Di, O, p, tslot); break;
         case MCPT_PRIM_CYLINDER: cylinder_test(best, fwd, Oi, Di, O, p, tslot); break;
-        case MCPT_PRIM_CONE: cone_test(best, fwd, Oi, Di, O, p, tslot); break;
-        case MCPT_PRIM_ORIENTED_QUAD: quad_test(best, fwd, Oi, Di, O, p, tslot); break;
+        case MCPT_PRIM_CONE: cone_test(best, fwd, Oi, Di, O, p, tslot, S.leaf_bb + 6 * p); break;
+        case MCPT_PRIM_ORIENTED_QUAD: quad_test(best, fwd, Oi, Di, O, p, tslot, S.leaf_bb + 6 * p); break;
         default: break;
     }
 }
