@@ -80,8 +80,32 @@ enum {
     MCPT_OPT_PASSES_PER_BATCH = 0, /* passes traced together in one wavefront (default auto) */
     MCPT_OPT_SMEM_STAGING = 1,     /* 1 = stage top BVH levels in shared memory (default 1)  */
     MCPT_OPT_FAST_MATH = 2,        /* 1 = MUFU sin/cos/log/pow in the bounce sampler         */
-    MCPT_OPT_SORT_QUEUES = 3       /* reserved                                               */
+    MCPT_OPT_SORT_QUEUES = 3,      /* reserved                                               */
+    MCPT_OPT_PROFILE_STAGES = 4,   /* 1 = bracket every stage launch with CUDA events         */
+    MCPT_OPT_COUNT_WORK = 5,       /* 1 = traversal kernels count boxes / records / triangles */
+    MCPT_OPT_FLAT_WALK = 6         /* 1 = warp-coherent flat walk for scenes of <= 16 primitives (default 1);
+                                      set before mcpt_upload_scene */
 };
+
+/* wavefront stages, in launch order inside one bounce */
+enum {
+    MCPT_STAGE_RAYGEN = 0,
+    MCPT_STAGE_TRAVERSE = 1,
+    MCPT_STAGE_SHADE = 2,
+    MCPT_STAGE_COMPACT = 3,
+    MCPT_STAGE_TRAVERSE_INTERIOR = 4,
+    MCPT_STAGE_SHADE_EXIT = 5,
+    MCPT_STAGE_ACCUMULATE = 6,
+    MCPT_STAGE_RESOLVE = 7,
+    MCPT_STAGE_COUNT = 8
+};
+
+/* per-stage device time (CUDA events on the context's stream) and launch counts
+ * gathered while MCPT_OPT_PROFILE_STAGES is on; reading them drains the record */
+typedef struct mcpt_stage_times {
+    double ms[MCPT_STAGE_COUNT];
+    uint64_t launches[MCPT_STAGE_COUNT];
+} mcpt_stage_times;
 
 /* counters filled by the wavefront since the last mcpt_clear / mcpt_reset_stats */
 typedef struct mcpt_stats {
@@ -89,6 +113,9 @@ typedef struct mcpt_stats {
     uint64_t rays;       /* traverse_all_bvh calls (primary + bounce + interior) */
     uint64_t segments;   /* shaded hits                                         */
     uint64_t launches;   /* kernels launched by this library                    */
+    uint64_t boxes;      /* boxes tested      (only with MCPT_OPT_COUNT_WORK)   */
+    uint64_t prim_tests; /* records tested    (only with MCPT_OPT_COUNT_WORK)   */
+    uint64_t tri_tests;  /* triangles tested  (only with MCPT_OPT_COUNT_WORK)   */
 } mcpt_stats;
 
 int mcpt_abi_version(void);
@@ -158,6 +185,8 @@ int mcpt_trace_rays_device(mcpt_ctx* ctx, int64_t n, const float* o4, const floa
 
 int mcpt_get_stats(mcpt_ctx* ctx, mcpt_stats* out);
 int mcpt_reset_stats(mcpt_ctx* ctx);
+/* synchronises the stream */
+int mcpt_get_stage_times(mcpt_ctx* ctx, mcpt_stage_times* out);
 
 #ifdef __cplusplus
 }

@@ -19,7 +19,8 @@ MCPT_OK = 0
 MCPT_E_INVALID, MCPT_E_CUDA, MCPT_E_NODEVICE, MCPT_E_NOMEM, MCPT_E_NCCL, MCPT_E_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 PRIM_MESH, PRIM_SPHERE, PRIM_CUBE, PRIM_CYLINDER, PRIM_CONE, PRIM_ORIENTED_QUAD = range(6)
 DST_HOST_RGB32F, DST_HOST_RGBA8, DST_DEVICE_RGB32F, DST_DEVICE_RGBA8 = range(4)
-OPT_PASSES_PER_BATCH, OPT_SMEM_STAGING, OPT_FAST_MATH, OPT_SORT_QUEUES = range(4)
+OPT_PASSES_PER_BATCH, OPT_SMEM_STAGING, OPT_FAST_MATH, OPT_SORT_QUEUES, OPT_PROFILE_STAGES, OPT_COUNT_WORK, OPT_FLAT_WALK = range(7)
+STAGE_NAMES = ("raygen", "traverse", "shade", "compact", "traverse_interior", "shade_exit", "accumulate", "resolve")
 
 
 class PrimData(C.Structure):  # include/mcpt_scene.h mcpt_prim_data
@@ -47,7 +48,12 @@ class Params(C.Structure):  # mcpt_params
 
 
 class Stats(C.Structure):
-    _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("segments", C.c_uint64), ("launches", C.c_uint64)]
+    _fields_ = [("paths", C.c_uint64), ("rays", C.c_uint64), ("segments", C.c_uint64), ("launches", C.c_uint64),
+                ("boxes", C.c_uint64), ("prim_tests", C.c_uint64), ("tri_tests", C.c_uint64)]
+
+
+class StageTimes(C.Structure):
+    _fields_ = [("ms", C.c_double * 8), ("launches", C.c_uint64 * 8)]
 
 
 HIT_DTYPE = np.dtype([("index", "<i4"), ("tri_index", "<i4"), ("shape", "<i4"), ("dir", "<i4"), ("dist", "<f4"),
@@ -60,7 +66,7 @@ MCPT_SYMBOLS = [
     "mcpt_synchronize", "mcpt_set_option", "mcpt_upload_scene", "mcpt_resize", "mcpt_set_camera", "mcpt_set_params",
     "mcpt_clear", "mcpt_render", "mcpt_resolve", "mcpt_get_accum", "mcpt_bind_accum", "mcpt_read_accum",
     "mcpt_write_accum", "mcpt_reduce_nccl", "mcpt_trace_rays", "mcpt_trace_rays_device", "mcpt_get_stats",
-    "mcpt_reset_stats",
+    "mcpt_reset_stats", "mcpt_get_stage_times",
 ]
 # every symbol include/mcpt_host.h declares
 MCPTH_SYMBOLS = [
@@ -113,6 +119,7 @@ def lib():
         L.mcpt_trace_rays_device.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mcpt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.mcpt_reset_stats.argtypes = [C.c_void_p]
+        L.mcpt_get_stage_times.argtypes = [C.c_void_p, C.POINTER(StageTimes)]
         _lib = L
     return _lib
 

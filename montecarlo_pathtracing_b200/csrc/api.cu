@@ -53,18 +53,31 @@ struct mcpt_ctx {
     uint32_t* queue[3] = {nullptr, nullptr, nullptr};
     uint32_t* counters = nullptr;  // 2 * max_bounces entries
     int counters_len = 0;
-    unsigned long long* dev_stats = nullptr;  // [0] rays, [1] segments
+    unsigned long long* dev_stats = nullptr;  // [0] rays, [1] segments, [2] boxes, [3] records, [4] triangles
 
     // options
     int opt_passes_per_batch = 0;  // 0 = auto
     int opt_smem_staging = 1;
     int opt_fast_math = 0;
+    int opt_profile = 0;
+    int opt_flat_walk = 1;
+    int opt_count_work = 0;
+
+    // stage profiling: (stage, start, stop) triples waiting to be read, plus a free list
+    struct Span {
+        int stage;
+        cudaEvent_t a, b;
+    };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> free_events;
 
     uint64_t paths_started = 0;
     unsigned long long launches_base = 0;
 };
 
 namespace {
+
+constexpr int kStatWords = 5;
 
 int fail(mcpt_ctx* c, int code, const char* fmt, ...) {
     if (c) {
@@ -185,13 +198,13 @@ int mcpt_create(int device, mcpt_ctx** out) {
     }
     c->stream = c->own_stream;
     void* p = nullptr;
-    if (cudaMalloc(&p, 2 * sizeof(unsigned long long)) != cudaSuccess) {
+    if (cudaMalloc(&p, kStatWords * sizeof(unsigned long long)) != cudaSuccess) {
         cudaStreamDestroy(c->own_stream);
         delete c;
         return MCPT_E_NOMEM;
     }
     c->dev_stats = static_cast<unsigned long long*>(p);
-    cudaMemset(c->dev_stats, 0, 2 * sizeof(unsigned long long));
+    cudaMemset(c->dev_stats, 0, kStatWords * sizeof(unsigned long long));
     c->prm.nb_bounces = 3;       // RTViewer defaults, montecarlo.cpp:126-141
     c->prm.refract_ind = 1.0f;
     c->user_params.nb_bounces = 3;
@@ -209,6 +222,11 @@ int mcpt_destroy(mcpt_ctx* c) {
     free_all(c->wf_allocs);
     if (c->accum_owned && c->accum) cudaFree(c->accum);
     if (c->dev_stats) cudaFree(c->dev_stats);
+    for (auto& sp : c->spans) {
+        cudaEventDestroy(sp.a);
+        cudaEventDestroy(sp.b);
+    }
+    for (cudaEvent_t e : c->free_events) cudaEventDestroy(e);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
     return MCPT_OK;
@@ -240,6 +258,9 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
             return MCPT_OK;
         case MCPT_OPT_FAST_MATH: c->opt_fast_math = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_SORT_QUEUES: return MCPT_OK;
+        case MCPT_OPT_PROFILE_STAGES: c->opt_profile = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_COUNT_WORK: c->opt_count_work = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;
     }
     return fail(c, MCPT_E_INVALID, "unknown option %d", option);
 }

@@ -43,6 +43,32 @@ int passes_per_batch(const mcpt_ctx* c, uint32_t npix) {
     return int(std::min<uint64_t>(std::max<uint64_t>(ppb, 1), 64));
 }
 
+// RAII bracket of one stage launch with two events when profiling is on
+struct StageSpan {
+    mcpt_ctx* c;
+    int idx = -1;
+    StageSpan(mcpt_ctx* ctx, int stage) : c(ctx) {
+        if (!c->opt_profile) return;
+        auto get = [&]() {
+            cudaEvent_t e = nullptr;
+            if (!c->free_events.empty()) {
+                e = c->free_events.back();
+                c->free_events.pop_back();
+            } else {
+                cudaEventCreate(&e);
+            }
+            return e;
+        };
+        mcpt_ctx::Span sp{stage, get(), get()};
+        cudaEventRecord(sp.a, c->stream);
+        c->spans.push_back(sp);
+        idx = int(c->spans.size()) - 1;
+    }
+    ~StageSpan() {
+        if (idx >= 0) cudaEventRecord(c->spans[idx].b, c->stream);
+    }
+};
+
 // raytracer.vert:9-22 evaluated for the four strip vertices, in fp32
 void camera_rays(const float iv[16], const float ipv[16], CameraRays& out) {
     // P4 = invV * vec4(0,0,0,1)
@@ -131,18 +157,25 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
     if (rc) return rc;
     const LaunchCfg lc = lcfg(c);
     const DevScene& S = c->scene;
+    unsigned long long* work = c->opt_count_work ? c->dev_stats + 2 : nullptr;
 
     for (int b0 = 0; b0 < n_passes; b0 += ppb) {
         const int nb = std::min(ppb, n_passes - b0);
         const uint32_t slots = npix * uint32_t(nb);
         CK(c, cudaMemsetAsync(c->counters, 0, sizeof(uint32_t) * c->counters_len, c->stream));
-        launch_raygen(lc, c->prm, c->cam, c->wf, first_pass + b0, nb, npix);
+        {
+            StageSpan sp(c, MCPT_STAGE_RAYGEN);
+            launch_raygen(lc, c->prm, c->cam, c->wf, first_pass + b0, nb, npix);
+        }
         uint32_t* q_cur = nullptr;  // identity queue for the first bounce
         const uint32_t* n_cur = nullptr;
         int spare = 0;  // queue[spare] receives survivors
         for (int it = 0; it < iters; ++it) {
             const bool last = (it == iters - 1);
-            launch_traverse(lc, S, c->wf, q_cur, n_cur, slots, c->dev_stats + 0);
+            {
+                StageSpan sp(c, MCPT_STAGE_TRAVERSE);
+                launch_traverse(lc, S, c->wf, q_cur, n_cur, slots, c->dev_stats + 0, work);
+            }
             QueueSet q{};
             q.cur = q_cur;
             q.n_cur = n_cur;
@@ -152,16 +185,31 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
             q.n_next = c->counters + 2 * it;
             q.n_interior = c->counters + 2 * it + 1;
             q.seg_counter = c->dev_stats + 1;
-            launch_shade(lc, S, c->prm, c->wf, q, last, c->opt_fast_math != 0);
+            {
+                StageSpan sp(c, MCPT_STAGE_SHADE);
+                launch_shade(lc, S, c->prm, c->wf, q, last, c->opt_fast_math != 0);
+            }
             if (last) break;
-            launch_compact(lc, c->wf, q);
-            launch_traverse(lc, S, c->wf, q.interior, q.n_interior, 0, c->dev_stats + 0);
-            launch_shade_exit(lc, S, c->prm, c->wf, q.interior, q.n_interior);
+            {
+                StageSpan sp(c, MCPT_STAGE_COMPACT);
+                launch_compact(lc, c->wf, q);
+            }
+            {
+                StageSpan sp(c, MCPT_STAGE_TRAVERSE_INTERIOR);
+                launch_traverse(lc, S, c->wf, q.interior, q.n_interior, 0, c->dev_stats + 0, work);
+            }
+            {
+                StageSpan sp(c, MCPT_STAGE_SHADE_EXIT);
+                launch_shade_exit(lc, S, c->prm, c->wf, q.interior, q.n_interior);
+            }
             q_cur = q.next;
             n_cur = q.n_next;
             spare ^= 1;
         }
-        launch_accumulate(lc, c->wf, c->accum, npix, nb);
+        {
+            StageSpan sp(c, MCPT_STAGE_ACCUMULATE);
+            launch_accumulate(lc, c->wf, c->accum, npix, nb);
+        }
         c->paths_started += slots;
     }
     CK(c, cudaGetLastError());
@@ -298,20 +346,39 @@ int mcpt_trace_rays(mcpt_ctx* c, int64_t n, const float* o, const float* d, mcpt
 int mcpt_get_stats(mcpt_ctx* c, mcpt_stats* out) {
     if (!c || !out) return MCPT_E_INVALID;
     CK(c, cudaSetDevice(c->device));
-    unsigned long long h[2] = {0, 0};
+    unsigned long long h[kStatWords] = {0, 0, 0, 0, 0};
     CK(c, cudaMemcpyAsync(h, c->dev_stats, sizeof h, cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
     out->paths = c->paths_started;
     out->rays = h[0];
     out->segments = h[1];
     out->launches = launches_issued() - c->launches_base;
+    out->boxes = h[2];
+    out->prim_tests = h[3];
+    out->tri_tests = h[4];
+    return MCPT_OK;
+}
+
+int mcpt_get_stage_times(mcpt_ctx* c, mcpt_stage_times* out) {
+    if (!c || !out) return MCPT_E_INVALID;
+    CK(c, cudaSetDevice(c->device));
+    CK(c, cudaStreamSynchronize(c->stream));
+    std::memset(out, 0, sizeof *out);
+    for (auto& sp : c->spans) {
+        float ms = 0.0f;
+        if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) out->ms[sp.stage] += ms;
+        out->launches[sp.stage] += 1;
+        c->free_events.push_back(sp.a);
+        c->free_events.push_back(sp.b);
+    }
+    c->spans.clear();
     return MCPT_OK;
 }
 
 int mcpt_reset_stats(mcpt_ctx* c) {
     if (!c) return MCPT_E_INVALID;
     CK(c, cudaSetDevice(c->device));
-    CK(c, cudaMemsetAsync(c->dev_stats, 0, 2 * sizeof(unsigned long long), c->stream));
+    CK(c, cudaMemsetAsync(c->dev_stats, 0, kStatWords * sizeof(unsigned long long), c->stream));
     c->paths_started = 0;
     c->launches_base = launches_issued();
     return MCPT_OK;

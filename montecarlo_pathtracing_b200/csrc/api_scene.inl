@@ -89,6 +89,12 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         if (!empty) top[k] = pack_node(d->root.bb[k - 1], aux);
     }
 
+    // ---- small scenes: flat list of leaf boxes for the warp-coherent walk
+    std::vector<DevNode> flat;
+    if (c->opt_flat_walk && d->n_prims > 0 && d->n_prims <= 16 && d->n_meshes == 0)
+        for (uint32_t k = t_nodes - 1; k >= t_first_leaf; --k)  // the reference's visit order: high slots first
+            if (d->root.ind[k - t_first_leaf] >= 0) flat.push_back(top[k]);
+
     // ---- meshes
     std::vector<DevMesh> meshes(d->n_meshes);
     for (int m = 0; m < d->n_meshes; ++m) {
@@ -155,6 +161,7 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             S.smem_mesh_nodes = off;
         }
     }
+    if (!flat.empty()) S.smem_top_nodes = int(flat.size()) - 1;  // the flat list takes the tree's place (always staged)
     S.smem_bytes = int(sizeof(DevNode)) * (S.smem_top_nodes + 1 + S.smem_mesh_nodes) + int(sizeof(DevPrim)) * S.smem_prims;
 
     DevNode* d_top = nullptr;
@@ -162,8 +169,10 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     float4 *d_color = nullptr, *d_mat = nullptr;
     DevMesh* d_meshes = nullptr;
     float* d_leaf_bb = nullptr;
+    DevNode* d_flat = nullptr;
     if ((rc = upload_vec(c, top, &d_top)) || (rc = upload_vec(c, prims, &d_prims)) || (rc = upload_vec(c, color, &d_color)) ||
-        (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)) || (rc = upload_vec(c, leaf_bb, &d_leaf_bb)))
+        (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)) || (rc = upload_vec(c, leaf_bb, &d_leaf_bb)) ||
+        (rc = upload_vec(c, flat, &d_flat)))
         return rc;
     S.top_nodes = d_top;
     S.prims = d_prims;
@@ -171,6 +180,8 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.mat = d_mat;
     S.meshes = d_meshes;
     S.leaf_bb = d_leaf_bb;
+    S.flat = flat.empty() ? nullptr : d_flat;
+    S.n_flat = int(flat.size());
     S.top_depth = td;
     S.n_prims = d->n_prims;
     S.n_meshes = d->n_meshes;

@@ -36,7 +36,8 @@ __device__ __forceinline__ SmemScene stage_scene(const DevScene& S, unsigned cha
     DevNode* mesh = top + (S.smem_top_nodes + 1);
     DevPrim* prims = reinterpret_cast<DevPrim*>(mesh + S.smem_mesh_nodes);
     {
-        const float4* src = reinterpret_cast<const float4*>(S.top_nodes);
+        // the flat leaf list (small scenes) or the top levels of the tree
+        const float4* src = reinterpret_cast<const float4*>(S.n_flat > 0 ? S.flat : S.top_nodes);
         float4* dst = reinterpret_cast<float4*>(top);
         const int n4 = (S.smem_top_nodes + 1) * 2;
         for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);
@@ -107,28 +108,69 @@ void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& 
 }
 
 // ----------------------------------------------------------------- traverse
+// warp-reduce the optional work counters and add them to work[0..2]
+__device__ __forceinline__ void flush_work(const Work& wk, unsigned long long* work) {
+    uint32_t b = wk.boxes, p = wk.prims, t = wk.tris;
+    for (int off = 16; off > 0; off >>= 1) {
+        b += __shfl_down_sync(0xffffffffu, b, off);
+        p += __shfl_down_sync(0xffffffffu, p, off);
+        t += __shfl_down_sync(0xffffffffu, t, off);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (b) atomicAdd(work + 0, (unsigned long long)b);
+        if (p) atomicAdd(work + 1, (unsigned long long)p);
+        if (t) atomicAdd(work + 2, (unsigned long long)t);
+    }
+}
+
+template <bool COUNT>
 __global__ void __launch_bounds__(kBlock) k_traverse(DevScene S, Wavefront wf, const uint32_t* __restrict__ queue,
                                                       const uint32_t* __restrict__ n_dev, uint32_t n_host,
-                                                      unsigned long long* ray_counter) {
+                                                      unsigned long long* ray_counter, unsigned long long* work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t n = n_dev ? *n_dev : n_host;
     if (uint64_t(blockIdx.x) * blockDim.x >= n) return;
     if (blockIdx.x == 0 && threadIdx.x == 0 && ray_counter) atomicAdd(ray_counter, (unsigned long long)n);
     SmemScene sm = stage_scene(S, smem_raw);
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t p = queue ? queue[i] : i;
-        float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
-        Best best;
-        scene_walk(S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
-        wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
-        wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
+    Work wk;
+    if (S.n_flat > 0) {
+        // warp-uniform trip count: every lane of a warp stays in the loop together
+        for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
+            const uint32_t i = base + threadIdx.x;
+            const bool valid = i < n;
+            const uint32_t p = valid ? (queue ? queue[i] : i) : 0u;
+            float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
+            if (valid) {
+                o4 = wf.ray_o[p];
+                d4 = wf.ray_d[p];
+            }
+            Best best;
+            scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
+            if (valid) {
+                wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
+                wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
+            }
+        }
+    } else {
+        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+            const uint32_t p = queue ? queue[i] : i;
+            float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
+            Best best;
+            scene_walk<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
+            wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
+            wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
+        }
     }
+    if (COUNT) flush_work(wk, work);
 }
 
 void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const uint32_t* queue, const uint32_t* n_dev,
-                     uint32_t n_host, unsigned long long* ray_counter) {
+                     uint32_t n_host, unsigned long long* ray_counter, unsigned long long* work) {
     uint64_t n = n_dev ? 0xffffffffull : n_host;
-    k_traverse<<<grid_for(lc, n, 8), kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter);
+    if (work)
+        k_traverse<true><<<grid_for(lc, n, 8), kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, work);
+    else
+        k_traverse<false><<<grid_for(lc, n, 8), kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, nullptr);
     ++g_launches;
 }
 
@@ -138,11 +180,23 @@ __global__ void __launch_bounds__(kBlock) k_trace(DevScene S, int64_t n, const f
     extern __shared__ __align__(16) unsigned char smem_raw[];
     if (int64_t(blockIdx.x) * blockDim.x >= n) return;
     SmemScene sm = stage_scene(S, smem_raw);
-    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
-        float4 o4 = o[i], d4 = d[i];
+    for (int64_t base = int64_t(blockIdx.x) * blockDim.x; base < n; base += int64_t(gridDim.x) * blockDim.x) {
+        const int64_t i = base + threadIdx.x;
+        const bool valid = i < n;
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
+        if (valid) {
+            o4 = o[i];
+            d4 = d[i];
+        }
         Best best;
+        Work wk;
         f3 O = mk3(o4.x, o4.y, o4.z);
-        scene_walk(S, sm, O, mk3(d4.x, d4.y, d4.z), any_hit != 0, best);
+        if (S.n_flat > 0) {
+            scene_walk_flat<false>(wk, S, sm, O, mk3(d4.x, d4.y, d4.z), any_hit != 0, valid, best);
+        } else if (valid) {
+            scene_walk<false>(wk, S, sm, O, mk3(d4.x, d4.y, d4.z), any_hit != 0, best);
+        }
+        if (!valid) continue;
         mcpt_hit h;
         h.index = best.h.prim;
         h.dist = best.h.dist;

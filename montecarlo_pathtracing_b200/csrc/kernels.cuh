@@ -35,7 +35,7 @@ struct LaunchCfg {
 void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,
                    int n_passes, uint32_t npix);
 void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const uint32_t* queue, const uint32_t* n_dev,
-                     uint32_t n_host, unsigned long long* ray_counter);
+                     uint32_t n_host, unsigned long long* ray_counter, unsigned long long* work);
 void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueSet& q,
                   bool last_bounce, bool fast_math);
 void launch_compact(const LaunchCfg& lc, Wavefront wf, const QueueSet& q);

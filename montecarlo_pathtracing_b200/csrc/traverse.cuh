@@ -23,6 +23,12 @@
 
 namespace mcpt {
 
+// optional per-thread work counters (MCPT_OPT_COUNT_WORK): boxes tested, primitive
+// records tested, triangles tested
+struct Work {
+    uint32_t boxes = 0, prims = 0, tris = 0;
+};
+
 struct SmemScene {
     const DevNode* top_nodes;   // staged top-level nodes, index 1-based like global
     const DevPrim* prims;       // staged primitive records
@@ -57,7 +63,8 @@ MCPT_DEV f3 safe_rcp3(f3 d) { return mk3(safe_rcp(d.x), safe_rcp(d.y), safe_rcp(
 
 // Walk one mesh (second level). Oi/Di: ray in mesh-local space (Di normalised by
 // intersect_prim, raytracer_func.frag:688); Ow: world origin; fwd: mesh -> world.
-MCPT_DEV void mesh_walk(const DevMesh& M, const DevNode* smem_mesh_nodes, f3 Oi, f3 Di, f3 Ow, const Aff& fwd, int prim,
+template <bool COUNT>
+MCPT_DEV void mesh_walk(Work& wk, const DevMesh& M, const DevNode* smem_mesh_nodes, f3 Oi, f3 Di, f3 Ow, const Aff& fwd, int prim,
                         int tslot, float slack, Best& best) {
     // world length of one unit of local parameter: dist ~= a * scale
     f3 wd = mk3(fwd.r0.x * Di.x + fwd.r0.y * Di.y + fwd.r0.z * Di.z, fwd.r1.x * Di.x + fwd.r1.y * Di.y + fwd.r1.z * Di.z,
@@ -84,11 +91,13 @@ MCPT_DEV void mesh_walk(const DevMesh& M, const DevNode* smem_mesh_nodes, f3 Oi,
         if (k < first_leaf) {
             DevNode n = (k <= staged) ? load_node_smem(snodes + k) : load_node(gnodes + k);
             descend = slab(n, idir, od, tmax);
+            if (COUNT) ++wk.boxes;
         } else {
             const DevTri* tp = M.tris + (k - first_leaf);
             float4 ta = __ldg(&tp->a);
             int tri = __float_as_int(ta.w);
             if (tri >= 0) {
+                if (COUNT) ++wk.tris;
                 float4 tb = __ldg(&tp->b), tc = __ldg(&tp->c);
                 float a;
                 if (triangle_test(best, fwd, mk3(ta.x, ta.y, ta.z), mk3(tb.x, tb.y, tb.z), mk3(tc.x, tc.y, tc.z), Oi, Di, Ow,
@@ -117,7 +126,8 @@ MCPT_DEV void mesh_walk(const DevMesh& M, const DevNode* smem_mesh_nodes, f3 Oi,
 }
 
 // intersect_prim, raytracer_func.frag:681-705
-MCPT_DEV void prim_test(const DevScene& S, const SmemScene& sm, int p, f3 O, f3 D, float slack, Best& best) {
+template <bool COUNT>
+MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p, f3 O, f3 D, float slack, Best& best) {
     const DevPrim* pp = (p < S.smem_prims) ? (sm.prims + p) : (S.prims + p);
     const int type = pp->type;
     if (type < 0) return;
@@ -129,11 +139,12 @@ MCPT_DEV void prim_test(const DevScene& S, const SmemScene& sm, int p, f3 O, f3 
     fwd.r1 = pp->fwd.r1;
     fwd.r2 = pp->fwd.r2;
     const int tslot = pp->slot;
+    if (COUNT) ++wk.prims;
     f3 Oi = xform_point(inv, O);
     f3 Di = normalize3(xform_vector(inv, D));
     switch (type) {
         case MCPT_PRIM_MESH:
-            mesh_walk(S.meshes[pp->mesh], sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
+            mesh_walk<COUNT>(wk, S.meshes[pp->mesh], sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
             break;
         case MCPT_PRIM_SPHERE: sphere_test(best, fwd, Oi, Di, O, p, tslot); break;
         case MCPT_PRIM_CUBE: cube_test(best, fwd, Oi, Di, O, p, tslot); break;
@@ -146,7 +157,8 @@ MCPT_DEV void prim_test(const DevScene& S, const SmemScene& sm, int p, f3 O, f3 
 
 // traverse_all_bvh, raytracer_func.frag:777-781. D need not be unit length.
 // any_hit: just_hit_bvh (:771-775) — stop at the first accepted candidate.
-MCPT_DEV void scene_walk(const DevScene& S, const SmemScene& sm, f3 O, f3 D, bool any_hit, Best& best) {
+template <bool COUNT>
+MCPT_DEV void scene_walk(Work& wk, const DevScene& S, const SmemScene& sm, f3 O, f3 D, bool any_hit, Best& best) {
     best_reset(best);
     const float len = sqrtf(D.x * D.x + D.y * D.y + D.z * D.z);
     if (!(len > 0.0f) || !(len < FLT_MAX)) return;  // zero / NaN / inf direction: nothing is hit
@@ -169,10 +181,11 @@ MCPT_DEV void scene_walk(const DevScene& S, const SmemScene& sm, f3 O, f3 D, boo
     while (true) {
         DevNode n = (k <= staged) ? load_node_smem(snodes + k) : load_node(gnodes + k);
         bool inside = slab(n, idir, od, tmax);
+        if (COUNT) ++wk.boxes;
         if (inside && k >= first_leaf) {
             int p = __float_as_int(n.lo.w);
             if (p >= 0) {
-                prim_test(S, sm, p, O, D, slack, best);
+                prim_test<COUNT>(wk, S, sm, p, O, D, slack, best);
                 if (best.h.prim >= 0) {
                     if (any_hit) return;
                     tmax = best.h.dist * 1.0001f + slack;
@@ -196,6 +209,45 @@ MCPT_DEV void scene_walk(const DevScene& S, const SmemScene& sm, f3 O, f3 D, boo
         if (level == 0) break;
         k ^= 1u;
         trail &= ~1u;
+    }
+}
+
+
+// Warp-coherent walk for scenes with a handful of primitives (the reference's box
+// scenes and the four-sphere scene): the leaf boxes form one flat list that every
+// lane of the warp steps through TOGETHER. Each lane culls the box against its own
+// ray; the exact primitive test runs under that predicate, and only if some lane of
+// the warp needs it. All 32 lanes therefore execute the same instruction stream for
+// the same primitive (same type: no switch divergence, no per-lane loop trip counts,
+// one shared-memory broadcast per box). The winner is chosen by the same total order
+// as in the tree walk, so the result does not depend on the visiting order.
+// Must be called by all 32 lanes of a warp; `valid` masks lanes without a ray.
+template <bool COUNT>
+MCPT_DEV void scene_walk_flat(Work& wk, const DevScene& S, const SmemScene& sm, f3 O, f3 D, bool any_hit, bool valid,
+                              Best& best) {
+    best_reset(best);
+    const float len = sqrtf(D.x * D.x + D.y * D.y + D.z * D.z);
+    valid = valid && (len > 0.0f) && (len < FLT_MAX);
+    const float rl = 1.0f / len;
+    const f3 dn = mk3(D.x * rl, D.y * rl, D.z * rl);  // culling only
+    const f3 idir = safe_rcp3(dn);
+    const f3 od = mk3(-O.x * idir.x, -O.y * idir.y, -O.z * idir.z);
+    const float slack = 1e-4f * (fabsf(O.x) + fabsf(O.y) + fabsf(O.z)) + 1e-3f;
+    float tmax = FLT_MAX;
+    const int n = S.n_flat;
+    for (int i = 0; i < n; ++i) {
+        const DevNode nd = sm.top_nodes[i];  // flat list is staged where the tree would be
+        const bool pass = valid && slab(nd, idir, od, tmax);
+        if (COUNT && valid) ++wk.boxes;
+        if (__any_sync(0xffffffffu, pass)) {
+            if (pass) {
+                prim_test<COUNT>(wk, S, sm, __float_as_int(nd.lo.w), O, D, slack, best);
+                if (best.h.prim >= 0) {
+                    tmax = best.h.dist * 1.0001f + slack;
+                    if (any_hit) valid = false;
+                }
+            }
+        }
     }
 }
 

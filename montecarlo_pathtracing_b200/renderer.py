@@ -11,7 +11,7 @@ import ctypes as C
 import numpy as np
 
 from . import capi
-from .capi import McptError, Params, SceneDesc, Stats
+from .capi import McptError, Params, SceneDesc, StageTimes, Stats
 
 
 class Scene:
@@ -249,7 +249,14 @@ class Context:
     def stats(self) -> dict:
         s = Stats()
         self._ck(self._L.mcpt_get_stats(self._c, C.byref(s)))
-        return {"paths": s.paths, "rays": s.rays, "segments": s.segments, "launches": s.launches}
+        return {"paths": s.paths, "rays": s.rays, "segments": s.segments, "launches": s.launches,
+                "boxes": s.boxes, "prim_tests": s.prim_tests, "tri_tests": s.tri_tests}
+
+    def stage_times(self) -> dict:
+        """{stage: (ms, launches)} since the last call (needs OPT_PROFILE_STAGES)."""
+        t = StageTimes()
+        self._ck(self._L.mcpt_get_stage_times(self._c, C.byref(t)))
+        return {n: (t.ms[i], int(t.launches[i])) for i, n in enumerate(capi.STAGE_NAMES)}
 
     def reset_stats(self):
         self._ck(self._L.mcpt_reset_stats(self._c))

@@ -114,3 +114,20 @@ def test_empty_batch_and_errors(ctx):
     s, o = both(1)
     ctx.upload_scene(s)
     assert len(ctx.trace_rays(np.zeros((0, 3)), np.zeros((0, 3)))) == 0
+
+
+def test_flat_walk_equals_tree_walk(ctx):
+    """The warp-coherent flat walk (small scenes) and the per-thread tree walk must agree bit for bit."""
+    s, o = both(2)
+    ro, rd = random_rays(o.prim_data(), 100_000, seed=21)
+    ref = o.trace(ro, rd)
+    c2 = Context(0)
+    c2.set_option(capi.OPT_FLAT_WALK, 0)
+    c2.upload_scene(s)
+    a = c2.trace_rays(ro, rd)
+    c2.set_option(capi.OPT_SMEM_STAGING, 0) if False else None
+    c2.close()
+    ctx.upload_scene(s)
+    b = ctx.trace_rays(ro, rd)
+    assert a.tobytes() == b.tobytes()
+    assert len(compare_hits(a, ref)) == 0
