@@ -156,6 +156,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fast-math", type=int, default=0)
     ap.add_argument("--ppb", type=int, default=0, help="passes per wavefront batch (0 = auto)")
+    ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
         return run_reference(args)
@@ -185,6 +186,8 @@ def main():
     if args.ppb:
         ctx.set_option(capi.OPT_PASSES_PER_BATCH, args.ppb)
     ctx.set_option(capi.OPT_FAST_MATH, args.fast_math)
+    if args.occ:
+        ctx.set_option(capi.OPT_TRAVERSE_OCC, args.occ)
     ctx.upload_scene(s)
     ctx.resize(w, h)
     # accumulate straight into a torch tensor: it is the NCCL send/recv buffer, no staging copy
@@ -209,8 +212,6 @@ def main():
         step()
     barrier()
     ctx.reset_stats()
-    ctx.set_option(capi.OPT_PROFILE_STAGES, 1)
-    ctx.stage_times()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
@@ -223,9 +224,17 @@ def main():
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     ms = ev0.elapsed_time(ev1)
-    stages = ctx.stage_times()
     st = ctx.stats()
+    # per-stage device times: the same steps again with every launch bracketed by CUDA events on
+    # the launching stream (kept out of the timed region above: the events cost a few percent)
+    ctx.set_option(capi.OPT_PROFILE_STAGES, 1)
+    ctx.stage_times()
+    for _ in range(args.steps):
+        step()
+    barrier()
+    stages = ctx.stage_times()
     ctx.set_option(capi.OPT_PROFILE_STAGES, 0)
+    ctx.reset_stats()
     if world > 1:
         t = torch.tensor([ms], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)

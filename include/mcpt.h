@@ -83,8 +83,10 @@ enum {
     MCPT_OPT_SORT_QUEUES = 3,      /* reserved                                               */
     MCPT_OPT_PROFILE_STAGES = 4,   /* 1 = bracket every stage launch with CUDA events         */
     MCPT_OPT_COUNT_WORK = 5,       /* 1 = traversal kernels count boxes / records / triangles */
-    MCPT_OPT_FLAT_WALK = 6         /* 1 = warp-coherent flat walk for scenes of <= 16 primitives (default 1);
+    MCPT_OPT_FLAT_WALK = 6,        /* 1 = warp-coherent flat walk for scenes of <= 16 primitives (default 1);
                                       set before mcpt_upload_scene */
+    MCPT_OPT_TRAVERSE_OCC = 7      /* resident 256-thread CTAs per SM the traversal kernel is register-capped
+                                      for: 2 (<=128 regs), 3 (<=80) or 4 (<=64) */
 };
 
 /* wavefront stages, in launch order inside one bounce */

@@ -61,6 +61,7 @@ struct mcpt_ctx {
     int opt_fast_math = 0;
     int opt_profile = 0;
     int opt_flat_walk = 1;
+    int opt_traverse_occ = 2;
     int opt_count_work = 0;
 
     // stage profiling: (stage, start, stop) triples waiting to be read, plus a free list
@@ -115,7 +116,7 @@ void free_all(std::vector<void*>& v) {
     v.clear();
 }
 
-LaunchCfg lcfg(const mcpt_ctx* c) { return LaunchCfg{c->sm_count, c->stream}; }
+LaunchCfg lcfg(const mcpt_ctx* c) { return LaunchCfg{c->sm_count, c->stream, c->opt_traverse_occ}; }
 
 // rows of the affine part of a column-major mat4
 Aff rows_of(const float m[16]) {
@@ -261,6 +262,10 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
         case MCPT_OPT_PROFILE_STAGES: c->opt_profile = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_COUNT_WORK: c->opt_count_work = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_TRAVERSE_OCC:
+            if (value < 2 || value > 4) return fail(c, MCPT_E_INVALID, "traverse occupancy must be 2, 3 or 4 CTAs per SM");
+            c->opt_traverse_occ = value;
+            return MCPT_OK;
     }
     return fail(c, MCPT_E_INVALID, "unknown option %d", option);
 }

@@ -123,17 +123,18 @@ __device__ __forceinline__ void flush_work(const Work& wk, unsigned long long* w
     }
 }
 
-template <bool COUNT>
-__global__ void __launch_bounds__(kBlock) k_traverse(DevScene S, Wavefront wf, const uint32_t* __restrict__ queue,
-                                                      const uint32_t* __restrict__ n_dev, uint32_t n_host,
-                                                      unsigned long long* ray_counter, unsigned long long* work) {
+// FLAT: warp-coherent flat walk (S.n_flat > 0); MESHES: the scene has triangle meshes.
+template <bool COUNT, int MINB, bool FLAT, bool MESHES>
+__global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront wf, const uint32_t* __restrict__ queue,
+                                                            const uint32_t* __restrict__ n_dev, uint32_t n_host,
+                                                            unsigned long long* ray_counter, unsigned long long* work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t n = n_dev ? *n_dev : n_host;
     if (uint64_t(blockIdx.x) * blockDim.x >= n) return;
     if (blockIdx.x == 0 && threadIdx.x == 0 && ray_counter) atomicAdd(ray_counter, (unsigned long long)n);
     SmemScene sm = stage_scene(S, smem_raw);
     Work wk;
-    if (S.n_flat > 0) {
+    if (FLAT) {
         // warp-uniform trip count: every lane of a warp stays in the loop together
         for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
             const uint32_t i = base + threadIdx.x;
@@ -156,7 +157,7 @@ __global__ void __launch_bounds__(kBlock) k_traverse(DevScene S, Wavefront wf, c
             const uint32_t p = queue ? queue[i] : i;
             float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
             Best best;
-            scene_walk<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
+            scene_walk<COUNT, MESHES>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
             wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
             wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
         }
@@ -164,13 +165,30 @@ __global__ void __launch_bounds__(kBlock) k_traverse(DevScene S, Wavefront wf, c
     if (COUNT) flush_work(wk, work);
 }
 
+template <bool COUNT, int MINB>
+static void launch_traverse_kind(const LaunchCfg& lc, int grid, const DevScene& S, Wavefront wf, const uint32_t* queue,
+                                 const uint32_t* n_dev, uint32_t n_host, unsigned long long* ray_counter,
+                                 unsigned long long* work) {
+    if (S.n_flat > 0)
+        k_traverse<COUNT, MINB, true, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, work);
+    else if (S.n_meshes == 0)
+        k_traverse<COUNT, MINB, false, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, work);
+    else
+        k_traverse<COUNT, MINB, false, true><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, work);
+}
+
 void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const uint32_t* queue, const uint32_t* n_dev,
                      uint32_t n_host, unsigned long long* ray_counter, unsigned long long* work) {
     uint64_t n = n_dev ? 0xffffffffull : n_host;
+    const int grid = grid_for(lc, n, 8);
     if (work)
-        k_traverse<true><<<grid_for(lc, n, 8), kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, work);
+        launch_traverse_kind<true, 2>(lc, grid, S, wf, queue, n_dev, n_host, ray_counter, work);
+    else if (lc.traverse_occ >= 4)
+        launch_traverse_kind<false, 4>(lc, grid, S, wf, queue, n_dev, n_host, ray_counter, nullptr);
+    else if (lc.traverse_occ == 3)
+        launch_traverse_kind<false, 3>(lc, grid, S, wf, queue, n_dev, n_host, ray_counter, nullptr);
     else
-        k_traverse<false><<<grid_for(lc, n, 8), kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, nullptr);
+        launch_traverse_kind<false, 2>(lc, grid, S, wf, queue, n_dev, n_host, ray_counter, nullptr);
     ++g_launches;
 }
 

@@ -30,6 +30,7 @@ struct QueueSet {
 struct LaunchCfg {
     int sm_count;
     cudaStream_t stream;
+    int traverse_occ = 2;  // resident CTAs per SM the traversal kernel is compiled for (register cap)
 };
 
 void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,

@@ -52,6 +52,9 @@ struct Tm {
     static MCPT_DEV float cos_(float x) { return FAST ? __cosf(x) : cosf(x); }
     static MCPT_DEV float log_(float x) { return FAST ? __logf(x) : logf(x); }
     static MCPT_DEV float pow_(float x, float y) { return FAST ? __powf(x, y) : powf(x, y); }
+    // 1/sqrt(x): MUFU.RSQ (<= 2 ulp) or the IEEE sqrt + divide pair of normalize3
+    static MCPT_DEV float rsqrt_(float x) { return FAST ? rsqrtf(x) : 1.0f / sqrtf(x); }
+    static MCPT_DEV f3 normalize_(f3 a) { return a * rsqrt_(dot3(a, a)); }
 };
 
 #define MCPT_PI 3.14159274101257324f /* float(2*acos(0)) */
@@ -62,22 +65,22 @@ MCPT_DEV f3 sample_hemisphere(float roughness, uint3& seed) {
     float alpha = roughness * roughness;
     float beta = 2.0f * MCPT_PI * random_float(seed);
     float tanTheta2 = -alpha * alpha * Tm<FAST>::log_(1.0f - random_float(seed));
-    float cosTheta = 1.0f / sqrtf(1.0f + tanTheta2);
+    float cosTheta = Tm<FAST>::rsqrt_(1.0f + tanTheta2);
     float sinTheta = sqrtf(fmaxf(0.0f, 1.0f - cosTheta * cosTheta));
     f3 localDir = mk3(Tm<FAST>::cos_(beta) * sinTheta, Tm<FAST>::sin_(beta) * sinTheta, cosTheta);
-    return normalize3(localDir);
+    return Tm<FAST>::normalize_(localDir);
 }
 
 // random_ray, tp/montecarlo.frag:72-89: frame (U,V,D) around D, M * sample
 template <bool FAST>
 MCPT_DEV f3 random_ray(f3 D, float roughness, uint3& seed) {
-    f3 W = normalize3(mk3(D.x, D.y + 5.0f, D.z + 3.0f));
-    f3 U = normalize3(cross3(D, W));
-    f3 V = normalize3(cross3(D, U));
+    f3 W = Tm<FAST>::normalize_(mk3(D.x, D.y + 5.0f, D.z + 3.0f));
+    f3 U = Tm<FAST>::normalize_(cross3(D, W));
+    f3 V = Tm<FAST>::normalize_(cross3(D, U));
     f3 s = sample_hemisphere<FAST>(roughness, seed);
     // mat3(U,V,D) * s = U*s.x + V*s.y + D*s.z
     f3 r = mk3(U.x * s.x + V.x * s.y + D.x * s.z, U.y * s.x + V.y * s.y + D.y * s.z, U.z * s.x + V.z * s.y + D.z * s.z);
-    return normalize3(r);
+    return Tm<FAST>::normalize_(r);
 }
 
 // rSchlick, tp/montecarlo.frag:91-98 (I is the incoming direction, as written)
@@ -178,7 +181,7 @@ MCPT_DEV BounceOut bounce(f3 O, f3 D, f3 N, f3 P, float4 mat, float4 col, f3 att
     f3 ray = random_ray<FAST>(N, 1.0f - mat.y, seed);
     float rs = r_schlick(D, N, refract_ind);
     f3 R = reflect3(-ray, N);
-    f3 E = normalize3(O - P);
+    f3 E = Tm<FAST>::normalize_(O - P);
     float se = mixf(100.0f, 2.0f, mat.y);
     float spec = Tm<FAST>::pow_(fmaxf(0.0f, dot3(E, R)), se);
 

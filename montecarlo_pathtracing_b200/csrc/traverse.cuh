@@ -125,8 +125,9 @@ MCPT_DEV void mesh_walk(Work& wk, const DevMesh& M, const DevNode* smem_mesh_nod
     }
 }
 
-// intersect_prim, raytracer_func.frag:681-705
-template <bool COUNT>
+// intersect_prim, raytracer_func.frag:681-705. MESHES = false compiles the mesh walk out
+// (scenes made of analytic primitives only: fewer live registers).
+template <bool COUNT, bool MESHES = true>
 MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p, f3 O, f3 D, float slack, Best& best) {
     const DevPrim* pp = (p < S.smem_prims) ? (sm.prims + p) : (S.prims + p);
     const int type = pp->type;
@@ -144,7 +145,7 @@ MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p,
     f3 Di = normalize3(xform_vector(inv, D));
     switch (type) {
         case MCPT_PRIM_MESH:
-            mesh_walk<COUNT>(wk, S.meshes[pp->mesh], sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
+            if (MESHES) mesh_walk<COUNT>(wk, S.meshes[pp->mesh], sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
             break;
         case MCPT_PRIM_SPHERE: sphere_test(best, fwd, Oi, Di, O, p, tslot); break;
         case MCPT_PRIM_CUBE: cube_test(best, fwd, Oi, Di, O, p, tslot); break;
@@ -157,7 +158,7 @@ MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p,
 
 // traverse_all_bvh, raytracer_func.frag:777-781. D need not be unit length.
 // any_hit: just_hit_bvh (:771-775) — stop at the first accepted candidate.
-template <bool COUNT>
+template <bool COUNT, bool MESHES = true>
 MCPT_DEV void scene_walk(Work& wk, const DevScene& S, const SmemScene& sm, f3 O, f3 D, bool any_hit, Best& best) {
     best_reset(best);
     const float len = sqrtf(D.x * D.x + D.y * D.y + D.z * D.z);
@@ -185,7 +186,7 @@ MCPT_DEV void scene_walk(Work& wk, const DevScene& S, const SmemScene& sm, f3 O,
         if (inside && k >= first_leaf) {
             int p = __float_as_int(n.lo.w);
             if (p >= 0) {
-                prim_test<COUNT>(wk, S, sm, p, O, D, slack, best);
+                prim_test<COUNT, MESHES>(wk, S, sm, p, O, D, slack, best);
                 if (best.h.prim >= 0) {
                     if (any_hit) return;
                     tmax = best.h.dist * 1.0001f + slack;
@@ -241,7 +242,7 @@ MCPT_DEV void scene_walk_flat(Work& wk, const DevScene& S, const SmemScene& sm, 
         if (COUNT && valid) ++wk.boxes;
         if (__any_sync(0xffffffffu, pass)) {
             if (pass) {
-                prim_test<COUNT>(wk, S, sm, __float_as_int(nd.lo.w), O, D, slack, best);
+                prim_test<COUNT, false>(wk, S, sm, __float_as_int(nd.lo.w), O, D, slack, best);
                 if (best.h.prim >= 0) {
                     tmax = best.h.dist * 1.0001f + slack;
                     if (any_hit) valid = false;

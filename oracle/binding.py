@@ -14,13 +14,20 @@ HERE = Path(__file__).resolve().parent
 HIT_DTYPE = np.dtype([("index", "<i4"), ("tri_index", "<i4"), ("shape", "<i4"), ("dir", "<i4"), ("dist", "<f4"),
                       ("pl", "<f4", 3), ("pg", "<f4", 3)])
 
-_lib = None
+_libs = {}
+REF_LIB = HERE / "_ref" / "libref.so"
 
 
-def lib():
-    global _lib
-    if _lib is None:
-        path = HERE / "liboracle.so"
+def have_reference():
+    """True when oracle/_ref/libref.so (the reference's own sources compiled as C++) is present."""
+    return REF_LIB.exists()
+
+
+def lib(kind="port"):
+    """kind 'port': liboracle.so, the hand restatement. kind 'reference': oracle/_ref/libref.so, the
+    reference's own .cpp / shader text compiled by oracle/build_ref.py. Same entry points."""
+    if kind not in _libs:
+        path = REF_LIB if kind == "reference" else HERE / "liboracle.so"
         if not path.exists():
             raise ImportError(f"{path} missing: run __graft_entry__.build()")
         L = C.CDLL(str(path))
@@ -58,8 +65,13 @@ def lib():
         L.oracle_rng_stream.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, C.c_int, fp, vp]
         L.oracle_random_rays.argtypes = [fp, C.c_float, C.c_float, C.c_float, C.c_int, fp]
         L.oracle_primary_ray.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, fp, fp]
-        _lib = L
-    return _lib
+        if kind == "reference":
+            L.oracle_build_repo_scene.argtypes = [vp, C.c_int, C.c_float]
+            L.oracle_default_camera.argtypes = [C.c_int, C.c_int, fp, fp]
+            L.oracle_transfo.argtypes = [C.c_char_p, fp, fp]
+            L.oracle_tex_width.argtypes = [vp, C.c_int]
+        _libs[kind] = L
+    return _libs[kind]
 
 
 def _f32(a):
@@ -69,10 +81,30 @@ def _f32(a):
 class Oracle:
     """CPU restatement of the reference scene tables + shaders."""
 
-    def __init__(self):
-        self.L = lib()
+    def __init__(self, kind="port"):
+        self.kind = kind
+        self.L = lib(kind)
         self.h = C.c_void_p(self.L.oracle_new())
         self._keep = []
+
+    # ---- only on the 'reference' library: the reference's own scene builders / camera / Transfo
+    def build_repo_scene(self, scene_id, light_intensity=1.2):
+        assert self.kind == "reference"
+        rc = self.L.oracle_build_repo_scene(self.h, int(scene_id), light_intensity)
+        assert rc == 0, scene_id
+        return self
+
+    def default_camera(self, w, h):
+        assert self.kind == "reference"
+        iv, ipv = np.zeros(16, np.float32), np.zeros(16, np.float32)
+        self.L.oracle_default_camera(w, h, iv.ctypes.data, ipv.ctypes.data)
+        return iv, ipv
+
+    def transfo(self, ops, *args):
+        assert self.kind == "reference"
+        a, out = _f32(args), np.zeros(16, np.float32)
+        self.L.oracle_transfo(ops.encode(), a.ctypes.data, out.ctypes.data)
+        return out
 
     def __del__(self):
         try:
@@ -111,9 +143,13 @@ class Oracle:
         for r in np.asarray(prims64, np.float32).reshape(-1, 64):
             kind = int(r[48])
             if kind == 0:
-                self.place_mesh(line_to_id[int(r[49])], r[32:48], r[52:56], r[56], r[57], r[58])
+                i = self.place_mesh(line_to_id[int(r[49])], r[32:48], r[52:56], r[56], r[57], r[58])
             else:
-                self.add_prim(kind, r[0:16], r[52:56], r[56], r[57], r[58])
+                i = self.add_prim(kind, r[0:16], r[52:56], r[56], r[57], r[58])
+            # keep the inverse the table's author computed (trf.inverse() is Eigen's in the reference;
+            # every stand-in rounds it a little differently), so both sides trace the SAME table
+            for w in range(16, 32):
+                self.poke_prim(i, w, float(r[w]))
         return self
 
     def finalize(self):
@@ -149,11 +185,13 @@ class Oracle:
     def texture(self, k):
         """k: 0 prim, 1 bb, 2 ind, 3 tri, 4 pos, 5 nrm -> (height, 1024, comps) array."""
         hgt, comps = self.L.oracle_tex_height(self.h, k), self.L.oracle_tex_comps(self.h, k)
+        wid = self.L.oracle_tex_width(self.h, k) if self.kind == "reference" else 1024
         ctype = C.c_int32 if k in (2, 3) else C.c_float
         if hgt == 0:
             return np.zeros((0, 1024, comps), np.int32 if k in (2, 3) else np.float32)
         p = C.cast(self.L.oracle_tex_data(self.h, k), C.POINTER(ctype))
-        return np.ctypeslib.as_array(p, shape=(hgt, 1024, comps)).copy()
+        # the reference allocates its primitive texture 1204 wide (scene.h:77) and fills 1024 columns
+        return np.ctypeslib.as_array(p, shape=(hgt, wid, comps))[:, :1024].copy()
 
     def scene_desc(self):
         """The oracle's tables as an include/mcpt_scene.h descriptor (borrowed pointers)."""

@@ -1,0 +1,12 @@
+set -x
+nvidia-smi -L
+python -m pytest tests -m gpu -x -q > gpurun_out/pytest.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest.log
+python bench.py > gpurun_out/bench_c2.json 2> gpurun_out/bench_c2.err
+python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err
+python bench.py --workload mesh --steps 5 > gpurun_out/bench_mesh.json 2> gpurun_out/bench_mesh.err
+python bench.py --workload c5 --steps 5 --no-cpu-baseline > gpurun_out/bench_c5.json 2> gpurun_out/bench_c5.err
+CMD="python bench.py --steps 2 --warmup 1 --no-cpu-baseline"
+$CMD > gpurun_out/plain.log 2>&1 && ncu --metrics gpu__time_duration.sum --clock-control none -c 1500 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/ncu_launches.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_traverse -s 30 -c 3 -o gpurun_out/prof_traverse $CMD > gpurun_out/ncu_full.log 2>&1
+ncu --set full --clock-control none --import-source on -k regex:k_shade -s 30 -c 2 -o gpurun_out/prof_shade $CMD > gpurun_out/ncu_full2.log 2>&1
+ls -la gpurun_out

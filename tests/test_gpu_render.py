@@ -46,6 +46,20 @@ def test_fixed_seed_image_matches_oracle(ctx, kind, bounces, ior):
     _assert_image_parity(img, ref)
 
 
+@pytest.mark.parametrize("kind,bounces,ior", [(2, 8, 1.5), ("c2", 8, 1.5), (8, 6, 1.0)])
+def test_fast_math_image_parity(ctx, kind, bounces, ior):
+    """MCPT_OPT_FAST_MATH (MUFU sin/cos/log/pow/rsqrt in the bounce sampler) and the register-capped
+    traversal variants stay inside the same image-parity tolerance."""
+    ctx.set_option(capi.OPT_FAST_MATH, 1)
+    ctx.set_option(capi.OPT_TRAVERSE_OCC, 4)
+    try:
+        img, ref = _render_both(ctx, kind, 160, 120, 8, bounces, ior)
+    finally:
+        ctx.set_option(capi.OPT_FAST_MATH, 0)
+        ctx.set_option(capi.OPT_TRAVERSE_OCC, 2)
+    _assert_image_parity(img, ref, frac=0.98)
+
+
 def test_divergence_stress_image(ctx):
     img, ref = _render_both(ctx, "c5", 160, 90, 4, 16, 1.5)
     _assert_image_parity(img, ref, frac=0.97)
