@@ -154,7 +154,7 @@ def main():
     ap.add_argument("--impl", default="b200")
     ap.add_argument("--workload", default="c2", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--fast-math", type=int, default=0)
+    ap.add_argument("--fast-math", type=int, default=1, help="1 = MUFU sin/cos/log/pow/rsqrt in the bounce sampler (same parity tolerance, tests/test_gpu_golden.py)")
     ap.add_argument("--ppb", type=int, default=0, help="passes per wavefront batch (0 = auto)")
     ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
     args = ap.parse_args()
@@ -195,13 +195,14 @@ def main():
     ctx.bind_accum(accum.data_ptr(), accum.numel() * 4)
     ctx.set_camera(iv, ipv)
     ctx.set_params(nb_bounces=bounces, refract_ind=ior, date=DATE)
-    first = rank * spp
+    from montecarlo_pathtracing_b200.distributed import pass_range, reduce_accum
+    first, count = pass_range(rank, world, spp * world)     # weak scaling: spp passes per rank
+    assert count == spp
 
     def step():
         accum.zero_()
         ctx.render(first, spp)
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        reduce_accum(accum, root=0)
 
     def barrier():
         if world > 1:
@@ -255,8 +256,7 @@ def main():
         ctx.set_params(nb_bounces=bounces, refract_ind=ior, date=DATE)
         accum.zero_()
         ctx.render(first, spp)
-        if world > 1:
-            dist.reduce(accum, dst=0, op=dist.ReduceOp.SUM)
+        reduce_accum(accum, root=0)
         if rank == 0:
             ctx._ck(ctx._L.mcpt_resolve(ctx._c, float(spp * world), 1, img.ctypes.data, capi.DST_HOST_RGB32F))
 

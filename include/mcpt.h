@@ -86,7 +86,7 @@ enum {
     MCPT_OPT_FLAT_WALK = 6,        /* 1 = warp-coherent flat walk for scenes of <= 16 primitives (default 1);
                                       set before mcpt_upload_scene */
     MCPT_OPT_TRAVERSE_OCC = 7      /* resident 256-thread CTAs per SM the traversal kernel is register-capped
-                                      for: 2 (<=128 regs), 3 (<=80) or 4 (<=64) */
+                                      for: 2 (<=128 regs), 3 (<=80), 4 (<=64); 0 = auto (default) */
 };
 
 /* wavefront stages, in launch order inside one bounce */

@@ -61,7 +61,7 @@ struct mcpt_ctx {
     int opt_fast_math = 0;
     int opt_profile = 0;
     int opt_flat_walk = 1;
-    int opt_traverse_occ = 2;
+    int opt_traverse_occ = 0;  // 0 = auto
     int opt_count_work = 0;
 
     // stage profiling: (stage, start, stop) triples waiting to be read, plus a free list
@@ -116,7 +116,13 @@ void free_all(std::vector<void*>& v) {
     v.clear();
 }
 
-LaunchCfg lcfg(const mcpt_ctx* c) { return LaunchCfg{c->sm_count, c->stream, c->opt_traverse_occ}; }
+// register cap of the traversal kernel: the flat walk fits 64 registers without spilling (4 CTAs
+// of 256 threads per SM); the tree and mesh walks spill below their natural 80 / 103 registers.
+LaunchCfg lcfg(const mcpt_ctx* c) {
+    int occ = c->opt_traverse_occ;
+    if (occ == 0) occ = (c->have_scene && c->scene.n_flat > 0) ? 4 : 2;
+    return LaunchCfg{c->sm_count, c->stream, occ};
+}
 
 // rows of the affine part of a column-major mat4
 Aff rows_of(const float m[16]) {
@@ -263,7 +269,8 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
         case MCPT_OPT_COUNT_WORK: c->opt_count_work = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TRAVERSE_OCC:
-            if (value < 2 || value > 4) return fail(c, MCPT_E_INVALID, "traverse occupancy must be 2, 3 or 4 CTAs per SM");
+            if (value != 0 && (value < 2 || value > 4))
+                return fail(c, MCPT_E_INVALID, "traverse occupancy must be 0 (auto), 2, 3 or 4 CTAs per SM");
             c->opt_traverse_occ = value;
             return MCPT_OK;
     }

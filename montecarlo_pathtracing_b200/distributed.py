@@ -1,0 +1,47 @@
+"""spp-split rendering across the GPUs of one box: one process per GPU (torchrun), every rank
+traces its own seed range of the SAME frame into its own accumulation buffer, and the buffers are
+combined by ONE sum-reduce to the root (NCCL over NVLink on GPUs; gloo in the CPU tests).
+
+The path shards without any data-path exchange: passes are independent given numero_pass
+(shaders/raytracer_func.frag:105-110) and accumulation is a plain sum (additive blending,
+MontecarloGPU/montecarlo.cpp:450-466). The accumulation buffer IS the collective's send/recv buffer
+(mcpt_bind_accum), so the accumulate kernel writes straight into it and no staging copy exists."""
+from __future__ import annotations
+
+
+def pass_range(rank: int, world: int, n_passes: int, first_pass: int = 0):
+    """Contiguous, disjoint, exhaustive split of passes [first_pass, first_pass + n_passes) over
+    `world` ranks; the first n_passes % world ranks take one extra pass. Returns (first, count)."""
+    if world <= 0 or not (0 <= rank < world) or n_passes < 0:
+        raise ValueError(f"bad split: rank {rank} of {world}, {n_passes} passes")
+    base, rem = divmod(n_passes, world)
+    return first_pass + rank * base + min(rank, rem), base + (1 if rank < rem else 0)
+
+
+def reduce_accum(accum, root: int = 0, group=None):
+    """One sum-reduce of the per-rank accumulation buffers to `root` (in place)."""
+    import torch.distributed as dist
+    if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
+        dist.reduce(accum, dst=root, op=dist.ReduceOp.SUM, group=group)
+    return accum
+
+
+class SplitRenderer:
+    """Drives one Context per rank. `accum` is a float32 torch tensor of h*w*4 elements on the
+    context's device, bound as the library's accumulation target."""
+
+    def __init__(self, ctx, width, height, rank=0, world=1, group=None):
+        import torch
+        self.ctx, self.rank, self.world, self.group = ctx, rank, world, group
+        ctx.resize(width, height)
+        self.accum = torch.zeros(height * width * 4, dtype=torch.float32, device="cuda")
+        ctx.bind_accum(self.accum.data_ptr(), self.accum.numel() * 4)
+
+    def render(self, n_passes, first_pass=0, root=0):
+        """Clear, trace this rank's share of the passes, reduce to root. Asynchronous on the current
+        torch stream (make it the context's stream with Context.set_stream)."""
+        first, count = pass_range(self.rank, self.world, n_passes, first_pass)
+        self.accum.zero_()
+        self.ctx.render(first, count)
+        reduce_accum(self.accum, root, self.group)
+        return self.accum

@@ -83,3 +83,28 @@ def compare_hits(a, b, rtol=1e-5):
         rel = np.abs(a["dist"] - b["dist"]) > rtol * np.abs(b["dist"])
     bad |= hit & rel
     return np.nonzero(bad)[0]
+
+
+def desc_from_arrays(prims, root, meshes=()):
+    """An include/mcpt_scene.h descriptor straight from numpy tables (golden fixtures): prims (n,64)
+    float32 finalized records, root = {'depth','bb','ind'}, meshes = [{'bvh','tri','pos','nrm','mesh_line'}].
+    Returns (desc, keepalive)."""
+    import ctypes as C
+    from montecarlo_pathtracing_b200.capi import BvhDesc, MeshDesc, SceneDesc
+    keep = []
+
+    def arr(a, dt):
+        a = np.ascontiguousarray(a, dtype=dt)
+        keep.append(a)
+        return a.ctypes.data
+
+    def bvh(b):
+        return BvhDesc(arr(b["bb"], np.float32), arr(b["ind"], np.int32), int(b["depth"]))
+
+    marr = (MeshDesc * max(len(meshes), 1))()
+    for i, m in enumerate(meshes):
+        marr[i] = MeshDesc(bvh(m["bvh"]), arr(m["tri"], np.uint32), arr(m["pos"], np.float32), arr(m["nrm"], np.float32),
+                           len(m["tri"]), len(m["pos"]), int(m["mesh_line"]))
+    keep.append(marr)
+    d = SceneDesc(arr(prims, np.float32), len(prims), 0, bvh(root), C.cast(marr, C.POINTER(MeshDesc)), len(meshes))
+    return d, keep

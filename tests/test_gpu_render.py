@@ -56,7 +56,7 @@ def test_fast_math_image_parity(ctx, kind, bounces, ior):
         img, ref = _render_both(ctx, kind, 160, 120, 8, bounces, ior)
     finally:
         ctx.set_option(capi.OPT_FAST_MATH, 0)
-        ctx.set_option(capi.OPT_TRAVERSE_OCC, 2)
+        ctx.set_option(capi.OPT_TRAVERSE_OCC, 0)
     _assert_image_parity(img, ref, frac=0.98)
 
 
