@@ -106,9 +106,14 @@ def desc_bytes(d):
 
 
 def oracle_for(s, raw):
-    from oracle.binding import Oracle
+    """The CPU arm: oracle/_ref/libref.so (the reference's own sources compiled as C++, kind
+    'reference') when it travelled with the repo, else the hand restatement (kind 'port')."""
+    from oracle.binding import Oracle, have_reference
     meshes = s.tables()["meshes"]
-    return Oracle().load_unsorted(raw, meshes).finalize()
+    kind = "reference" if have_reference() else "port"
+    o = Oracle(kind).load_unsorted(raw, meshes).finalize()
+    o.cpu_kind = kind
+    return o
 
 
 def run_reference(args):
@@ -140,8 +145,8 @@ def run_reference(args):
         "impl": "reference", "metric": "Msamples/s", "value": val, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": desc, "note": "reference algorithm on host cores; GLSL via a graphics API is unavailable on this box"},
-        "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": cores, "kind": "port", "sample": sample},
+        "config": {"workload": desc, "note": "reference shader text + host code compiled as C++ (oracle/_ref) on the host cores; GLSL via a graphics API is unavailable on this box"},
+        "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": cores, "kind": o.cpu_kind, "sample": sample},
         "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }))
 
@@ -318,7 +323,7 @@ def main():
         t0 = time.perf_counter()
         o.render(w, h, 1, n_spp, 0, acc, y0, y0 + rows)
         dt = time.perf_counter() - t0
-        cpu = {"value": rows * w * n_spp / dt / 1e6, "unit": "Msamples/s", "cores": cores, "kind": "port",
+        cpu = {"value": rows * w * n_spp / dt / 1e6, "unit": "Msamples/s", "cores": cores, "kind": o.cpu_kind,
                "sample": f"{rows} rows x {w} px x {n_spp} spp (centre band of the {w}x{h} frame), {dt:.1f} s",
                "counters": o.last_counters}
 

@@ -18,7 +18,7 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
         if ((rc = dev_alloc(c, c->wf_allocs, &w.ray_o, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.ray_d, slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &w.hit_a, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.hit_b, slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &w.attenu, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.total, slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &w.seed, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.keep_n, slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &w.keep_n, slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &w.keep_p, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.result, slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &w.flag, slots)) || (rc = dev_alloc(c, c->wf_allocs, &c->queue[0], slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &c->queue[1], slots)) || (rc = dev_alloc(c, c->wf_allocs, &c->queue[2], slots))) {
@@ -148,6 +148,8 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
     if (!c->have_camera) return fail(c, MCPT_E_INVALID, "mcpt_render before mcpt_set_camera");
     if (n_passes < 0) return fail(c, MCPT_E_INVALID, "n_passes < 0");
     if (n_passes == 0) return MCPT_OK;
+    // NB_BOUNCES = 0: random_path's loop body never runs and every path returns vec3(0)
+    if (c->prm.mode == 0 && c->prm.nb_bounces == 0) return MCPT_OK;
     CK(c, cudaSetDevice(c->device));
     const uint32_t npix = uint32_t(c->prm.width) * uint32_t(c->prm.height);
     const int ppb = std::min(passes_per_batch(c, npix), n_passes);
@@ -187,7 +189,7 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
             q.seg_counter = c->dev_stats + 1;
             {
                 StageSpan sp(c, MCPT_STAGE_SHADE);
-                launch_shade(lc, S, c->prm, c->wf, q, last, c->opt_fast_math != 0);
+                launch_shade(lc, S, c->prm, c->wf, q, it == 0, last, first_pass + b0, npix, c->opt_fast_math != 0);
             }
             if (last) break;
             {

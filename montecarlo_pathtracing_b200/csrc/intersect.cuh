@@ -90,7 +90,12 @@ MCPT_DEV void sphere_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, 
     if (delta4 > 0.0f) {
         float sq = sqrtf(delta4);
         float a = -(OD + sq) / D2;
-        if (a > MCPT_EPSILON) offer_at(b, fwd, O, D, a, Ow, prim, 0, tslot, 0);
+        if (a > MCPT_EPSILON) {
+            offer_at(b, fwd, O, D, a, Ow, prim, 0, tslot, 0);
+            // The far root loses against the near one under the shader's strict '<' whenever the
+            // two are separated by more than rounding noise; it is evaluated only when they are not.
+            if (a > 1e-3f && 2.0f * sq > 1e-3f * (a * D2)) return;
+        }
         a = -(OD - sq) / D2;
         if (a > MCPT_EPSILON) offer_at(b, fwd, O, D, a, Ow, prim, 0, tslot, 0);
     }

@@ -89,14 +89,10 @@ __global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam
         else
             dir = d1 * (1.0f - v) + d2 * (1.0f - u) + d3 * ((u + v) - 1.0f);
         dir = normalize3(dir);
-        const int numero_pass = first_pass + int(k);
-        uint3 seed = rng_seed(u, v, numero_pass, prm.date);
+        // attenuation 0.8, total 0 and the RNG seed of a fresh path are implied (k_shade, first
+        // bounce); every path writes its result exactly once, so nothing else is initialised here
         wf.ray_o[p] = make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f);
         wf.ray_d[p] = make_float4(dir.x, dir.y, dir.z, 0.0f);
-        wf.attenu[p] = make_float4(0.8f, 0.8f, 0.8f, 0.0f);
-        wf.total[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-        wf.seed[p] = make_uint4(seed.x, seed.y, seed.z, 0u);
-        wf.result[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
     }
 }
 

@@ -9,7 +9,8 @@
 // interior traversal.
 template <bool FAST>
 __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wavefront wf, const uint32_t* __restrict__ queue,
-                                                   const uint32_t* __restrict__ n_dev, uint32_t n_host, int last_bounce,
+                                                   const uint32_t* __restrict__ n_dev, uint32_t n_host, int first_bounce,
+                                                   int last_bounce, int first_pass, uint32_t npix,
                                                    unsigned long long* seg_counter) {
     const uint32_t n = n_dev ? *n_dev : n_host;
     unsigned int my_segments = 0;
@@ -19,15 +20,21 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
         const int2 hb = wf.hit_b[p];
         const float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
         const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
-        float4 t4 = wf.total[p];
-        f3 total = mk3(t4.x, t4.y, t4.z);
+        const uint32_t n_draws = first_bounce ? 0u : __float_as_uint(d4.w);
+        // a fresh path starts with total = 0 and attenuation 0.8 (tp/montecarlo.frag:105-107)
+        f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
+        if (!first_bounce && prm.mode == 0) {
+            const float4 t4 = wf.total[p];
+            total = mk3(t4.x, t4.y, t4.z);
+            const float4 a4 = wf.attenu[p];
+            attenu = mk3(a4.x, a4.y, a4.z);
+        }
         uint8_t flag = 0;
         if (prm.mode != 0) {
             // debug shaders: a single traversal, no bounce
             f3 res = mk3(0.0f, 0.0f, 0.2f);
             if (hb.x >= 0) {
-                uint4 s4 = wf.seed[p];
-                uint3 seed = make_uint3(s4.x, s4.y, s4.z);
+                uint3 seed = path_seed(p, npix, prm.width, prm.height, first_pass, prm.date, n_draws);
                 f3 N = mk3(0, 0, 0), P = mk3(0, 0, 0);
                 intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
                 if (prm.mode == 1) {
@@ -41,29 +48,28 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
             }
             wf.result[p] = make_float4(res.x, res.y, res.z, 0.0f);
         } else if (hb.x < 0) {
-            float4 a4 = wf.attenu[p];
-            f3 res = sky(total, mk3(a4.x, a4.y, a4.z), D);
+            f3 res = sky(total, attenu, D);
             wf.result[p] = make_float4(res.x, res.y, res.z, 0.0f);
         } else {
             ++my_segments;
-            float4 a4 = wf.attenu[p];
-            uint4 s4 = wf.seed[p];
-            uint3 seed = make_uint3(s4.x, s4.y, s4.z);
+            const uint3 seed0 = path_seed(p, npix, prm.width, prm.height, first_pass, prm.date, n_draws);
+            uint3 seed = seed0;
             f3 N = mk3(0, 0, 0), P = mk3(0, 0, 0);
             intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
             const float4 mat = __ldg(S.mat + hb.x);
             const float4 col = __ldg(S.color + hb.x);
-            BounceOut bo = bounce<FAST>(O, D, N, P, mat, col, mk3(a4.x, a4.y, a4.z), total, seed, prm.refract_ind);
+            BounceOut bo = bounce<FAST>(O, D, N, P, mat, col, attenu, total, seed, prm.refract_ind);
             if (bo.kind == 0) {
                 wf.result[p] = make_float4(total.x, total.y, total.z, 0.0f);
-            } else if (!last_bounce) {
-                // a path still alive after the last iteration returns vec3(0)
-                // (tp/montecarlo.frag:178): result stays at its initial zero.
+            } else if (last_bounce) {
+                // a path still alive after the last iteration returns vec3(0) (tp/montecarlo.frag:178)
+                wf.result[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+            } else {
+                const uint32_t nd = n_draws + draws_between(seed0, seed);
                 wf.ray_o[p] = make_float4(bo.nO.x, bo.nO.y, bo.nO.z, 0.0f);
-                wf.ray_d[p] = make_float4(bo.nD.x, bo.nD.y, bo.nD.z, 0.0f);
+                wf.ray_d[p] = make_float4(bo.nD.x, bo.nD.y, bo.nD.z, __uint_as_float(nd));
                 wf.attenu[p] = make_float4(bo.new_att.x, bo.new_att.y, bo.new_att.z, 0.0f);
                 wf.total[p] = make_float4(total.x, total.y, total.z, 0.0f);
-                wf.seed[p] = make_uint4(seed.x, seed.y, seed.z, 0u);
                 if (bo.kind == 2) {
                     wf.keep_n[p] = make_float4(N.x, N.y, N.z, 0.0f);
                     wf.keep_p[p] = make_float4(P.x, P.y, P.z, 0.0f);
@@ -81,15 +87,15 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
 }
 
 void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueSet& q,
-                  bool last_bounce, bool fast_math) {
+                  bool first_bounce, bool last_bounce, int first_pass, uint32_t npix, bool fast_math) {
     uint64_t n = q.n_cur ? 0xffffffffull : q.n_cur_host;
     int grid = grid_for(lc, n, 8);
     if (fast_math)
-        k_shade<true><<<grid, kBlock, 0, lc.stream>>>(S, prm, wf, q.cur, q.n_cur, q.n_cur_host, last_bounce ? 1 : 0,
-                                                      q.seg_counter);
+        k_shade<true><<<grid, kBlock, 0, lc.stream>>>(S, prm, wf, q.cur, q.n_cur, q.n_cur_host, first_bounce ? 1 : 0,
+                                                      last_bounce ? 1 : 0, first_pass, npix, q.seg_counter);
     else
-        k_shade<false><<<grid, kBlock, 0, lc.stream>>>(S, prm, wf, q.cur, q.n_cur, q.n_cur_host, last_bounce ? 1 : 0,
-                                                       q.seg_counter);
+        k_shade<false><<<grid, kBlock, 0, lc.stream>>>(S, prm, wf, q.cur, q.n_cur, q.n_cur_host, first_bounce ? 1 : 0,
+                                                       last_bounce ? 1 : 0, first_pass, npix, q.seg_counter);
     ++g_launches;
 }
 
@@ -171,7 +177,7 @@ __global__ void __launch_bounds__(kBlock) k_shade_exit(DevScene S, DevParams prm
         f3 nO = P + N * MCPT_BIAS;
         f3 nD = refract3(mk3(d4.x, d4.y, d4.z), -N, 1.0f / prm.refract_ind);
         wf.ray_o[p] = make_float4(nO.x, nO.y, nO.z, 0.0f);
-        wf.ray_d[p] = make_float4(nD.x, nD.y, nD.z, 0.0f);
+        wf.ray_d[p] = make_float4(nD.x, nD.y, nD.z, d4.w);  // w: the path's RNG draw count
     }
 }
 

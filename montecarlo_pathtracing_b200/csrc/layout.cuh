@@ -105,12 +105,11 @@ struct DevParams {
 // SoA wavefront state, one entry per path slot
 struct Wavefront {
     float4* ray_o;     // origin.xyz
-    float4* ray_d;     // direction.xyz
+    float4* ray_d;     // direction.xyz, w = number of RNG draws the path has consumed (uint bits)
     float4* hit_a;     // pl.xyz, dist
     int2* hit_b;       // prim, sub
     float4* attenu;    // attenuation.xyz
     float4* total;     // radiance gathered so far .xyz
-    uint4* seed;       // xxhash32 state .xyz
     float4* keep_n;    // N of the entry hit (interior rays)
     float4* keep_p;    // P of the entry hit (interior rays)
     float4* result;    // value returned by random_path

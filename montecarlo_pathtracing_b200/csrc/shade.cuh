@@ -34,6 +34,24 @@ MCPT_DEV uint3 rng_seed(float tcx, float tcy, int numero_pass, float date) {
     return make_uint3(__float_as_uint(wx), __float_as_uint(wy), __float_as_uint(wz));
 }
 
+// The xxhash32 state after n draws is seed0 + n * (11, 43, 67) (mod 2^32), and seed0 is a function
+// of the pixel, the pass and `date` only. So the wavefront stores the draw COUNT (4 bytes, in the
+// spare lane of the direction) instead of the 12-byte state, and shade rebuilds the state.
+MCPT_DEV uint3 path_seed(uint32_t p, uint32_t npix, int width, int height, int first_pass, float date, uint32_t n_draws) {
+    const uint32_t k = p / npix;
+    const uint32_t pix = p - k * npix;
+    const int x = int(pix % uint32_t(width)), y = int(pix / uint32_t(width));
+    const float u = (float(x) + 0.5f) / float(width);
+    const float v = (float(y) + 0.5f) / float(height);
+    uint3 s = rng_seed(u, v, first_pass + int(k), date);
+    s.x += 11u * n_draws;
+    s.y += 43u * n_draws;
+    s.z += 67u * n_draws;
+    return s;
+}
+// draws consumed between two states: (x1 - x0) / 11 in Z/2^32 (11^-1 = 0xBA2E8BA3)
+MCPT_DEV uint32_t draws_between(uint3 s0, uint3 s1) { return (s1.x - s0.x) * 0xBA2E8BA3u; }
+
 MCPT_DEV float random_float(uint3& s) {
     uint32_t m = xxhash32(s);
     m &= 0x007FFFFFu;

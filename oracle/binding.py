@@ -78,6 +78,26 @@ def _f32(a):
     return np.ascontiguousarray(a, dtype=np.float32)
 
 
+class _quiet_stdout:
+    """The reference's BVH builder prints the root box to std::cout (bvh_gpu/bvh.cpp:92) and add_mesh
+    the mesh box (gpu_bvh_scene.cpp:53); callers such as bench.py own stdout (one JSON line)."""
+
+    def __enter__(self):
+        import os
+        import sys
+        sys.stdout.flush()
+        self._saved = os.dup(1)
+        self._null = os.open(os.devnull, os.O_WRONLY)
+        os.dup2(self._null, 1)
+
+    def __exit__(self, *exc):
+        import os
+        C.CDLL(None).fflush(None)
+        os.dup2(self._saved, 1)
+        os.close(self._saved)
+        os.close(self._null)
+
+
 class Oracle:
     """CPU restatement of the reference scene tables + shaders."""
 
@@ -124,6 +144,9 @@ class Oracle:
     def add_mesh(self, pos, tri, nrm):
         p, n = _f32(pos).reshape(-1, 3), _f32(nrm).reshape(-1, 3)
         t = np.ascontiguousarray(tri, dtype=np.uint32).reshape(-1, 3)
+        if self.kind == "reference":
+            with _quiet_stdout():
+                return self.L.oracle_add_mesh(self.h, p.ctypes.data, len(p), n.ctypes.data, t.ctypes.data, len(t))
         return self.L.oracle_add_mesh(self.h, p.ctypes.data, len(p), n.ctypes.data, t.ctypes.data, len(t))
 
     def place_mesh(self, mesh_id, trf, color, shininess=0.0, roughness=0.0, emissivity=0.0):
@@ -153,7 +176,11 @@ class Oracle:
         return self
 
     def finalize(self):
-        self.L.oracle_finalize(self.h)
+        if self.kind == "reference":
+            with _quiet_stdout():
+                self.L.oracle_finalize(self.h)
+        else:
+            self.L.oracle_finalize(self.h)
         return self
 
     @property
