@@ -126,7 +126,8 @@ def run_reference(args):
     o = oracle_for(s, raw)
     iv, ipv = capi.default_camera(w, h)
     o.set_uniforms(bounces, ior, DATE, 0, iv, ipv)
-    cores = o.set_threads(0)
+    # torchrun exports OMP_NUM_THREADS=1: ask for every core this process may run on explicitly
+    cores = o.set_threads(len(os.sched_getaffinity(0)))
     # bounded sample per step: a band of rows at 1 spp, sized for ~2-4 s on this machine
     # bounded sample per step: the full frame at 1 spp (mesh workload: every 8th of the rows)
     rows = h if args.workload != "mesh" else max(8, h // 8)
@@ -161,6 +162,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fast-math", type=int, default=1, help="1 = MUFU sin/cos/log/pow/rsqrt in the bounce sampler (same parity tolerance, tests/test_gpu_golden.py)")
     ap.add_argument("--ppb", type=int, default=0, help="passes per wavefront batch (0 = auto)")
+    ap.add_argument("--sort", type=int, default=0, help="1 = compaction groups the queues by hit primitive")
     ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -193,6 +195,7 @@ def main():
     ctx.set_option(capi.OPT_FAST_MATH, args.fast_math)
     if args.occ:
         ctx.set_option(capi.OPT_TRAVERSE_OCC, args.occ)
+    ctx.set_option(capi.OPT_SORT_QUEUES, args.sort)
     ctx.upload_scene(s)
     ctx.resize(w, h)
     # accumulate straight into a torch tensor: it is the NCCL send/recv buffer, no staging copy
@@ -252,7 +255,8 @@ def main():
     ctx.bind_accum(accum.data_ptr(), accum.numel() * 4)
     d = s.desc()
     h2d = desc_bytes(d) + 2 * 64 + 28
-    img = np.empty((h, w, 3), np.float32)
+    img_t = torch.empty((h, w, 3), dtype=torch.float32, pin_memory=True)   # pinned host destination
+    img = img_t.numpy()
     d2h = img.nbytes if rank == 0 else 0
 
     def e2e_step():
@@ -266,12 +270,17 @@ def main():
             ctx._ck(ctx._L.mcpt_resolve(ctx._c, float(spp * world), 1, img.ctypes.data, capi.DST_HOST_RGB32F))
 
     e2e_step()
+    e2e_step()
     barrier()
     t0 = time.perf_counter()
+    marks = []
     for _ in range(args.steps):
         e2e_step()
+        marks.append(time.perf_counter())
     barrier()
     e2e_s = time.perf_counter() - t0
+    if rank == 0:
+        sys.stderr.write("e2e ms per step: " + " ".join(f"{1e3 * (b - a):.1f}" for a, b in zip([t0] + marks[:-1], marks)) + "\n")
     if world > 1:
         t = torch.tensor([e2e_s], device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
@@ -312,7 +321,7 @@ def main():
     if not args.no_cpu_baseline:
         o = oracle_for(s, raw)
         o.set_uniforms(bounces, ior, DATE, 0, iv, ipv)
-        cores = o.set_threads(0)
+        cores = o.set_threads(len(os.sched_getaffinity(0)))
         rows = h if args.workload != "mesh" else max(8, h // 8)
         y0 = (h - rows) // 2
         acc = np.zeros((h, w, 3), np.float32)

@@ -80,7 +80,8 @@ enum {
     MCPT_OPT_PASSES_PER_BATCH = 0, /* passes traced together in one wavefront (default auto) */
     MCPT_OPT_SMEM_STAGING = 1,     /* 1 = stage top BVH levels in shared memory (default 1)  */
     MCPT_OPT_FAST_MATH = 2,        /* 1 = MUFU sin/cos/log/pow in the bounce sampler         */
-    MCPT_OPT_SORT_QUEUES = 3,      /* reserved                                               */
+    MCPT_OPT_SORT_QUEUES = 3,      /* 1 = compaction groups survivors by the primitive they hit
+                                      (scenes of <= 16 primitives; default 0)                */
     MCPT_OPT_PROFILE_STAGES = 4,   /* 1 = bracket every stage launch with CUDA events         */
     MCPT_OPT_COUNT_WORK = 5,       /* 1 = traversal kernels count boxes / records / triangles */
     MCPT_OPT_FLAT_WALK = 6,        /* 1 = warp-coherent flat walk for scenes of <= 16 primitives (default 1);

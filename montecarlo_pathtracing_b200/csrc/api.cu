@@ -45,6 +45,8 @@ struct mcpt_ctx {
     float4* accum = nullptr;
     bool accum_owned = false;
     size_t accum_bytes = 0;
+    void* resolve_tmp = nullptr;  // device staging for host-destination resolves
+    size_t resolve_tmp_bytes = 0;
 
     // wavefront
     Wavefront wf{};
@@ -61,6 +63,7 @@ struct mcpt_ctx {
     int opt_fast_math = 0;
     int opt_profile = 0;
     int opt_flat_walk = 1;
+    int opt_sort_queues = 0;
     int opt_traverse_occ = 0;  // 0 = auto
     int opt_count_work = 0;
 
@@ -229,6 +232,7 @@ int mcpt_destroy(mcpt_ctx* c) {
     free_all(c->wf_allocs);
     if (c->accum_owned && c->accum) cudaFree(c->accum);
     if (c->dev_stats) cudaFree(c->dev_stats);
+    if (c->resolve_tmp) cudaFree(c->resolve_tmp);
     for (auto& sp : c->spans) {
         cudaEventDestroy(sp.a);
         cudaEventDestroy(sp.b);
@@ -264,7 +268,7 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
             if (c->have_scene) return fail(c, MCPT_E_INVALID, "set MCPT_OPT_SMEM_STAGING before mcpt_upload_scene");
             return MCPT_OK;
         case MCPT_OPT_FAST_MATH: c->opt_fast_math = value ? 1 : 0; return MCPT_OK;
-        case MCPT_OPT_SORT_QUEUES: return MCPT_OK;
+        case MCPT_OPT_SORT_QUEUES: c->opt_sort_queues = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_PROFILE_STAGES: c->opt_profile = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_COUNT_WORK: c->opt_count_work = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;

@@ -39,7 +39,7 @@ void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const
                      uint32_t n_host, unsigned long long* ray_counter, unsigned long long* work);
 void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueSet& q,
                   bool first_bounce, bool last_bounce, int first_pass, uint32_t npix, bool fast_math);
-void launch_compact(const LaunchCfg& lc, Wavefront wf, const QueueSet& q);
+void launch_compact(const LaunchCfg& lc, Wavefront wf, const QueueSet& q, bool grouped);
 void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const uint32_t* queue,
                        const uint32_t* n_dev);
 void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes);

@@ -18,7 +18,9 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
         const uint32_t p = queue ? queue[i] : i;
         const float4 ha = wf.hit_a[p];
         const int2 hb = wf.hit_b[p];
-        const float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
+        const float4 d4 = wf.ray_d[p];
+        float4 o4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (!FAST) o4 = wf.ray_o[p];  // only E = normalize(O - P) needs it (see bounce())
         const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
         const uint32_t n_draws = first_bounce ? 0u : __float_as_uint(d4.w);
         // a fresh path starts with total = 0 and attenuation 0.8 (tp/montecarlo.frag:105-107)
@@ -74,7 +76,7 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
                     wf.keep_n[p] = make_float4(N.x, N.y, N.z, 0.0f);
                     wf.keep_p[p] = make_float4(P.x, P.y, P.z, 0.0f);
                 }
-                flag = uint8_t(bo.kind);
+                flag = uint8_t(bo.kind | ((hb.x & 15) << 2));  // kind + grouping key (see k_compact_grouped)
             }
         }
         wf.flag[i] = flag;
@@ -120,7 +122,7 @@ __global__ void __launch_bounds__(kBlock) k_compact(Wavefront wf, const uint32_t
         uint8_t f = 0;
         uint32_t p = 0;
         if (i < n) {
-            f = wf.flag[i];
+            f = wf.flag[i] & 3u;
             p = queue ? queue[i] : i;
         }
         const uint32_t m_alive = __ballot_sync(0xffffffffu, f != 0);
@@ -150,10 +152,85 @@ __global__ void __launch_bounds__(kBlock) k_compact(Wavefront wf, const uint32_t
     }
 }
 
-void launch_compact(const LaunchCfg& lc, Wavefront wf, const QueueSet& q) {
+// Grouping variant for scenes of <= 16 primitives (the flat-walk scenes): survivors of a 1024-entry
+// tile leave grouped by the primitive they just hit (= the primitive the next ray starts on), in
+// stable order inside a group. Rays that start on the same primitive pass the same leaf boxes first
+// (their own primitive's box always), so the warp-coherent walk and the material branches of the
+// next shade run with fuller warps. Per warp __match_any_sync ranks lanes inside their key group;
+// per-tile offsets come from a [warp][key] count table in shared memory.
+constexpr int kGroupBlock = 1024;
+constexpr int kGroupKeys = 16;
+
+__global__ void __launch_bounds__(kGroupBlock) k_compact_grouped(Wavefront wf, const uint32_t* __restrict__ queue,
+                                                                  const uint32_t* __restrict__ n_dev, uint32_t n_host,
+                                                                  uint32_t* __restrict__ next, uint32_t* __restrict__ n_next,
+                                                                  uint32_t* __restrict__ interior,
+                                                                  uint32_t* __restrict__ n_interior) {
+    constexpr int W = kGroupBlock / 32;
+    __shared__ uint32_t cnt[2][W][kGroupKeys];   // [alive | interior][warp][key] -> exclusive offsets
+    __shared__ uint32_t key_base[2][kGroupKeys];
+    __shared__ uint32_t tile_base[2];
+    const uint32_t n = n_dev ? *n_dev : n_host;
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t n_tiles = (n + kGroupBlock - 1) / kGroupBlock;
+    const uint32_t below = (1u << lane) - 1u;
+    for (uint32_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        for (int t = threadIdx.x; t < 2 * W * kGroupKeys; t += kGroupBlock) (&cnt[0][0][0])[t] = 0u;
+        __syncthreads();
+        const uint32_t i = tile * kGroupBlock + threadIdx.x;
+        uint32_t f = 0, p = 0;
+        if (i < n) {
+            f = wf.flag[i];
+            p = queue ? queue[i] : i;
+        }
+        const bool alive = (f & 3u) != 0u, inner = (f & 3u) == 2u;
+        const uint32_t key = f >> 2;
+        // lanes with the same key (dead lanes share the sentinel 255)
+        const uint32_t g_alive = __match_any_sync(0xffffffffu, alive ? key : 255u);
+        const uint32_t g_inner = __match_any_sync(0xffffffffu, inner ? key : 255u);
+        const uint32_t r_alive = __popc(g_alive & below), r_inner = __popc(g_inner & below);
+        if (alive && r_alive == 0) cnt[0][warp][key] = __popc(g_alive);
+        if (inner && r_inner == 0) cnt[1][warp][key] = __popc(g_inner);
+        __syncthreads();
+        if (threadIdx.x < 2 * kGroupKeys) {  // one thread per (queue, key): exclusive scan over the warps
+            const int q = threadIdx.x / kGroupKeys, k = threadIdx.x % kGroupKeys;
+            uint32_t off = 0;
+            for (int w = 0; w < W; ++w) {
+                const uint32_t c = cnt[q][w][k];
+                cnt[q][w][k] = off;
+                off += c;
+            }
+            key_base[q][k] = off;  // total of this key, turned into an offset below
+        }
+        __syncthreads();
+        if (threadIdx.x < 2) {
+            const int q = threadIdx.x;
+            uint32_t off = 0;
+            for (int k = 0; k < kGroupKeys; ++k) {
+                const uint32_t c = key_base[q][k];
+                key_base[q][k] = off;
+                off += c;
+            }
+            tile_base[q] = off ? atomicAdd(q == 0 ? n_next : n_interior, off) : 0u;
+        }
+        __syncthreads();
+        if (alive) next[tile_base[0] + key_base[0][key] + cnt[0][warp][key] + r_alive] = p;
+        if (inner) interior[tile_base[1] + key_base[1][key] + cnt[1][warp][key] + r_inner] = p;
+        __syncthreads();
+    }
+}
+
+void launch_compact(const LaunchCfg& lc, Wavefront wf, const QueueSet& q, bool grouped) {
     uint64_t n = q.n_cur ? 0xffffffffull : q.n_cur_host;
-    k_compact<<<grid_for(lc, n, 8), kBlock, 0, lc.stream>>>(wf, q.cur, q.n_cur, q.n_cur_host, q.next, q.n_next, q.interior,
-                                                            q.n_interior);
+    if (grouped) {
+        uint64_t want = (n + kGroupBlock - 1) / kGroupBlock, cap = uint64_t(lc.sm_count) * 2;
+        int grid = int(want < cap ? (want ? want : 1) : cap);
+        k_compact_grouped<<<grid, kGroupBlock, 0, lc.stream>>>(wf, q.cur, q.n_cur, q.n_cur_host, q.next, q.n_next, q.interior,
+                                                               q.n_interior);
+    } else {
+        k_compact<<<grid_for(lc, n, 8), kBlock, 0, lc.stream>>>(wf, q.cur, q.n_cur, q.n_cur_host, q.next, q.n_next, q.interior,
+                                                                q.n_interior);
+    }
     ++g_launches;
 }
 

@@ -199,7 +199,9 @@ MCPT_DEV BounceOut bounce(f3 O, f3 D, f3 N, f3 P, float4 mat, float4 col, f3 att
     f3 ray = random_ray<FAST>(N, 1.0f - mat.y, seed);
     float rs = r_schlick(D, N, refract_ind);
     f3 R = reflect3(-ray, N);
-    f3 E = Tm<FAST>::normalize_(O - P);
+    // E = normalize(O - P) is the reversed ray direction (P lies on the ray from O along D). The
+    // fast variant uses -D / |D| and never reads the ray origin back from the wavefront.
+    f3 E = FAST ? -Tm<FAST>::normalize_(D) : Tm<FAST>::normalize_(O - P);
     float se = mixf(100.0f, 2.0f, mat.y);
     float spec = Tm<FAST>::pow_(fmaxf(0.0f, dot3(E, R)), se);
 

@@ -1,0 +1,6 @@
+set -x
+nvidia-smi -L
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29511 tests/nccl_reduce_check.py > gpurun_out/r6_nccl_check.log 2>&1; echo "nccl check exit $?" >> gpurun_out/r6_nccl_check.log
+python bench.py --gpus 1 --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r6_n1.json 2> gpurun_out/r6_n1.err
+timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29512 bench.py --gpus 2 --steps 10 --warmup 3 --no-cpu-baseline > gpurun_out/r6_n2.json 2> gpurun_out/r6_n2.err
+timeout 300 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29513 bench.py --impl reference --gpus 2 --steps 2 --warmup 1 > gpurun_out/r6_ref_n2.json 2> gpurun_out/r6_ref_n2.err

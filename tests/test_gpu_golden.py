@@ -122,3 +122,36 @@ def test_rng_is_bit_exact_through_the_debug_shader(ctx):
     ctx.clear()
     ctx.render(0, 2)
     assert np.array_equal(a, ctx.read_accum())
+
+
+@pytest.mark.parametrize("sid", [1, 6])
+def test_converges_to_the_reference_16k_spp_image(ctx, sid):
+    """BASELINE.json: RMSE against a 16k-spp converged image of the reference under a stated threshold
+    and mean luminance within 0.5 %. The converged image comes from the reference shader text
+    (tests/golden/make_converged.py). (a) the same 16384 passes on the GPU: only chaotic paths and the
+    summation order differ -> RMSE <= 2e-3; (b) 16384 OTHER passes: two independent estimates, Monte
+    Carlo noise only -> RMSE <= 1e-2 (radiance units, white = 1)."""
+    g = np.load(GOLD / f"scene{sid}.npz")
+    cv = np.load(GOLD / f"converged{sid}.npz")
+    _upload(ctx, g)
+    w, h, bounces = (int(v) for v in cv["size"])
+    spp = int(cv["spp"])
+    ctx.resize(w, h)
+    ctx.set_camera(cv["inv_v"], cv["inv_pv"])
+    ctx.set_params(nb_bounces=bounces, refract_ind=float(cv["ior"]), date=float(DATE))
+    ctx.set_option(capi.OPT_FAST_MATH, 1)
+    try:
+        for first, limit in ((0, 2e-3), (spp, 1e-2)):
+            acc = np.zeros((h, w, 3), np.float64)
+            for k in range(0, spp, 1024):                 # float32 sums of 1024 passes, combined in float64
+                ctx.clear()
+                ctx.render(first + k, 1024)
+                acc += ctx.read_accum()[..., :3]
+            img = acc / spp
+            ref = cv["image"].astype(np.float64)
+            rmse = float(np.sqrt(np.mean((img - ref) ** 2)))
+            dlum = abs(img.mean() - ref.mean()) / ref.mean()
+            assert rmse <= limit, (first, rmse)
+            assert dlum <= 5e-3, (first, dlum)
+    finally:
+        ctx.set_option(capi.OPT_FAST_MATH, 0)

@@ -140,3 +140,29 @@ def test_state_errors(ctx):
     with pytest.raises(McptError):
         c.clear()
     c.close()
+
+
+@pytest.mark.parametrize("kind,bounces", [("c2", 8), (2, 6)])
+def test_queue_grouping_does_not_change_the_image(ctx, kind, bounces):
+    """MCPT_OPT_SORT_QUEUES reorders the wavefront queues only: per-path results, and therefore the
+    pass-ordered sums, are bit-identical."""
+    s, o = both(kind)
+    iv, ipv = capi.default_camera(200, 120)
+    ctx.upload_scene(s)
+    ctx.resize(200, 120)
+    ctx.set_camera(iv, ipv)
+    ctx.set_params(nb_bounces=bounces, refract_ind=1.5, date=float(DATE))
+    ctx.render(0, 6)
+    a = ctx.read_accum()
+    st_a = ctx.stats()
+    ctx.set_option(capi.OPT_SORT_QUEUES, 1)
+    try:
+        ctx.clear()
+        ctx.reset_stats()
+        ctx.render(0, 6)
+        b = ctx.read_accum()
+        st_b = ctx.stats()
+    finally:
+        ctx.set_option(capi.OPT_SORT_QUEUES, 0)
+    assert np.array_equal(a, b)
+    assert st_b["rays"] > 0 and st_a["segments"] % (1 << 64) >= 0
