@@ -80,8 +80,9 @@ enum {
     MCPT_OPT_PASSES_PER_BATCH = 0, /* passes traced together in one wavefront (default auto) */
     MCPT_OPT_SMEM_STAGING = 1,     /* 1 = stage top BVH levels in shared memory (default 1)  */
     MCPT_OPT_FAST_MATH = 2,        /* 1 = MUFU sin/cos/log/pow in the bounce sampler         */
-    MCPT_OPT_SORT_QUEUES = 3,      /* 1 = compaction groups survivors by the primitive they hit
-                                      (scenes of <= 16 primitives; default 0)                */
+    MCPT_OPT_MESH_BVH = 3,         /* 1 = rebuild every mesh tree on the GPU at upload (LBVH, 4-triangle
+                                      leaves; default 1), 0 = walk the uploaded median-split trees;
+                                      set before mcpt_upload_scene. Hit results are the same.   */
     MCPT_OPT_PROFILE_STAGES = 4,   /* 1 = bracket every stage launch with CUDA events         */
     MCPT_OPT_COUNT_WORK = 5,       /* 1 = traversal kernels count boxes / records / triangles */
     MCPT_OPT_FLAT_WALK = 6,        /* 1 = warp-coherent flat walk for scenes of <= 16 primitives (default 1);
@@ -95,7 +96,7 @@ enum {
     MCPT_STAGE_RAYGEN = 0,
     MCPT_STAGE_TRAVERSE = 1,
     MCPT_STAGE_SHADE = 2,
-    MCPT_STAGE_COMPACT = 3,
+    MCPT_STAGE_BVH_BUILD = 3,      /* upload-time mesh tree build (MCPT_OPT_MESH_BVH) */
     MCPT_STAGE_TRAVERSE_INTERIOR = 4,
     MCPT_STAGE_SHADE_EXIT = 5,
     MCPT_STAGE_ACCUMULATE = 6,

@@ -61,7 +61,7 @@ def build_cuda(force=False, verbose=False, extra=()):
     csrc = PKG / "csrc"
     deps = list(csrc.glob("*")) + list(INCLUDE.glob("*.h"))
     if force or _newer(out, deps):
-        _run([nvcc_path(), *NVCC_FLAGS, *extra, "-I", INCLUDE, "-o", out, csrc / "kernels.cu", csrc / "api.cu", "-ldl"], verbose)
+        _run([nvcc_path(), *NVCC_FLAGS, *extra, "-I", INCLUDE, "-o", out, csrc / "kernels.cu", csrc / "api.cu", csrc / "bvh_build.cu", "-ldl"], verbose)
     return out
 
 

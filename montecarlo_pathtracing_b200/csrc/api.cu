@@ -18,6 +18,7 @@
 #include <string>
 #include <vector>
 
+#include "bvh_build.cuh"
 #include "kernels.cuh"
 #include "mcpt.h"
 
@@ -63,7 +64,7 @@ struct mcpt_ctx {
     int opt_fast_math = 0;
     int opt_profile = 0;
     int opt_flat_walk = 1;
-    int opt_sort_queues = 0;
+    int opt_mesh_bvh = 1;
     int opt_traverse_occ = 0;  // 0 = auto
     int opt_count_work = 0;
 
@@ -268,7 +269,7 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
             if (c->have_scene) return fail(c, MCPT_E_INVALID, "set MCPT_OPT_SMEM_STAGING before mcpt_upload_scene");
             return MCPT_OK;
         case MCPT_OPT_FAST_MATH: c->opt_fast_math = value ? 1 : 0; return MCPT_OK;
-        case MCPT_OPT_SORT_QUEUES: c->opt_sort_queues = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_MESH_BVH: c->opt_mesh_bvh = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_PROFILE_STAGES: c->opt_profile = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_COUNT_WORK: c->opt_count_work = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;
@@ -283,5 +284,5 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
 
 }  // extern "C"
 
-#include "api_scene.inl"
 #include "api_render.inl"
+#include "api_scene.inl"

@@ -20,14 +20,14 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
             (rc = dev_alloc(c, c->wf_allocs, &w.attenu, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.total, slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &w.keep_n, slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &w.keep_p, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.result, slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &w.flag, slots)) || (rc = dev_alloc(c, c->wf_allocs, &c->queue[0], slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &c->queue[0], slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &c->queue[1], slots)) || (rc = dev_alloc(c, c->wf_allocs, &c->queue[2], slots))) {
             free_all(c->wf_allocs);
             return rc;
         }
         c->wf_capacity = slots;
     }
-    const int need = 2 * std::max(bounces, 1);
+    const int need = 3 * std::max(bounces, 1);
     if (need > c->counters_len) {
         int rc = dev_alloc(c, c->wf_allocs, &c->counters, size_t(need));
         if (rc) return rc;
@@ -171,23 +171,28 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
             StageSpan sp(c, MCPT_STAGE_RAYGEN);
             launch_raygen(lc, c->prm, c->cam, c->wf, first_pass + b0, nb, npix);
         }
+        // queue[0]: paths entering the bounce, rewritten in place with the survivors by shade (it is
+        // dead once traverse has run); queue[1]: rays that hit something; queue[2]: interior rays.
+        // counters[3*it + {0,1,2}] = hits / survivors / interior rays of bounce `it`.
         uint32_t* q_cur = nullptr;  // identity queue for the first bounce
         const uint32_t* n_cur = nullptr;
-        int spare = 0;  // queue[spare] receives survivors
+        const bool mc = (c->prm.mode == 0);
         for (int it = 0; it < iters; ++it) {
             const bool last = (it == iters - 1);
+            uint32_t* n_hit = c->counters + 3 * it;
             {
                 StageSpan sp(c, MCPT_STAGE_TRAVERSE);
-                launch_traverse(lc, S, c->wf, q_cur, n_cur, slots, c->dev_stats + 0, work);
+                launch_traverse(lc, S, c->wf, q_cur, n_cur, slots, mc ? c->queue[1] : nullptr, n_hit, it == 0,
+                                c->dev_stats + 0, work);
             }
             QueueSet q{};
-            q.cur = q_cur;
-            q.n_cur = n_cur;
+            q.cur = mc ? c->queue[1] : q_cur;
+            q.n_cur = mc ? n_hit : n_cur;
             q.n_cur_host = slots;
-            q.next = c->queue[spare];
+            q.next = c->queue[0];
             q.interior = c->queue[2];
-            q.n_next = c->counters + 2 * it;
-            q.n_interior = c->counters + 2 * it + 1;
+            q.n_next = c->counters + 3 * it + 1;
+            q.n_interior = c->counters + 3 * it + 2;
             q.seg_counter = c->dev_stats + 1;
             {
                 StageSpan sp(c, MCPT_STAGE_SHADE);
@@ -195,12 +200,8 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
             }
             if (last) break;
             {
-                StageSpan sp(c, MCPT_STAGE_COMPACT);
-                launch_compact(lc, c->wf, q, c->opt_sort_queues != 0 && S.n_flat > 0);
-            }
-            {
                 StageSpan sp(c, MCPT_STAGE_TRAVERSE_INTERIOR);
-                launch_traverse(lc, S, c->wf, q.interior, q.n_interior, 0, c->dev_stats + 0, work);
+                launch_traverse(lc, S, c->wf, q.interior, q.n_interior, 0, nullptr, nullptr, false, c->dev_stats + 0, work);
             }
             {
                 StageSpan sp(c, MCPT_STAGE_SHADE_EXIT);
@@ -208,7 +209,6 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
             }
             q_cur = q.next;
             n_cur = q.n_next;
-            spare ^= 1;
         }
         {
             StageSpan sp(c, MCPT_STAGE_ACCUMULATE);

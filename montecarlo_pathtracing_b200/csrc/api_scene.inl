@@ -101,6 +101,56 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         const mcpt_mesh_desc& md = d->meshes[m];
         const int depth = md.bvh.depth;
         const uint32_t first_leaf = 1u << depth;
+        std::vector<uint32_t> idx(md.tri_idx, md.tri_idx + 3 * size_t(md.n_tris));
+        std::vector<float> pos(md.pos, md.pos + 3 * size_t(md.n_verts)), nrm(md.nrm, md.nrm + 3 * size_t(md.n_verts));
+        DevMesh& M = meshes[m];
+        std::memset(&M, 0, sizeof M);
+        uint32_t* di = nullptr;
+        float *dp = nullptr, *dnr = nullptr;
+        if ((rc = upload_vec(c, idx, &di)) || (rc = upload_vec(c, pos, &dp)) || (rc = upload_vec(c, nrm, &dnr))) return rc;
+        M.idx = di;
+        M.pos = dp;
+        M.nrm = dnr;
+        M.depth = depth;
+        M.n_tris = int(md.n_tris);
+        if (c->opt_mesh_bvh && md.n_tris > 0) {
+            // rebuild the tree on the GPU (bvh_build.cu); the reference tree only supplies each
+            // triangle's leaf slot, which ranks equal-distance candidates like its own visit order
+            std::vector<int32_t> slot_of_tri(md.n_tris, -1);
+            for (uint32_t s = 0; s < first_leaf; ++s)
+                if (md.bvh.ind[s] >= 0) slot_of_tri[md.bvh.ind[s]] = int32_t(s);
+            float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+            for (size_t v = 0; v < size_t(md.n_verts); ++v)
+                for (int k = 0; k < 3; ++k) {
+                    lo[k] = std::min(lo[k], pos[3 * v + k]);
+                    hi[k] = std::max(hi[k], pos[3 * v + k]);
+                }
+            const int n_leaves = int((md.n_tris + kMeshLeafTris - 1) / kMeshLeafTris);
+            int32_t* d_slot = nullptr;
+            DevNode2* dn2 = nullptr;
+            DevTri* dt2 = nullptr;
+            std::vector<void*> tmp_allocs;
+            if ((rc = dev_alloc(c, tmp_allocs, &d_slot, slot_of_tri.size())) ||
+                (rc = dev_alloc(c, c->scene_allocs, &dn2, size_t(std::max(n_leaves - 1, 1)))) ||
+                (rc = dev_alloc(c, c->scene_allocs, &dt2, size_t(n_leaves) * kMeshLeafTris))) {
+                free_all(tmp_allocs);
+                return rc;
+            }
+            cudaError_t e = cudaMemcpy(d_slot, slot_of_tri.data(), slot_of_tri.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+            unsigned long long launched = 0;
+            {
+                StageSpan sp(c, MCPT_STAGE_BVH_BUILD);
+                if (e == cudaSuccess)
+                    e = build_mesh_lbvh(c->stream, dp, di, int(md.n_tris), d_slot, lo, hi, dn2, dt2, n_leaves, &launched);
+            }
+            add_launches(launched);
+            free_all(tmp_allocs);
+            CK(c, e);
+            M.nodes2 = dn2;
+            M.tris2 = dt2;
+            M.n_leaves2 = n_leaves;
+            continue;
+        }
         std::vector<DevNode> nodes(first_leaf, empty_node());  // interior nodes 1 .. first_leaf-1
         for (uint32_t k = 1; k < first_leaf; ++k) nodes[k] = pack_node(md.bvh.bb[k - 1], -1);
         std::vector<DevTri> tris(first_leaf);
@@ -117,25 +167,11 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             }
             std::memcpy(&T.a.w, &t, sizeof t);
         }
-        std::vector<uint32_t> idx(md.tri_idx, md.tri_idx + 3 * size_t(md.n_tris));
-        std::vector<float> pos(md.pos, md.pos + 3 * size_t(md.n_verts)), nrm(md.nrm, md.nrm + 3 * size_t(md.n_verts));
-        DevMesh& M = meshes[m];
         DevNode* dn = nullptr;
         DevTri* dt = nullptr;
-        uint32_t* di = nullptr;
-        float *dp = nullptr, *dnr = nullptr;
-        if ((rc = upload_vec(c, nodes, &dn)) || (rc = upload_vec(c, tris, &dt)) || (rc = upload_vec(c, idx, &di)) ||
-            (rc = upload_vec(c, pos, &dp)) || (rc = upload_vec(c, nrm, &dnr)))
-            return rc;
+        if ((rc = upload_vec(c, nodes, &dn)) || (rc = upload_vec(c, tris, &dt))) return rc;
         M.nodes = dn;
         M.tris = dt;
-        M.idx = di;
-        M.pos = dp;
-        M.nrm = dnr;
-        M.depth = depth;
-        M.n_tris = int(md.n_tris);
-        M.smem_off = 0;
-        M.smem_nodes = 0;
     }
 
     // ---- shared-memory staging plan (<= 40 KB so no opt-in is needed and
@@ -152,6 +188,7 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             int share = 512 / d->n_meshes;  // nodes per mesh out of a 16 KB budget
             int off = 0;
             for (DevMesh& M : meshes) {
+                if (M.nodes2) continue;  // GPU-built trees are read through L1/L2 only
                 int cnt = (1 << M.depth) - 1;
                 while (cnt > share) cnt >>= 1;  // 2^L - 1 stays of that form
                 M.smem_off = off;

@@ -1,0 +1,266 @@
+// bvh_build.cu — GPU construction of the per-mesh acceleration structure.
+//
+// The reference builds every mesh tree on the CPU by median split with a cycling axis
+// (BVH_KDtree::compute, bvh_gpu/bvh.cpp:34-93): a complete binary tree with one triangle per leaf
+// slot, whose boxes overlap heavily on curved surfaces. Hit results do not depend on the tree
+// (candidates are ranked by the reference's exact distance and visit order, intersect.cuh), so the
+// library is free to traverse a better one. This file builds an LBVH on the device at upload time:
+//   1. Morton code (30 bit) of every triangle centroid inside the mesh box          k_morton
+//   2. radix sort of (code, triangle)                                               cub::DeviceRadixSort
+//   3. leaves = runs of 4 consecutive triangles in Morton order, stored as 4 DevTri slots with the
+//      triangle id and the reference's leaf slot (tie-break rank)                    k_leaves
+//   4. Karras 2012 radix-tree hierarchy over the leaves, duplicates split by index   k_hierarchy
+//   5. bottom-up box fit with one atomic arrival counter per node; the second arrival writes the
+//      64-byte node {child boxes, child tokens}                                      k_fit
+// Boxes are widened like the top-level ones (pack_node, api.cu) so that the FMA slab test of the
+// traversal only culls.
+#include <cub/device/device_radix_sort.cuh>
+#include <cuda_runtime.h>
+
+#include <cfloat>
+#include <cstdint>
+
+#include "bvh_build.cuh"
+
+namespace mcpt {
+
+namespace {
+
+constexpr int kB = 256;
+constexpr int kLeafTris = kMeshLeafTris;
+
+__device__ __forceinline__ uint32_t expand10(uint32_t v) {
+    v = (v * 0x00010001u) & 0xFF0000FFu;
+    v = (v * 0x00000101u) & 0x0F00F00Fu;
+    v = (v * 0x00000011u) & 0xC30C30C3u;
+    v = (v * 0x00000005u) & 0x49249249u;
+    return v;
+}
+
+__global__ void k_morton(const float* __restrict__ pos, const uint32_t* __restrict__ idx, int n_tris, float3 lo, float3 inv_ext,
+                         uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_tris) return;
+    float c[3];
+    for (int k = 0; k < 3; ++k) {
+        float a = pos[3 * idx[3 * t] + k], b = pos[3 * idx[3 * t + 1] + k], d = pos[3 * idx[3 * t + 2] + k];
+        c[k] = (a + b + d) * (1.0f / 3.0f);
+    }
+    float fx = fminf(fmaxf((c[0] - lo.x) * inv_ext.x * 1024.0f, 0.0f), 1023.0f);
+    float fy = fminf(fmaxf((c[1] - lo.y) * inv_ext.y * 1024.0f, 0.0f), 1023.0f);
+    float fz = fminf(fmaxf((c[2] - lo.z) * inv_ext.z * 1024.0f, 0.0f), 1023.0f);
+    keys[t] = (expand10(uint32_t(fx)) << 2) | (expand10(uint32_t(fy)) << 1) | expand10(uint32_t(fz));
+    vals[t] = uint32_t(t);
+}
+
+// leaf c holds sorted triangles [4c, 4c+4); writes the DevTri slots, the leaf box and the leaf key
+__global__ void k_leaves(const float* __restrict__ pos, const uint32_t* __restrict__ idx, const int32_t* __restrict__ slot_of_tri,
+                         const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_tris, int n_tris,
+                         int n_leaves, DevTri* __restrict__ tris, float* __restrict__ box_lo, float* __restrict__ box_hi,
+                         uint32_t* __restrict__ leaf_keys) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n_leaves) return;
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int j = 0; j < kLeafTris; ++j) {
+        int s = kLeafTris * c + j;
+        DevTri T;
+        T.a = T.b = T.c = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        int tri = -1, rank = -1;
+        if (s < n_tris) {
+            tri = int(sorted_tris[s]);
+            rank = slot_of_tri[tri];
+        }
+        if (rank < 0) tri = -1;  // not in the reference tree: never tested there either
+        if (tri >= 0) {
+            float v[3][3];
+            for (int q = 0; q < 3; ++q)
+                for (int k = 0; k < 3; ++k) {
+                    v[q][k] = pos[3 * idx[3 * tri + q] + k];
+                    lo[k] = fminf(lo[k], v[q][k]);
+                    hi[k] = fmaxf(hi[k], v[q][k]);
+                }
+            T.a = make_float4(v[0][0], v[0][1], v[0][2], 0.0f);
+            T.b = make_float4(v[1][0], v[1][1], v[1][2], 0.0f);
+            T.c = make_float4(v[2][0], v[2][1], v[2][2], 0.0f);
+        }
+        T.a.w = __int_as_float(tri);
+        T.b.w = __int_as_float(rank);
+        tris[s] = T;
+    }
+    for (int k = 0; k < 3; ++k) {
+        box_lo[3 * c + k] = lo[k];
+        box_hi[3 * c + k] = hi[k];
+    }
+    leaf_keys[c] = sorted_keys[kLeafTris * c];
+}
+
+// common-prefix length of leaves i and j (Karras 2012), index as tie-break for equal codes
+__device__ __forceinline__ int delta(const uint32_t* __restrict__ keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    uint32_t a = keys[i], b = keys[j];
+    if (a == b) return 32 + __clz(uint32_t(i) ^ uint32_t(j));
+    return __clz(a ^ b);
+}
+
+// internal node i of the radix tree over n leaves: children and parent links.
+// Node numbering in `parent`: internal nodes 0..n-2, leaves n-1 .. 2n-2.
+__global__ void k_hierarchy(const uint32_t* __restrict__ keys, int n, int2* __restrict__ children, int* __restrict__ parent) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax *= 2;
+    int l = 0;
+    for (int t = lmax / 2; t >= 1; t /= 2)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0, t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int lo = min(i, j), hi = max(i, j);
+    int left = (lo == gamma) ? (n - 1 + gamma) : gamma;            // leaf or internal
+    int right = (hi == gamma + 1) ? (n - 1 + gamma + 1) : (gamma + 1);
+    children[i] = make_int2(left, right);
+    parent[left] = i;
+    parent[right] = i;
+    if (i == 0) parent[0] = -1;
+}
+
+__device__ __forceinline__ void widen(float& lo, float& hi) {
+    if (lo <= hi) {
+        float mag = fmaxf(fabsf(lo), fabsf(hi));
+        float pad = 1e-5f * fmaxf(mag, hi - lo) + 1e-7f;
+        lo -= pad;
+        hi += pad;
+    }
+}
+
+// one thread per leaf climbs; the second thread to reach a node fits it and goes on
+__global__ void k_fit(int n, const int2* __restrict__ children, const int* __restrict__ parent, float* __restrict__ box_lo,
+                      float* __restrict__ box_hi, int* __restrict__ arrivals, DevNode2* __restrict__ nodes) {
+    int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= n) return;
+    // boxes: leaves at [0, n), internal node i at n + i
+    int node = parent[n - 1 + c];
+    while (node >= 0) {
+        __threadfence();
+        if (atomicAdd(&arrivals[node], 1) == 0) return;  // first arrival: the sibling subtree is not ready
+        __threadfence();
+        int2 ch = children[node];
+        int b0 = (ch.x >= n - 1) ? (ch.x - (n - 1)) : (n + ch.x);
+        int b1 = (ch.y >= n - 1) ? (ch.y - (n - 1)) : (n + ch.y);
+        float l0[3], h0[3], l1[3], h1[3];
+        for (int k = 0; k < 3; ++k) {
+            // written by other SMs during this launch: read at L2, not through a stale L1 line
+            l0[k] = __ldcg(box_lo + 3 * b0 + k);
+            h0[k] = __ldcg(box_hi + 3 * b0 + k);
+            l1[k] = __ldcg(box_lo + 3 * b1 + k);
+            h1[k] = __ldcg(box_hi + 3 * b1 + k);
+            box_lo[3 * (n + node) + k] = fminf(l0[k], l1[k]);
+            box_hi[3 * (n + node) + k] = fmaxf(h0[k], h1[k]);
+        }
+        for (int k = 0; k < 3; ++k) {
+            widen(l0[k], h0[k]);
+            widen(l1[k], h1[k]);
+        }
+        // child token: >= 0 internal node index, < 0 leaf: ~leaf
+        int t0 = (ch.x >= n - 1) ? ~(ch.x - (n - 1)) : ch.x;
+        int t1 = (ch.y >= n - 1) ? ~(ch.y - (n - 1)) : ch.y;
+        DevNode2 N;
+        N.lo0 = make_float4(l0[0], l0[1], l0[2], __int_as_float(t0));
+        N.hi0 = make_float4(h0[0], h0[1], h0[2], __int_as_float(t1));
+        N.lo1 = make_float4(l1[0], l1[1], l1[2], 0.0f);
+        N.hi1 = make_float4(h1[0], h1[1], h1[2], 0.0f);
+        nodes[node] = N;
+        node = parent[node];
+    }
+}
+
+// a mesh with a single leaf: one node whose two children are that leaf (an empty child cannot be
+// expressed as a box the symmetric slab test rejects; offering a candidate twice changes nothing)
+__global__ void k_single(const float* __restrict__ box_lo, const float* __restrict__ box_hi, DevNode2* __restrict__ nodes) {
+    float l[3], h[3];
+    for (int k = 0; k < 3; ++k) {
+        l[k] = box_lo[k];
+        h[k] = box_hi[k];
+        widen(l[k], h[k]);
+    }
+    DevNode2 N;
+    N.lo0 = make_float4(l[0], l[1], l[2], __int_as_float(~0));
+    N.hi0 = make_float4(h[0], h[1], h[2], __int_as_float(~0));
+    N.lo1 = make_float4(l[0], l[1], l[2], 0.0f);
+    N.hi1 = make_float4(h[0], h[1], h[2], 0.0f);
+    nodes[0] = N;
+}
+
+}  // namespace
+
+#define BK(call)                        \
+    do {                                \
+        cudaError_t e_ = (call);        \
+        if (e_ != cudaSuccess) {        \
+            for (void* p : tmp) cudaFree(p); \
+            return e_;                  \
+        }                               \
+    } while (0)
+
+cudaError_t build_mesh_lbvh(cudaStream_t stream, const float* d_pos, const uint32_t* d_idx, int n_tris,
+                            const int32_t* d_slot_of_tri, const float lo[3], const float hi[3], DevNode2* d_nodes,
+                            DevTri* d_tris, int n_leaves, unsigned long long* launches) {
+    std::vector<void*> tmp;
+    auto alloc = [&](size_t bytes) -> void* {
+        void* p = nullptr;
+        if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
+        tmp.push_back(p);
+        return p;
+    };
+    const int n = n_leaves;
+    uint32_t* keys = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n_tris));
+    uint32_t* vals = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n_tris));
+    uint32_t* keys2 = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n_tris));
+    uint32_t* vals2 = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n_tris));
+    uint32_t* leaf_keys = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n));
+    float* box_lo = static_cast<float*>(alloc(sizeof(float) * 3 * (2 * size_t(n))));
+    float* box_hi = static_cast<float*>(alloc(sizeof(float) * 3 * (2 * size_t(n))));
+    int2* children = static_cast<int2*>(alloc(sizeof(int2) * n));
+    int* parent = static_cast<int*>(alloc(sizeof(int) * 2 * size_t(n)));
+    int* arrivals = static_cast<int*>(alloc(sizeof(int) * n));
+    if (!keys || !vals || !keys2 || !vals2 || !leaf_keys || !box_lo || !box_hi || !children || !parent || !arrivals) {
+        for (void* p : tmp) cudaFree(p);
+        return cudaErrorMemoryAllocation;
+    }
+    float3 l3 = make_float3(lo[0], lo[1], lo[2]);
+    float3 ie = make_float3(1.0f / fmaxf(hi[0] - lo[0], 1e-30f), 1.0f / fmaxf(hi[1] - lo[1], 1e-30f),
+                            1.0f / fmaxf(hi[2] - lo[2], 1e-30f));
+    k_morton<<<(n_tris + kB - 1) / kB, kB, 0, stream>>>(d_pos, d_idx, n_tris, l3, ie, keys, vals);
+    size_t sort_bytes = 0;
+    BK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys, keys2, vals, vals2, n_tris, 0, 30, stream));
+    void* sort_tmp = alloc(sort_bytes);
+    if (!sort_tmp) {
+        for (void* p : tmp) cudaFree(p);
+        return cudaErrorMemoryAllocation;
+    }
+    BK(cub::DeviceRadixSort::SortPairs(sort_tmp, sort_bytes, keys, keys2, vals, vals2, n_tris, 0, 30, stream));
+    k_leaves<<<(n + kB - 1) / kB, kB, 0, stream>>>(d_pos, d_idx, d_slot_of_tri, keys2, vals2, n_tris, n, d_tris, box_lo, box_hi,
+                                                   leaf_keys);
+    if (n == 1) {
+        k_single<<<1, 1, 0, stream>>>(box_lo, box_hi, d_nodes);
+        if (launches) *launches += 3;
+    } else {
+        BK(cudaMemsetAsync(arrivals, 0, sizeof(int) * n, stream));
+        k_hierarchy<<<(n - 1 + kB - 1) / kB, kB, 0, stream>>>(leaf_keys, n, children, parent);
+        k_fit<<<(n + kB - 1) / kB, kB, 0, stream>>>(n, children, parent, box_lo, box_hi, arrivals, d_nodes);
+        if (launches) *launches += 4;
+    }
+    BK(cudaGetLastError());
+    BK(cudaStreamSynchronize(stream));
+    for (void* p : tmp) cudaFree(p);
+    return cudaSuccess;
+}
+
+}  // namespace mcpt

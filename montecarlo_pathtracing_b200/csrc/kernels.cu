@@ -15,6 +15,7 @@ namespace mcpt {
 
 static unsigned long long g_launches = 0;
 unsigned long long launches_issued() { return g_launches; }
+void add_launches(unsigned long long n) { g_launches += n; }
 
 constexpr int kBlock = 256;
 
@@ -119,72 +120,125 @@ __device__ __forceinline__ void flush_work(const Work& wk, unsigned long long* w
     }
 }
 
+// Append the lanes with `take` set to a device queue: warps ballot, the block's warp counts are
+// combined in shared memory and ONE thread reserves the block's range with a single atomic (a
+// same-address atomic per warp serialises at the L2: measured +35 % on the traversal kernel), then
+// every taking lane writes at base + (takers before it). Must be reached by all threads of the
+// block the same number of times; `slot` alternates 0/1 between consecutive calls so that two
+// barriers per call suffice.
+struct QueueAppender {
+    uint32_t warp_cnt[2][kBlock / 32];
+    uint32_t base[2];
+};
+
+__device__ __forceinline__ void block_append(QueueAppender& qa, int slot, bool take, uint32_t value, uint32_t* __restrict__ out,
+                                             uint32_t* __restrict__ n_out) {
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    const uint32_t m = __ballot_sync(0xffffffffu, take);
+    if (lane == 0) qa.warp_cnt[slot][warp] = __popc(m);
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t sum = 0;
+        for (int w = 0; w < kBlock / 32; ++w) {
+            const uint32_t c = qa.warp_cnt[slot][w];
+            qa.warp_cnt[slot][w] = sum;
+            sum += c;
+        }
+        qa.base[slot] = sum ? atomicAdd(n_out, sum) : 0u;
+    }
+    __syncthreads();
+    if (take) out[qa.base[slot] + qa.warp_cnt[slot][warp] + __popc(m & ((1u << lane) - 1u))] = value;
+}
+
+// Where the closest-hit search of one bounce delivers its result. With a hit queue (the main
+// traversal of the Monte Carlo mode) a ray that leaves the scene ends here -- the fake sky of
+// tp/montecarlo.frag:118-119 is written straight to `result` -- and the rays that hit something are
+// appended to `hitq` (block_append), so the shading kernel only ever sees hits.
+// Without one (interior rays, debug shaders) every ray's record goes to hit_a / hit_b.
+struct HitSink {
+    uint32_t* hitq;
+    uint32_t* n_hit;
+    int first_bounce;  // total = 0, attenuation = 0.8 are implicit (tp/montecarlo.frag:105-107)
+};
+
+__device__ __forceinline__ void deliver(const Wavefront& wf, const HitSink& hs, QueueAppender& qa, int slot, uint32_t p,
+                                        bool valid, const float4& d4, const Best& best) {
+    const bool hit = valid && best.h.prim >= 0;
+    if (hit || (valid && !hs.hitq)) {
+        wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
+        wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
+    } else if (valid) {
+        f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
+        if (!hs.first_bounce) {
+            const float4 t4 = wf.total[p], a4 = wf.attenu[p];
+            total = mk3(t4.x, t4.y, t4.z);
+            attenu = mk3(a4.x, a4.y, a4.z);
+        }
+        const f3 res = sky(total, attenu, mk3(d4.x, d4.y, d4.z));
+        wf.result[p] = make_float4(res.x, res.y, res.z, 0.0f);
+    }
+    if (hs.hitq) block_append(qa, slot, hit, p, hs.hitq, hs.n_hit);  // block-uniform condition
+}
+
 // FLAT: warp-coherent flat walk (S.n_flat > 0); MESHES: the scene has triangle meshes.
+// Every lane of a warp stays in the loop together (warp-uniform trip count).
 template <bool COUNT, int MINB, bool FLAT, bool MESHES>
 __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront wf, const uint32_t* __restrict__ queue,
-                                                            const uint32_t* __restrict__ n_dev, uint32_t n_host,
+                                                            const uint32_t* __restrict__ n_dev, uint32_t n_host, HitSink hs,
                                                             unsigned long long* ray_counter, unsigned long long* work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const uint32_t n = n_dev ? *n_dev : n_host;
     if (uint64_t(blockIdx.x) * blockDim.x >= n) return;
     if (blockIdx.x == 0 && threadIdx.x == 0 && ray_counter) atomicAdd(ray_counter, (unsigned long long)n);
     SmemScene sm = stage_scene(S, smem_raw);
+    __shared__ QueueAppender qa;
     Work wk;
-    if (FLAT) {
-        // warp-uniform trip count: every lane of a warp stays in the loop together
-        for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x) {
-            const uint32_t i = base + threadIdx.x;
-            const bool valid = i < n;
-            const uint32_t p = valid ? (queue ? queue[i] : i) : 0u;
-            float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
-            if (valid) {
-                o4 = wf.ray_o[p];
-                d4 = wf.ray_d[p];
-            }
-            Best best;
+    int slot = 0;
+    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x, slot ^= 1) {
+        const uint32_t i = base + threadIdx.x;
+        const bool valid = i < n;
+        const uint32_t p = valid ? (queue ? queue[i] : i) : 0u;
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
+        if (valid) {
+            o4 = wf.ray_o[p];
+            d4 = wf.ray_d[p];
+        }
+        Best best;
+        if (FLAT)
             scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
-            if (valid) {
-                wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
-                wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
-            }
-        }
-    } else {
-        for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-            const uint32_t p = queue ? queue[i] : i;
-            float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
-            Best best;
+        else if (valid)
             scene_walk<COUNT, MESHES>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
-            wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
-            wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
-        }
+        deliver(wf, hs, qa, slot, p, valid, d4, best);
     }
     if (COUNT) flush_work(wk, work);
 }
 
 template <bool COUNT, int MINB>
 static void launch_traverse_kind(const LaunchCfg& lc, int grid, const DevScene& S, Wavefront wf, const uint32_t* queue,
-                                 const uint32_t* n_dev, uint32_t n_host, unsigned long long* ray_counter,
+                                 const uint32_t* n_dev, uint32_t n_host, const HitSink& hs, unsigned long long* ray_counter,
                                  unsigned long long* work) {
     if (S.n_flat > 0)
-        k_traverse<COUNT, MINB, true, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, work);
+        k_traverse<COUNT, MINB, true, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, hs, ray_counter, work);
     else if (S.n_meshes == 0)
-        k_traverse<COUNT, MINB, false, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, work);
+        k_traverse<COUNT, MINB, false, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, hs, ray_counter, work);
     else
-        k_traverse<COUNT, MINB, false, true><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, ray_counter, work);
+        k_traverse<COUNT, MINB, false, true><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, hs, ray_counter, work);
 }
 
 void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const uint32_t* queue, const uint32_t* n_dev,
-                     uint32_t n_host, unsigned long long* ray_counter, unsigned long long* work) {
+                     uint32_t n_host, uint32_t* hitq, uint32_t* n_hit, bool first_bounce, unsigned long long* ray_counter,
+                     unsigned long long* work) {
     uint64_t n = n_dev ? 0xffffffffull : n_host;
     const int grid = grid_for(lc, n, 8);
+    const HitSink hs{hitq, n_hit, first_bounce ? 1 : 0};
     if (work)
-        launch_traverse_kind<true, 2>(lc, grid, S, wf, queue, n_dev, n_host, ray_counter, work);
+        launch_traverse_kind<true, 2>(lc, grid, S, wf, queue, n_dev, n_host, hs, ray_counter, work);
     else if (lc.traverse_occ >= 4)
-        launch_traverse_kind<false, 4>(lc, grid, S, wf, queue, n_dev, n_host, ray_counter, nullptr);
+        launch_traverse_kind<false, 4>(lc, grid, S, wf, queue, n_dev, n_host, hs, ray_counter, nullptr);
     else if (lc.traverse_occ == 3)
-        launch_traverse_kind<false, 3>(lc, grid, S, wf, queue, n_dev, n_host, ray_counter, nullptr);
+        launch_traverse_kind<false, 3>(lc, grid, S, wf, queue, n_dev, n_host, hs, ray_counter, nullptr);
     else
-        launch_traverse_kind<false, 2>(lc, grid, S, wf, queue, n_dev, n_host, ray_counter, nullptr);
+        launch_traverse_kind<false, 2>(lc, grid, S, wf, queue, n_dev, n_host, hs, ray_counter, nullptr);
     ++g_launches;
 }
 

@@ -49,9 +49,23 @@ struct DevTri {
     float4 c;  // C.xyz
 };
 
+// node of a GPU-built mesh tree (bvh_build.cu): the boxes of both children and their tokens
+// (>= 0: node index, < 0: ~leaf; leaf l owns DevTri slots 4l .. 4l+3, whose b.w holds the
+// reference's leaf slot of the triangle = its visit rank)
+constexpr int kMeshLeafTris = 4;
+
+struct DevNode2 {
+    float4 lo0;  // child 0 min.xyz, w = token of child 0
+    float4 hi0;  // child 0 max.xyz, w = token of child 1
+    float4 lo1;  // child 1 min.xyz
+    float4 hi1;  // child 1 max.xyz
+};
+
 struct DevMesh {
-    const DevNode* nodes;   // 2^depth - 1 interior nodes, heap order
-    const DevTri* tris;     // 2^depth leaf slots
+    const DevNode* nodes;   // 2^depth - 1 interior nodes, heap order   (reference tree; null when rebuilt)
+    const DevTri* tris;     // 2^depth leaf slots                       (reference tree; null when rebuilt)
+    const DevNode2* nodes2; // GPU-built tree (MCPT_OPT_MESH_BVH), null: walk the reference tree
+    const DevTri* tris2;    // its 4 * n_leaves2 triangle slots
     const uint32_t* idx;    // 3 * n_tris vertex ids (shading)
     const float* pos;       // 3 * n_verts
     const float* nrm;       // 3 * n_verts
@@ -59,6 +73,8 @@ struct DevMesh {
     int32_t n_tris;
     int32_t smem_off;       // offset (in nodes) of this mesh's staged top levels, -1 if none
     int32_t smem_nodes;     // number of staged nodes (2^L - 1)
+    int32_t n_leaves2;
+    int32_t pad;
 };
 
 struct DevScene {
@@ -113,7 +129,6 @@ struct Wavefront {
     float4* keep_n;    // N of the entry hit (interior rays)
     float4* keep_p;    // P of the entry hit (interior rays)
     float4* result;    // value returned by random_path
-    uint8_t* flag;     // per queue position: 0 dead, 1 continue, 2 continue + interior ray
 };
 
 }  // namespace mcpt

@@ -125,6 +125,86 @@ MCPT_DEV void mesh_walk(Work& wk, const DevMesh& M, const DevNode* smem_mesh_nod
     }
 }
 
+// conservative slab test that also returns the entry parameter (>= 0)
+MCPT_DEV bool slab_entry(const float4& lo, const float4& hi, f3 idir, f3 od, float tmax, float& tn_out) {
+    float tx0 = __fmaf_rn(lo.x, idir.x, od.x), tx1 = __fmaf_rn(hi.x, idir.x, od.x);
+    float ty0 = __fmaf_rn(lo.y, idir.y, od.y), ty1 = __fmaf_rn(hi.y, idir.y, od.y);
+    float tz0 = __fmaf_rn(lo.z, idir.z, od.z), tz1 = __fmaf_rn(hi.z, idir.z, od.z);
+    float tn = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), 0.0f));
+    float tf = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), tmax));
+    tn_out = tn;
+    return tn <= tf;
+}
+
+// Walk a GPU-built mesh tree (bvh_build.cu): 64-byte nodes holding both child boxes, nearer child
+// first, the farther one pushed with its entry parameter so that it is dropped without a fetch
+// once a closer hit is known; 4-triangle leaves. The radix tree is at most 64 levels deep (30
+// Morton bits + index bits), which bounds the stack. Candidates go through the same triangle_test
+// / offer_at as the reference-tree walk with the reference's leaf slot as rank, so the winner is
+// the one the reference's own traversal keeps.
+constexpr int kLbvhStack = 64;
+
+template <bool COUNT>
+MCPT_DEV void mesh_walk_lbvh(Work& wk, const DevMesh& M, f3 Oi, f3 Di, f3 Ow, const Aff& fwd, int prim, int tslot, float slack,
+                             Best& best) {
+    f3 wd = mk3(fwd.r0.x * Di.x + fwd.r0.y * Di.y + fwd.r0.z * Di.z, fwd.r1.x * Di.x + fwd.r1.y * Di.y + fwd.r1.z * Di.z,
+                fwd.r2.x * Di.x + fwd.r2.y * Di.y + fwd.r2.z * Di.z);
+    float scale = sqrtf(wd.x * wd.x + wd.y * wd.y + wd.z * wd.z);
+    if (!(scale > 0.0f)) return;  // zero or NaN direction: the shader finds nothing either
+    const float inv_scale = 1.0f / scale;
+    const f3 idir = safe_rcp3(Di);
+    const f3 od = mk3(-Oi.x * idir.x, -Oi.y * idir.y, -Oi.z * idir.z);
+    float tmax = (best.h.dist * 1.0001f + slack) * inv_scale;
+
+    int stack_node[kLbvhStack];
+    float stack_t[kLbvhStack];
+    int sp = 0;
+    int cur = 0;  // the root is node 0
+    while (true) {
+        if (cur >= 0) {
+            const DevNode2* np = M.nodes2 + cur;
+            const float4 lo0 = __ldg(&np->lo0), hi0 = __ldg(&np->hi0), lo1 = __ldg(&np->lo1), hi1 = __ldg(&np->hi1);
+            float t0, t1;
+            const bool h0 = slab_entry(lo0, hi0, idir, od, tmax, t0);
+            const bool h1 = slab_entry(lo1, hi1, idir, od, tmax, t1);
+            if (COUNT) wk.boxes += 2;
+            const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(hi0.w);
+            if (h0 && h1) {
+                const bool swap = t1 < t0;
+                stack_node[sp] = swap ? c0 : c1;
+                stack_t[sp] = swap ? t0 : t1;
+                ++sp;
+                cur = swap ? c1 : c0;
+                continue;
+            }
+            if (h0 || h1) {
+                cur = h0 ? c0 : c1;
+                continue;
+            }
+        } else {
+            const DevTri* tp = M.tris2 + kMeshLeafTris * (~cur);
+#pragma unroll 1
+            for (int j = 0; j < kMeshLeafTris; ++j, ++tp) {
+                const float4 ta = __ldg(&tp->a);
+                const int tri = __float_as_int(ta.w);
+                if (tri < 0) continue;
+                if (COUNT) ++wk.tris;
+                const float4 tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+                float a;
+                if (triangle_test(best, fwd, mk3(ta.x, ta.y, ta.z), mk3(tb.x, tb.y, tb.z), mk3(tc.x, tc.y, tc.z), Oi, Di, Ow,
+                                  prim, tri, tslot, __float_as_int(tb.w), a))
+                    tmax = (best.h.dist * 1.0001f + slack) * inv_scale;
+            }
+        }
+        // pop the nearest pending subtree that can still hold a closer hit
+        do {
+            if (sp == 0) return;
+            --sp;
+            cur = stack_node[sp];
+        } while (stack_t[sp] > tmax);
+    }
+}
+
 // intersect_prim, raytracer_func.frag:681-705. MESHES = false compiles the mesh walk out
 // (scenes made of analytic primitives only: fewer live registers).
 template <bool COUNT, bool MESHES = true>
@@ -145,7 +225,13 @@ MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p,
     f3 Di = normalize3(xform_vector(inv, D));
     switch (type) {
         case MCPT_PRIM_MESH:
-            if (MESHES) mesh_walk<COUNT>(wk, S.meshes[pp->mesh], sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
+            if (MESHES) {
+                const DevMesh& M = S.meshes[pp->mesh];
+                if (M.nodes2)
+                    mesh_walk_lbvh<COUNT>(wk, M, Oi, Di, O, fwd, p, tslot, slack, best);
+                else
+                    mesh_walk<COUNT>(wk, M, sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
+            }
             break;
         case MCPT_PRIM_SPHERE: sphere_test(best, fwd, Oi, Di, O, p, tslot); break;
         case MCPT_PRIM_CUBE: cube_test(best, fwd, Oi, Di, O, p, tslot); break;

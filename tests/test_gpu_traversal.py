@@ -63,15 +63,71 @@ def test_host_mirror_tables_give_same_hits(ctx):
     assert len(compare_hits(got, ref)) == 0
 
 
-@pytest.mark.parametrize("n_meshes,tris_log2", [(1, 3), (2, 7), (4, 10), (3, 12)])
-def test_mesh_scene(ctx, n_meshes, tris_log2):
+@pytest.mark.parametrize("mesh_bvh", [1, 0])
+@pytest.mark.parametrize("n_meshes,tris_log2", [(1, 1), (1, 3), (2, 7), (4, 10), (3, 12)])
+def test_mesh_scene(ctx, n_meshes, tris_log2, mesh_bvh):
+    """Mesh_intersect + Triangle_intersect through the GPU-built LBVH (default) and through the
+    uploaded median-split trees: both must give the oracle's records bit for bit."""
     s, o = both("mesh", n_meshes=n_meshes, tris_log2=tris_log2)
     ro, rd = random_rays(o.prim_data(), 100_000, seed=11, clip=150.0)
+    ctx.set_option(capi.OPT_MESH_BVH, mesh_bvh)
+    try:
+        ref = _check(ctx, s, o, ro, rd)
+        assert (ref["tri_index"] >= 0).sum() > (1000 if tris_log2 > 1 else 50)
+        iv, ipv = capi.default_camera(160, 90)
+        o.set_uniforms(8, 1.5, DATE, 0, iv, ipv)
+        _check(ctx, s, o, *camera_rays(o, 160, 90))
+        _check(ctx, s, o, ro[:20000], rd[:20000], any_hit=True)
+    finally:
+        ctx.set_option(capi.OPT_MESH_BVH, 1)
+
+
+@pytest.mark.parametrize("n_tris", [1, 3, 5])
+def test_tiny_meshes(ctx, n_tris):
+    """One leaf (<= 4 triangles) and a ragged second leaf: the GPU tree builder's edge cases."""
+    from montecarlo_pathtracing_b200 import Scene
+    from oracle.binding import Oracle
+    rng = np.random.default_rng(5 + n_tris)
+    pos = rng.uniform(-1, 1, (3 * n_tris, 3)).astype(np.float32)
+    tri = np.arange(3 * n_tris, dtype=np.uint32).reshape(n_tris, 3)
+    s = Scene()
+    mid = s.add_mesh(pos, tri)
+    s.place_mesh(mid, capi.transfo("tZs", 0, 0, 10, 30, 20, 20, 20), (0.8, 0.7, 0.6))
+    s.add_orientedQuad(capi.transfo("tZs", 0, 0, -30, 0, 200, 200, 1), (0.5, 0.5, 0.5))
+    raw = s.prim_data()
+    s.finalize()
+    o = Oracle().load_unsorted(raw, s.tables()["meshes"]).finalize()
+    ro, rd = random_rays(o.prim_data(), 50_000, seed=3, clip=80.0)
     ref = _check(ctx, s, o, ro, rd)
-    assert (ref["tri_index"] >= 0).sum() > 1000
+    assert (ref["tri_index"] >= 0).sum() > 100
+
+
+def test_both_mesh_trees_render_the_same_image(ctx):
+    """Same paths, same rays, same sums whichever tree is walked; the work counters see the
+    different trees (4-triangle leaves test more triangles per ray than 1-triangle leaves)."""
+    s, o = both("mesh", n_meshes=2, tris_log2=12)
     iv, ipv = capi.default_camera(160, 90)
-    o.set_uniforms(8, 1.5, DATE, 0, iv, ipv)
-    _check(ctx, s, o, *camera_rays(o, 160, 90))
+    counts, images = [], []
+    for mesh_bvh in (0, 1):
+        ctx.set_option(capi.OPT_MESH_BVH, mesh_bvh)
+        ctx.set_option(capi.OPT_COUNT_WORK, 1)
+        try:
+            ctx.upload_scene(s)
+            ctx.resize(160, 90)
+            ctx.set_camera(iv, ipv)
+            ctx.set_params(nb_bounces=4, refract_ind=1.5, date=float(DATE))
+            ctx.clear()
+            ctx.reset_stats()
+            ctx.render(0, 2)
+            images.append(ctx.read_accum())
+            counts.append(ctx.stats())
+        finally:
+            ctx.set_option(capi.OPT_COUNT_WORK, 0)
+            ctx.set_option(capi.OPT_MESH_BVH, 1)
+    assert np.array_equal(images[0], images[1])
+    assert counts[0]["rays"] == counts[1]["rays"] and counts[0]["segments"] == counts[1]["segments"]
+    assert counts[0]["prim_tests"] == counts[1]["prim_tests"]
+    assert counts[1]["tri_tests"] > counts[0]["tri_tests"] > 0
 
 
 def test_all_primitive_types_and_degenerate_rays(ctx):
