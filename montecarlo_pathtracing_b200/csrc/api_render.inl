@@ -4,7 +4,22 @@
 
 namespace {
 
-// wavefront buffers for `slots` path slots and up to `bounces` bounces
+// The queue-driven kernels of a batch run on a fixed grid of G CTAs, each owning one region of
+// every queue (kernels.cu): G = 8 CTAs per SM, fewer when the batch has fewer 256-path tiles.
+constexpr int kBlockPaths = 256;
+int wavefront_grid_max(const mcpt_ctx* c) { return c->sm_count * 8; }
+int wavefront_grid(const mcpt_ctx* c, uint64_t slots) {
+    const uint64_t tiles = (slots + kBlockPaths - 1) / kBlockPaths;
+    return int(std::max<uint64_t>(1, std::min<uint64_t>(tiles, uint64_t(wavefront_grid_max(c)))));
+}
+// region capacity: the most tiles any CTA is handed in the first bounce
+uint32_t queue_cap(const mcpt_ctx* c, uint64_t slots) {
+    const uint64_t tiles = (slots + kBlockPaths - 1) / kBlockPaths, g = uint64_t(wavefront_grid(c, slots));
+    return uint32_t((tiles + g - 1) / g * kBlockPaths);
+}
+size_t queue_entries(const mcpt_ctx* c, uint64_t slots) { return size_t(slots) + size_t(kBlockPaths) * size_t(wavefront_grid_max(c)); }
+
+// wavefront buffers for `slots` path slots
 int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
     if (slots > 0x7fffff00ull) return fail(c, MCPT_E_INVALID, "batch of %llu paths is too large", (unsigned long long)slots);
     if (slots > c->wf_capacity) {
@@ -19,15 +34,20 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
             (rc = dev_alloc(c, c->wf_allocs, &w.hit_a, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.hit_b, slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &w.attenu, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.total, slots)) ||
             (rc = dev_alloc(c, c->wf_allocs, &w.keep_n, slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &w.keep_p, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.result, slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &c->queue[0], slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &c->queue[1], slots)) || (rc = dev_alloc(c, c->wf_allocs, &c->queue[2], slots))) {
+            (rc = dev_alloc(c, c->wf_allocs, &w.keep_p, slots)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &c->queue[0], queue_entries(c, slots))) ||
+            (rc = dev_alloc(c, c->wf_allocs, &c->queue[1], queue_entries(c, slots))) ||
+            (rc = dev_alloc(c, c->wf_allocs, &c->queue[2], queue_entries(c, slots)))) {
             free_all(c->wf_allocs);
             return rc;
         }
+        // path tags live in attenu.w: start from a state no batch generation can match
+        CK(c, cudaMemsetAsync(w.attenu, 0, sizeof(float4) * slots, c->stream));
+        c->batch_gen = 0;
         c->wf_capacity = slots;
     }
-    const int need = 3 * std::max(bounces, 1);
+    (void)bounces;
+    const int need = 3 * wavefront_grid_max(c);  // region lengths of the three queues
     if (need > c->counters_len) {
         int rc = dev_alloc(c, c->wf_allocs, &c->counters, size_t(need));
         if (rc) return rc;
@@ -166,53 +186,53 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
     for (int b0 = 0; b0 < n_passes; b0 += ppb) {
         const int nb = std::min(ppb, n_passes - b0);
         const uint32_t slots = npix * uint32_t(nb);
-        CK(c, cudaMemsetAsync(c->counters, 0, sizeof(uint32_t) * c->counters_len, c->stream));
+        // a fresh generation per batch: stale tags of earlier batches never match (layout.cuh)
+        if (++c->batch_gen >= 0x7ffffff0u) {
+            CK(c, cudaMemsetAsync(c->wf.attenu, 0, sizeof(float4) * c->wf_capacity, c->stream));
+            c->batch_gen = 1;
+        }
+        c->prm.batch = c->batch_gen;
         {
             StageSpan sp(c, MCPT_STAGE_RAYGEN);
             launch_raygen(lc, c->prm, c->cam, c->wf, first_pass + b0, nb, npix);
         }
         // queue[0]: paths entering the bounce, rewritten in place with the survivors by shade (it is
         // dead once traverse has run); queue[1]: rays that hit something; queue[2]: interior rays.
-        // counters[3*it + {0,1,2}] = hits / survivors / interior rays of bounce `it`.
-        uint32_t* q_cur = nullptr;  // identity queue for the first bounce
-        const uint32_t* n_cur = nullptr;
+        // counters[q * G_max + b] = length of CTA b's region of queue q.
+        LaunchCfg lq = lc;
+        lq.grid = wavefront_grid(c, slots);
+        const uint32_t cap = queue_cap(c, slots);
+        const int gmax = wavefront_grid_max(c);
+        const QueueOut q_next{c->queue[0], c->counters + 0 * gmax, cap}, q_hit{c->queue[1], c->counters + 1 * gmax, cap},
+            q_int{c->queue[2], c->counters + 2 * gmax, cap}, q_none{nullptr, nullptr, 0};
+        const QueueIn in_identity{nullptr, nullptr, slots, cap}, in_next{q_next.items, q_next.counts, 0, cap},
+            in_hit{q_hit.items, q_hit.counts, 0, cap}, in_int{q_int.items, q_int.counts, 0, cap};
         const bool mc = (c->prm.mode == 0);
         for (int it = 0; it < iters; ++it) {
             const bool last = (it == iters - 1);
-            uint32_t* n_hit = c->counters + 3 * it;
+            const QueueIn& cur = (it == 0) ? in_identity : in_next;
             {
                 StageSpan sp(c, MCPT_STAGE_TRAVERSE);
-                launch_traverse(lc, S, c->wf, q_cur, n_cur, slots, mc ? c->queue[1] : nullptr, n_hit, it == 0,
-                                c->dev_stats + 0, work);
+                launch_traverse(lq, S, c->wf, cur, mc ? q_hit : q_none, c->dev_stats + 0, work);
             }
-            QueueSet q{};
-            q.cur = mc ? c->queue[1] : q_cur;
-            q.n_cur = mc ? n_hit : n_cur;
-            q.n_cur_host = slots;
-            q.next = c->queue[0];
-            q.interior = c->queue[2];
-            q.n_next = c->counters + 3 * it + 1;
-            q.n_interior = c->counters + 3 * it + 2;
-            q.seg_counter = c->dev_stats + 1;
             {
                 StageSpan sp(c, MCPT_STAGE_SHADE);
-                launch_shade(lc, S, c->prm, c->wf, q, it == 0, last, first_pass + b0, npix, c->opt_fast_math != 0);
+                launch_shade(lq, S, c->prm, c->wf, mc ? in_hit : cur, q_next, q_int, it == 0, last, first_pass + b0, npix,
+                             c->opt_fast_math != 0, c->dev_stats + 1);
             }
             if (last) break;
             {
                 StageSpan sp(c, MCPT_STAGE_TRAVERSE_INTERIOR);
-                launch_traverse(lc, S, c->wf, q.interior, q.n_interior, 0, nullptr, nullptr, false, c->dev_stats + 0, work);
+                launch_traverse(lq, S, c->wf, in_int, q_none, c->dev_stats + 0, work);
             }
             {
                 StageSpan sp(c, MCPT_STAGE_SHADE_EXIT);
-                launch_shade_exit(lc, S, c->prm, c->wf, q.interior, q.n_interior);
+                launch_shade_exit(lq, S, c->prm, c->wf, in_int);
             }
-            q_cur = q.next;
-            n_cur = q.n_next;
         }
         {
             StageSpan sp(c, MCPT_STAGE_ACCUMULATE);
-            launch_accumulate(lc, c->wf, c->accum, npix, nb);
+            launch_accumulate(lc, c->wf, c->accum, npix, nb, c->prm.batch);
         }
         c->paths_started += slots;
     }

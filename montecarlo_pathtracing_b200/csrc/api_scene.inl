@@ -222,6 +222,13 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.top_depth = td;
     S.n_prims = d->n_prims;
     S.n_meshes = d->n_meshes;
+    // persistent warps need every mesh tree in the GPU-built form
+    // (measured: 1.8x on the 1 M-triangle workload, but -14 % on a tree of analytic primitives, where
+    // the per-step bookkeeping outweighs the few idle lanes: auto = mesh scenes only)
+    S.persistent = (flat.empty() && ((c->opt_persistent == 1 && d->n_meshes > 0 && c->opt_mesh_bvh) ||
+                                     (c->opt_persistent == 2 && (d->n_meshes == 0 || c->opt_mesh_bvh))))
+                       ? 1
+                       : 0;
     c->scene = S;
     c->have_scene = true;
     return MCPT_OK;

@@ -217,6 +217,25 @@ MCPT_DEV void cone_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, in
 }
 
 // raytracer_func.frag:354-396 (Moeller-Trumbore, u,v in [0,1], a > EPSILON)
+// the parameter test alone (Triangle_intersect up to `a > EPSILON`): true when the candidate at
+// parameter a_out has to be offered
+MCPT_DEV bool triangle_param(f3 A, f3 B, f3 C, f3 O, f3 D, float& a_out) {
+    f3 edge1 = B - A;
+    f3 edge2 = C - A;
+    f3 h = cross3(D, edge2);
+    float det = dot3(edge1, h);
+    if (fabsf(det) < MCPT_EPSILON) return false;
+    float invdet = 1.0f / det;
+    f3 s = O - A;
+    float u = dot3(s, h) * invdet;
+    if (u < 0.0f || u > 1.0f) return false;
+    f3 q = cross3(s, edge1);
+    float v = dot3(D, q) * invdet;
+    if (v < 0.0f || (u + v) > 1.0f) return false;
+    a_out = dot3(edge2, q) * invdet;
+    return a_out > MCPT_EPSILON;
+}
+
 MCPT_DEV bool triangle_test(Best& b, const Aff& fwd, f3 A, f3 B, f3 C, f3 O, f3 D, f3 Ow, int prim, int tri, int tslot,
                             int rank, float& a_out) {
     f3 edge1 = B - A;

@@ -90,8 +90,8 @@ __global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam
         else
             dir = d1 * (1.0f - v) + d2 * (1.0f - u) + d3 * ((u + v) - 1.0f);
         dir = normalize3(dir);
-        // attenuation 0.8, total 0 and the RNG seed of a fresh path are implied (k_shade, first
-        // bounce); every path writes its result exactly once, so nothing else is initialised here
+        // attenuation 0.8, total 0 and the RNG seed of a fresh path are implied (k_shade first bounce,
+        // k_accumulate): nothing else is initialised here
         wf.ray_o[p] = make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f);
         wf.ray_d[p] = make_float4(dir.x, dir.y, dir.z, 0.0f);
     }
@@ -120,125 +120,183 @@ __device__ __forceinline__ void flush_work(const Work& wk, unsigned long long* w
     }
 }
 
-// Append the lanes with `take` set to a device queue: warps ballot, the block's warp counts are
-// combined in shared memory and ONE thread reserves the block's range with a single atomic (a
-// same-address atomic per warp serialises at the L2: measured +35 % on the traversal kernel), then
-// every taking lane writes at base + (takers before it). Must be reached by all threads of the
-// block the same number of times; `slot` alternates 0/1 between consecutive calls so that two
-// barriers per call suffice.
-struct QueueAppender {
-    uint32_t warp_cnt[2][kBlock / 32];
-    uint32_t base[2];
-};
+// ---- per-CTA path queues
+// A queue of path slots is split into one private region per CTA of the (fixed) wavefront grid:
+// CTA b reads region b of its input queue and appends to region b of its output queues, so the
+// append needs no global atomic and no barrier -- a warp ballots, lane 0 bumps the CTA's counter in
+// shared memory, and the lanes write at region base + offset + rank. (One same-address global atomic
+// per warp serialises at the L2, one per block needs two barriers per tile; both were measured at
+// +30 % on the traversal kernel.) A region can never overflow: what a CTA appends is a subset of what
+// it read, and the first bounce hands CTA b the tiles b, b + G, b + 2G ... of the batch, at most
+// `cap` slots. Region lengths live in counts[b]; every CTA writes its own before it exits.
+__device__ __forceinline__ uint32_t queue_len(const QueueIn& q) {
+    if (q.items) return q.counts[blockIdx.x];
+    const uint32_t n_tiles = (q.n_identity + kBlock - 1) / kBlock;
+    if (blockIdx.x >= n_tiles) return 0u;
+    return ((n_tiles - 1u - blockIdx.x) / gridDim.x + 1u) * kBlock;  // whole tiles; the last one is cut by queue_item
+}
 
-__device__ __forceinline__ void block_append(QueueAppender& qa, int slot, bool take, uint32_t value, uint32_t* __restrict__ out,
-                                             uint32_t* __restrict__ n_out) {
-    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    const uint32_t m = __ballot_sync(0xffffffffu, take);
-    if (lane == 0) qa.warp_cnt[slot][warp] = __popc(m);
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t sum = 0;
-        for (int w = 0; w < kBlock / 32; ++w) {
-            const uint32_t c = qa.warp_cnt[slot][w];
-            qa.warp_cnt[slot][w] = sum;
-            sum += c;
-        }
-        qa.base[slot] = sum ? atomicAdd(n_out, sum) : 0u;
+__device__ __forceinline__ bool queue_item(const QueueIn& q, uint32_t i, uint32_t len, uint32_t& p) {
+    p = 0u;
+    if (i >= len) return false;
+    if (q.items) {
+        p = q.items[size_t(blockIdx.x) * q.cap + i];
+        return true;
     }
-    __syncthreads();
-    if (take) out[qa.base[slot] + qa.warp_cnt[slot][warp] + __popc(m & ((1u << lane) - 1u))] = value;
+    p = (blockIdx.x + (i / kBlock) * gridDim.x) * kBlock + (i % kBlock);
+    return p < q.n_identity;
+}
+
+__device__ __forceinline__ void warp_append(uint32_t* s_count, const QueueOut& q, bool take, uint32_t p) {
+    const uint32_t m = __ballot_sync(0xffffffffu, take);
+    if (!m) return;
+    const uint32_t lane = threadIdx.x & 31u;
+    uint32_t off = 0;
+    if (lane == 0) off = atomicAdd(s_count, uint32_t(__popc(m)));
+    off = __shfl_sync(0xffffffffu, off, 0);
+    if (take) q.items[size_t(blockIdx.x) * q.cap + off + __popc(m & ((1u << lane) - 1u))] = p;
 }
 
 // Where the closest-hit search of one bounce delivers its result. With a hit queue (the main
-// traversal of the Monte Carlo mode) a ray that leaves the scene ends here -- the fake sky of
-// tp/montecarlo.frag:118-119 is written straight to `result` -- and the rays that hit something are
-// appended to `hitq` (block_append), so the shading kernel only ever sees hits.
-// Without one (interior rays, debug shaders) every ray's record goes to hit_a / hit_b.
-struct HitSink {
-    uint32_t* hitq;
-    uint32_t* n_hit;
-    int first_bounce;  // total = 0, attenuation = 0.8 are implicit (tp/montecarlo.frag:105-107)
-};
-
-__device__ __forceinline__ void deliver(const Wavefront& wf, const HitSink& hs, QueueAppender& qa, int slot, uint32_t p,
-                                        bool valid, const float4& d4, const Best& best) {
+// traversal of the Monte Carlo mode) the rays that hit something are appended to it, so the shading
+// kernel only ever sees hits, and a ray that leaves the scene needs nothing at all: its path simply
+// stays as it is, and k_accumulate evaluates the fake sky (tp/montecarlo.frag:118-119) from the
+// path's last total / attenuation / direction. No dependent load sits between two walks of a warp.
+// Without a hit queue (interior rays, debug shaders) every ray's record goes to hit_a / hit_b.
+__device__ __forceinline__ void deliver(const Wavefront& wf, const QueueOut& hitq, uint32_t* s_count, uint32_t p, bool valid,
+                                        const Best& best) {
     const bool hit = valid && best.h.prim >= 0;
-    if (hit || (valid && !hs.hitq)) {
+    if (hit || (valid && !hitq.items)) {
         wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
         wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
-    } else if (valid) {
-        f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
-        if (!hs.first_bounce) {
-            const float4 t4 = wf.total[p], a4 = wf.attenu[p];
-            total = mk3(t4.x, t4.y, t4.z);
-            attenu = mk3(a4.x, a4.y, a4.z);
-        }
-        const f3 res = sky(total, attenu, mk3(d4.x, d4.y, d4.z));
-        wf.result[p] = make_float4(res.x, res.y, res.z, 0.0f);
     }
-    if (hs.hitq) block_append(qa, slot, hit, p, hs.hitq, hs.n_hit);  // block-uniform condition
+    if (hitq.items) warp_append(s_count, hitq, hit, p);
 }
 
-// FLAT: warp-coherent flat walk (S.n_flat > 0); MESHES: the scene has triangle meshes.
+// Persistent warps over the CTA's queue region: a lane whose ray is finished delivers it and, once
+// kRefillLanes lanes of the warp are idle, the idle lanes take the next entries of the region (one
+// shared-memory atomic per refill). Incoherent rays -- a few lanes deep inside a mesh while the
+// others have left the scene -- no longer hold a whole warp: measured 4.4 of 32 lanes active in
+// late bounces of the mesh workload with one ray per lane per tile.
+constexpr int kRefillLanes = 8;
+
+template <bool COUNT, bool MESHES>
+__device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
+                                                    uint32_t len, const QueueOut& hitq, uint32_t* s_next,
+                                                    uint32_t* s_hits, Work& wk) {
+    int stack_node[MESHES ? kLbvhStack : 1];
+    float stack_t[MESHES ? kLbvhStack : 1];
+    float wsave[6];
+    WalkState w;
+    w.k = 0u;
+    w.mesh_prim = -1;
+    const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
+    bool has_ray = false, exhausted = false;
+    uint32_t p = 0;
+    while (true) {
+        const uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
+        if (idle) {
+            if (!exhausted && (idle == 0xffffffffu || __popc(idle) >= kRefillLanes)) {
+                uint32_t first = 0;
+                if (lane == 0) first = atomicAdd(s_next, uint32_t(__popc(idle)));
+                first = __shfl_sync(0xffffffffu, first, 0);
+                if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
+                    const float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
+                    walk_begin(w, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+                    has_ray = true;
+                }
+                exhausted = first + __popc(idle) >= len;
+            } else if (idle == 0xffffffffu) {
+                break;
+            }
+        }
+        bool finished = false;
+        if (has_ray) finished = walk_step<COUNT, MESHES>(w, wk, S, sm, stack_node, stack_t, wsave);
+        if (__any_sync(0xffffffffu, finished)) {
+            deliver(wf, hitq, s_hits, p, finished, w.best);
+            if (finished) has_ray = false;
+        }
+    }
+}
+
+// FLAT: warp-coherent flat walk (S.n_flat > 0); MESHES: the scene has triangle meshes; PERSIST:
+// persistent warps with per-lane refill (tree scenes; mesh trees must be the GPU-built ones).
 // Every lane of a warp stays in the loop together (warp-uniform trip count).
-template <bool COUNT, int MINB, bool FLAT, bool MESHES>
-__global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront wf, const uint32_t* __restrict__ queue,
-                                                            const uint32_t* __restrict__ n_dev, uint32_t n_host, HitSink hs,
+template <bool COUNT, int MINB, bool FLAT, bool MESHES, bool PERSIST>
+__global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront wf, QueueIn qin, QueueOut hitq,
                                                             unsigned long long* ray_counter, unsigned long long* work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    const uint32_t n = n_dev ? *n_dev : n_host;
-    if (uint64_t(blockIdx.x) * blockDim.x >= n) return;
-    if (blockIdx.x == 0 && threadIdx.x == 0 && ray_counter) atomicAdd(ray_counter, (unsigned long long)n);
-    SmemScene sm = stage_scene(S, smem_raw);
-    __shared__ QueueAppender qa;
+    __shared__ uint32_t s_hits, s_next;
+    const uint32_t len = queue_len(qin);
+    if (len == 0) {
+        if (threadIdx.x == 0 && hitq.items) hitq.counts[blockIdx.x] = 0u;
+        return;
+    }
+    if (threadIdx.x == 0) s_hits = s_next = 0u;
+    SmemScene sm = stage_scene(S, smem_raw);  // ends with a barrier
     Work wk;
-    int slot = 0;
-    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x, slot ^= 1) {
-        const uint32_t i = base + threadIdx.x;
-        const bool valid = i < n;
-        const uint32_t p = valid ? (queue ? queue[i] : i) : 0u;
-        float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
-        if (valid) {
-            o4 = wf.ray_o[p];
-            d4 = wf.ray_d[p];
-        }
+    if (PERSIST) traverse_persistent<COUNT, MESHES>(S, sm, wf, qin, len, hitq, &s_next, &s_hits, wk);
+    for (uint32_t base = 0; !PERSIST && base < len; base += kBlock) {
+        uint32_t p;
+        const bool valid = queue_item(qin, base + threadIdx.x, len, p);
         Best best;
-        if (FLAT)
-            scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
-        else if (valid)
-            scene_walk<COUNT, MESHES>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
-        deliver(wf, hs, qa, slot, p, valid, d4, best);
+        {
+            float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
+            if (valid) {
+                o4 = wf.ray_o[p];
+                d4 = wf.ray_d[p];
+            }
+            if (FLAT)
+                scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
+            else if (valid)
+                scene_walk<COUNT, MESHES>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
+        }
+        deliver(wf, hitq, &s_hits, p, valid, best);
+    }
+    if (ray_counter && threadIdx.x == 0) {
+        // rays this CTA traced: its region length, or its share of the identity queue (last tile cut at n)
+        unsigned long long rays = len;
+        if (!qin.items) {
+            const uint32_t last_tile = blockIdx.x + (len / kBlock - 1u) * gridDim.x;
+            if (last_tile * kBlock + kBlock > qin.n_identity) rays -= last_tile * kBlock + kBlock - qin.n_identity;
+        }
+        atomicAdd(ray_counter, rays);
     }
     if (COUNT) flush_work(wk, work);
+    if (hitq.items) {
+        __syncthreads();
+        if (threadIdx.x == 0) hitq.counts[blockIdx.x] = s_hits;
+    }
 }
 
 template <bool COUNT, int MINB>
-static void launch_traverse_kind(const LaunchCfg& lc, int grid, const DevScene& S, Wavefront wf, const uint32_t* queue,
-                                 const uint32_t* n_dev, uint32_t n_host, const HitSink& hs, unsigned long long* ray_counter,
-                                 unsigned long long* work) {
+static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const QueueOut& hitq,
+                                 unsigned long long* ray_counter, unsigned long long* work) {
+    const int grid = lc.grid;
+#define MCPT_TRAVERSE(FLAT, MESHES, PERSIST) \
+    k_traverse<COUNT, MINB, FLAT, MESHES, PERSIST><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, hitq, ray_counter, work)
     if (S.n_flat > 0)
-        k_traverse<COUNT, MINB, true, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, hs, ray_counter, work);
-    else if (S.n_meshes == 0)
-        k_traverse<COUNT, MINB, false, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, hs, ray_counter, work);
-    else
-        k_traverse<COUNT, MINB, false, true><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, queue, n_dev, n_host, hs, ray_counter, work);
+        MCPT_TRAVERSE(true, false, false);
+    else if (S.n_meshes == 0) {
+        if (S.persistent) MCPT_TRAVERSE(false, false, true);
+        else MCPT_TRAVERSE(false, false, false);
+    } else {
+        if (S.persistent) MCPT_TRAVERSE(false, true, true);
+        else MCPT_TRAVERSE(false, true, false);
+    }
+#undef MCPT_TRAVERSE
 }
 
-void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const uint32_t* queue, const uint32_t* n_dev,
-                     uint32_t n_host, uint32_t* hitq, uint32_t* n_hit, bool first_bounce, unsigned long long* ray_counter,
-                     unsigned long long* work) {
-    uint64_t n = n_dev ? 0xffffffffull : n_host;
-    const int grid = grid_for(lc, n, 8);
-    const HitSink hs{hitq, n_hit, first_bounce ? 1 : 0};
+void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const QueueOut& hitq,
+                     unsigned long long* ray_counter, unsigned long long* work) {
     if (work)
-        launch_traverse_kind<true, 2>(lc, grid, S, wf, queue, n_dev, n_host, hs, ray_counter, work);
+        launch_traverse_kind<true, 2>(lc, S, wf, qin, hitq, ray_counter, work);
     else if (lc.traverse_occ >= 4)
-        launch_traverse_kind<false, 4>(lc, grid, S, wf, queue, n_dev, n_host, hs, ray_counter, nullptr);
+        launch_traverse_kind<false, 4>(lc, S, wf, qin, hitq, ray_counter, nullptr);
     else if (lc.traverse_occ == 3)
-        launch_traverse_kind<false, 3>(lc, grid, S, wf, queue, n_dev, n_host, hs, ray_counter, nullptr);
+        launch_traverse_kind<false, 3>(lc, S, wf, qin, hitq, ray_counter, nullptr);
     else
-        launch_traverse_kind<false, 2>(lc, grid, S, wf, queue, n_dev, n_host, hs, ray_counter, nullptr);
+        launch_traverse_kind<false, 2>(lc, S, wf, qin, hitq, ray_counter, nullptr);
     ++g_launches;
 }
 

@@ -15,35 +15,37 @@ struct CameraRays {
     float dir[4][3];  // Dir_in at strip vertices (0,0) (1,0) (0,1) (1,1)
 };
 
-// device-side queue bookkeeping of one shade launch
-struct QueueSet {
-    uint32_t* cur;       // path slots to shade: the hit queue of this bounce (nullptr: identity)
-    uint32_t* next;      // survivors
-    uint32_t* interior;  // paths that need the interior traversal
-    const uint32_t* n_cur;  // device count of `cur` (nullptr: use n_cur_host)
-    uint32_t n_cur_host;
-    uint32_t* n_next;
-    uint32_t* n_interior;
-    unsigned long long* seg_counter;  // shaded-hit statistics (may be null)
+// A queue of path slots, split into one private region of `cap` entries per CTA of the wavefront
+// grid (see kernels.cu). items == nullptr as input: the identity over n_identity slots.
+struct QueueIn {
+    const uint32_t* items;
+    const uint32_t* counts;  // entries in each CTA's region
+    uint32_t n_identity;
+    uint32_t cap;
+};
+struct QueueOut {
+    uint32_t* items;  // nullptr: no queue
+    uint32_t* counts;
+    uint32_t cap;
 };
 
 struct LaunchCfg {
     int sm_count;
     cudaStream_t stream;
     int traverse_occ = 2;  // resident CTAs per SM the traversal kernel is compiled for (register cap)
+    int grid = 1;          // CTAs of every queue-driven kernel of the current batch (fixed: regions are per CTA)
 };
 
 void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,
                    int n_passes, uint32_t npix);
-// hitq != null: rays that leave the scene end in the kernel (sky), the others are appended to hitq
-void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const uint32_t* queue, const uint32_t* n_dev,
-                     uint32_t n_host, uint32_t* hitq, uint32_t* n_hit, bool first_bounce, unsigned long long* ray_counter,
-                     unsigned long long* work);
-void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueSet& q,
-                  bool first_bounce, bool last_bounce, int first_pass, uint32_t npix, bool fast_math);
-void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const uint32_t* queue,
-                       const uint32_t* n_dev);
-void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes);
+// hitq.items != null: rays that hit something are appended to hitq; the others are already settled
+void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const QueueOut& hitq,
+                     unsigned long long* ray_counter, unsigned long long* work);
+void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin,
+                  const QueueOut& next, const QueueOut& interior, bool first_bounce, bool last_bounce, int first_pass,
+                  uint32_t npix, bool fast_math, unsigned long long* seg_counter);
+void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin);
+void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes, uint32_t batch);
 void launch_resolve(const LaunchCfg& lc, const float4* accum, int w, int h, float divisor, int subsampling, void* dst,
                     bool rgba8);
 void launch_trace(const LaunchCfg& lc, const DevScene& S, int64_t n, const float4* o, const float4* d, void* hits_out,

@@ -7,26 +7,26 @@
 // (tp/montecarlo_mat.frag:5-20, tp/montecarlo_mat_tr.frag:5-20) when mode != 0.
 // In the Monte Carlo mode the queue holds only rays that hit something (k_traverse ends the
 // others). Paths that go on are appended to `next` -- and to `interior` when the new ray starts
-// inside a transparent primitive -- by block_append (warp ballots + one atomic per block and
-// queue): that is the whole compaction, there is no separate pass and no flag array. The loop
-// trip count is block-uniform so the barriers inside are legal.
+// inside a transparent primitive -- by warp_append into this CTA's regions of the two queues
+// (kernels.cu): that is the whole compaction, there is no separate pass and no flag array.
 template <bool FAST>
-__global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wavefront wf, const uint32_t* __restrict__ queue,
-                                                   const uint32_t* __restrict__ n_dev, uint32_t n_host,
-                                                   uint32_t* __restrict__ next, uint32_t* __restrict__ n_next,
-                                                   uint32_t* __restrict__ interior, uint32_t* __restrict__ n_interior,
-                                                   int first_bounce, int last_bounce, int first_pass, uint32_t npix,
-                                                   unsigned long long* seg_counter) {
-    const uint32_t n = n_dev ? *n_dev : n_host;
+__global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wavefront wf, QueueIn qin, QueueOut next,
+                                                   QueueOut interior, int first_bounce, int last_bounce, int first_pass,
+                                                   uint32_t npix, unsigned long long* seg_counter) {
+    __shared__ uint32_t s_count[2];
+    const uint32_t len = queue_len(qin);
+    if (len == 0) {
+        if (threadIdx.x == 0 && next.items) next.counts[blockIdx.x] = interior.counts[blockIdx.x] = 0u;
+        return;
+    }
+    if (threadIdx.x < 2) s_count[threadIdx.x] = 0u;
+    __syncthreads();
     const uint32_t lane = threadIdx.x & 31u;
+    const float tag_alive = __uint_as_float(2u * prm.batch), tag_ended = __uint_as_float(2u * prm.batch + 1u);
     unsigned int my_segments = 0;
-    __shared__ QueueAppender qa_next, qa_int;
-    int slot = 0;
-    for (uint32_t base = blockIdx.x * blockDim.x; base < n; base += gridDim.x * blockDim.x, slot ^= 1) {
-        const uint32_t i = base + threadIdx.x;
-        uint32_t kind = 0, p = 0;  // kind: 0 ended, 1 goes on, 2 goes on after an interior traversal
-        if (i < n) {
-            p = queue ? queue[i] : i;
+    for (uint32_t base = 0; base < len; base += kBlock) {
+        uint32_t kind = 0, p;  // kind: 0 ended, 1 goes on, 2 goes on after an interior traversal
+        if (queue_item(qin, base + threadIdx.x, len, p)) {
             const float4 ha = wf.hit_a[p];
             const int2 hb = wf.hit_b[p];
             const float4 d4 = wf.ray_d[p];
@@ -50,7 +50,8 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
                         res = mk3(col.x * r, col.y * r, col.z * r);
                     }
                 }
-                wf.result[p] = make_float4(res.x, res.y, res.z, 0.0f);
+                wf.total[p] = make_float4(res.x, res.y, res.z, 0.0f);
+                wf.attenu[p] = make_float4(0.0f, 0.0f, 0.0f, tag_ended);
             } else {
                 // a fresh path starts with total = 0 and attenuation 0.8 (tp/montecarlo.frag:105-107)
                 f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
@@ -69,15 +70,17 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
                 const float4 col = __ldg(S.color + hb.x);
                 BounceOut bo = bounce<FAST>(O, D, N, P, mat, col, attenu, total, seed, prm.refract_ind);
                 if (bo.kind == 0) {
-                    wf.result[p] = make_float4(total.x, total.y, total.z, 0.0f);
+                    wf.total[p] = make_float4(total.x, total.y, total.z, 0.0f);
+                    wf.attenu[p] = make_float4(0.0f, 0.0f, 0.0f, tag_ended);
                 } else if (last_bounce) {
                     // a path still alive after the last iteration returns vec3(0) (tp/montecarlo.frag:178)
-                    wf.result[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    wf.total[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+                    wf.attenu[p] = make_float4(0.0f, 0.0f, 0.0f, tag_ended);
                 } else {
                     const uint32_t nd = n_draws + draws_between(seed0, seed);
                     wf.ray_o[p] = make_float4(bo.nO.x, bo.nO.y, bo.nO.z, 0.0f);
                     wf.ray_d[p] = make_float4(bo.nD.x, bo.nD.y, bo.nD.z, __uint_as_float(nd));
-                    wf.attenu[p] = make_float4(bo.new_att.x, bo.new_att.y, bo.new_att.z, 0.0f);
+                    wf.attenu[p] = make_float4(bo.new_att.x, bo.new_att.y, bo.new_att.z, tag_alive);
                     wf.total[p] = make_float4(total.x, total.y, total.z, 0.0f);
                     if (bo.kind == 2) {
                         wf.keep_n[p] = make_float4(N.x, N.y, N.z, 0.0f);
@@ -87,9 +90,9 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
                 }
             }
         }
-        if (next) {  // block-uniform
-            block_append(qa_next, slot, kind != 0u, p, next, n_next);
-            block_append(qa_int, slot, kind == 2u, p, interior, n_interior);
+        if (next.items) {
+            warp_append(&s_count[0], next, kind != 0u, p);
+            warp_append(&s_count[1], interior, kind == 2u, p);
         }
     }
     if (seg_counter) {
@@ -97,21 +100,27 @@ __global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wav
         for (int off = 16; off > 0; off >>= 1) my_segments += __shfl_down_sync(0xffffffffu, my_segments, off);
         if (lane == 0 && my_segments) atomicAdd(seg_counter, (unsigned long long)my_segments);
     }
+    if (next.items) {
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            next.counts[blockIdx.x] = s_count[0];
+            interior.counts[blockIdx.x] = s_count[1];
+        }
+    }
 }
 
-void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueSet& q,
-                  bool first_bounce, bool last_bounce, int first_pass, uint32_t npix, bool fast_math) {
-    uint64_t n = q.n_cur ? 0xffffffffull : q.n_cur_host;
-    int grid = grid_for(lc, n, 8);
-    uint32_t* next = last_bounce ? nullptr : q.next;
+void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin,
+                  const QueueOut& next, const QueueOut& interior, bool first_bounce, bool last_bounce, int first_pass,
+                  uint32_t npix, bool fast_math, unsigned long long* seg_counter) {
+    const QueueOut none{nullptr, nullptr, 0};
+    const QueueOut& nx = last_bounce ? none : next;
+    const QueueOut& in = last_bounce ? none : interior;
     if (fast_math)
-        k_shade<true><<<grid, kBlock, 0, lc.stream>>>(S, prm, wf, q.cur, q.n_cur, q.n_cur_host, next, q.n_next, q.interior,
-                                                      q.n_interior, first_bounce ? 1 : 0, last_bounce ? 1 : 0, first_pass, npix,
-                                                      q.seg_counter);
+        k_shade<true><<<lc.grid, kBlock, 0, lc.stream>>>(S, prm, wf, qin, nx, in, first_bounce ? 1 : 0, last_bounce ? 1 : 0,
+                                                         first_pass, npix, seg_counter);
     else
-        k_shade<false><<<grid, kBlock, 0, lc.stream>>>(S, prm, wf, q.cur, q.n_cur, q.n_cur_host, next, q.n_next, q.interior,
-                                                       q.n_interior, first_bounce ? 1 : 0, last_bounce ? 1 : 0, first_pass, npix,
-                                                       q.seg_counter);
+        k_shade<false><<<lc.grid, kBlock, 0, lc.stream>>>(S, prm, wf, qin, nx, in, first_bounce ? 1 : 0, last_bounce ? 1 : 0,
+                                                          first_pass, npix, seg_counter);
     ++g_launches;
 }
 
@@ -120,12 +129,11 @@ void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, 
 // interior ray has been traced; take N,P of that hit (or keep the entry hit's
 // N,P when nothing was hit: intersection_info writes nothing for shape -1) and
 // leave through refract(D, -N, 1/refract_ind).
-__global__ void __launch_bounds__(kBlock) k_shade_exit(DevScene S, DevParams prm, Wavefront wf,
-                                                        const uint32_t* __restrict__ queue,
-                                                        const uint32_t* __restrict__ n_dev) {
-    const uint32_t n = *n_dev;
-    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        const uint32_t p = queue[i];
+__global__ void __launch_bounds__(kBlock) k_shade_exit(DevScene S, DevParams prm, Wavefront wf, QueueIn qin) {
+    const uint32_t len = queue_len(qin);
+    for (uint32_t i = threadIdx.x; i < len; i += kBlock) {
+        uint32_t p;
+        if (!queue_item(qin, i, len, p)) continue;
         const float4 ha = wf.hit_a[p];
         const int2 hb = wf.hit_b[p];
         const float4 d4 = wf.ray_d[p];
@@ -139,21 +147,40 @@ __global__ void __launch_bounds__(kBlock) k_shade_exit(DevScene S, DevParams prm
     }
 }
 
-void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const uint32_t* queue,
-                       const uint32_t* n_dev) {
-    k_shade_exit<<<grid_for(lc, 0xffffffffull, 8), kBlock, 0, lc.stream>>>(S, prm, wf, queue, n_dev);
+void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin) {
+    k_shade_exit<<<lc.grid, kBlock, 0, lc.stream>>>(S, prm, wf, qin);
     ++g_launches;
 }
 
 // --------------------------------------------------------------- accumulate
 // glBlendFunc(GL_ONE, GL_ONE) into the RGB32F target, one draw per pass in pass
 // order (montecarlo.cpp:450-466): accum = ((accum + r0) + r1) + ...
+// The value random_path returns is read off the path's final state: `total` when the path ended
+// in k_shade (emissive hit, absorbed, bounce limit), else the ray it was left with escaped and the
+// fake sky applies (tp/montecarlo.frag:118-119) with the path's total and attenuation -- the
+// initial 0 and 0.8 (:105-107) if it was never shaded in this batch.
 __global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __restrict__ accum, uint32_t npix,
-                                                        int n_passes) {
+                                                        int n_passes, uint32_t batch) {
     for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
         float4 a = accum[pix];
         for (int k = 0; k < n_passes; ++k) {
-            float4 r = wf.result[uint64_t(k) * npix + pix];
+            const uint64_t p = uint64_t(k) * npix + pix;
+            const float4 a4 = wf.attenu[p];
+            const uint32_t tag = __float_as_uint(a4.w);
+            f3 r;
+            if (tag == 2u * batch + 1u) {
+                const float4 t4 = wf.total[p];
+                r = mk3(t4.x, t4.y, t4.z);
+            } else {
+                f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
+                if (tag == 2u * batch) {
+                    const float4 t4 = wf.total[p];
+                    total = mk3(t4.x, t4.y, t4.z);
+                    attenu = mk3(a4.x, a4.y, a4.z);
+                }
+                const float4 d4 = wf.ray_d[p];
+                r = sky(total, attenu, mk3(d4.x, d4.y, d4.z));
+            }
             a.x += r.x;
             a.y += r.y;
             a.z += r.z;
@@ -162,8 +189,8 @@ __global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __r
     }
 }
 
-void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes) {
-    k_accumulate<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(wf, accum, npix, n_passes);
+void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes, uint32_t batch) {
+    k_accumulate<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(wf, accum, npix, n_passes, batch);
     ++g_launches;
 }
 

@@ -89,6 +89,7 @@ struct DevScene {
     int32_t top_depth;
     int32_t n_prims;
     int32_t n_meshes;
+    int32_t persistent;        // 1: tree scenes are traced by persistent warps (MCPT_OPT_PERSISTENT)
     // shared-memory staging plan (in units of DevNode / DevPrim)
     int32_t smem_top_nodes;    // first N top-level nodes staged
     int32_t smem_prims;        // first N primitive records staged
@@ -116,6 +117,7 @@ struct DevParams {
     float date;
     int32_t flat_face;
     int32_t mode;
+    uint32_t batch;    // generation of the batch being traced (path tags, see Wavefront::attenu)
 };
 
 // SoA wavefront state, one entry per path slot
@@ -124,11 +126,11 @@ struct Wavefront {
     float4* ray_d;     // direction.xyz, w = number of RNG draws the path has consumed (uint bits)
     float4* hit_a;     // pl.xyz, dist
     int2* hit_b;       // prim, sub
-    float4* attenu;    // attenuation.xyz
+    float4* attenu;    // attenuation.xyz, w = path tag (uint bits): 2*batch: alive, 2*batch + 1: ended, the value
+                       // random_path returns is `total`; anything else: never shaded in this batch
     float4* total;     // radiance gathered so far .xyz
     float4* keep_n;    // N of the entry hit (interior rays)
     float4* keep_p;    // P of the entry hit (interior rays)
-    float4* result;    // value returned by random_path
 };
 
 }  // namespace mcpt

@@ -165,3 +165,25 @@ def test_queue_order_does_not_change_the_image(ctx, kind, bounces):
         assert np.array_equal(runs[0][0], img)
         assert st["rays"] == runs[0][1]["rays"] and st["segments"] == runs[0][1]["segments"]
     assert runs[0][1]["rays"] > runs[0][1]["segments"] > 0
+
+
+@pytest.mark.parametrize("kind,kw", [(3, {}), (7, {}), ("c5", {}), ("mesh", {"n_meshes": 3, "tris_log2": 10})])
+def test_persistent_warps_do_not_change_the_image(kind, kw):
+    """MCPT_OPT_PERSISTENT changes which lane traces which ray and when, nothing else: sums, ray and
+    segment counts are bit-identical to the one-ray-per-lane kernel."""
+    s, o = both(kind, **kw)
+    iv, ipv = capi.default_camera(192, 108)
+    out = []
+    for persistent in (2, 0):
+        c = Context(0)
+        c.set_option(capi.OPT_PERSISTENT, persistent)
+        c.upload_scene(s)
+        c.resize(192, 108)
+        c.set_camera(iv, ipv)
+        c.set_params(nb_bounces=7, refract_ind=1.5, date=float(DATE))
+        c.render(0, 5)
+        out.append((c.read_accum(), c.stats()))
+        c.close()
+    assert np.array_equal(out[0][0], out[1][0])
+    assert out[0][1]["rays"] == out[1][1]["rays"] and out[0][1]["segments"] == out[1][1]["segments"]
+    assert out[0][0][..., :3].mean() > 0.01
