@@ -89,9 +89,9 @@ enum {
                                       set before mcpt_upload_scene */
     MCPT_OPT_TRAVERSE_OCC = 7,     /* resident 256-thread CTAs per SM the traversal kernel is register-capped
                                       for: 2 (<=128 regs), 3 (<=80), 4 (<=64); 0 = auto (default) */
-    MCPT_OPT_PERSISTENT = 8        /* persistent traversal warps whose idle lanes fetch new rays: 1 = on scenes with
-                                      meshes (default), 2 = on every scene walked through the tree, 0 = never
-                                      (one ray per lane per tile). Set before mcpt_upload_scene. Same results. */
+    MCPT_OPT_PERSISTENT = 8        /* 1 = scenes walked through the tree (> 16 primitives, or meshes) are traced by
+                                      persistent warps whose idle lanes fetch new rays (default), 0 = one ray per
+                                      lane per tile. Set before mcpt_upload_scene. Same results. */
 };
 
 /* wavefront stages, in launch order inside one bounce */

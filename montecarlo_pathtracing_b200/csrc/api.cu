@@ -10,6 +10,7 @@
 
 #include <algorithm>
 #include <cfloat>
+#include <climits>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -126,7 +127,9 @@ void free_all(std::vector<void*>& v) {
 // of 256 threads per SM); the tree and mesh walks spill below their natural 80 / 103 registers.
 LaunchCfg lcfg(const mcpt_ctx* c) {
     int occ = c->opt_traverse_occ;
-    if (occ == 0) occ = (c->have_scene && c->scene.n_flat > 0) ? 4 : 3;  // measured: tree scenes +8..10 % at 3 over 2
+    // measured: flat walk and persistent warps are best at 4 (latency hiding beats the spills of the
+    // 64-register cap: +7..10 % over 3); the one-ray-per-lane tree walk at 3
+    if (occ == 0) occ = (c->have_scene && (c->scene.n_flat > 0 || c->scene.persistent)) ? 4 : 3;
     return LaunchCfg{c->sm_count, c->stream, occ};
 }
 
@@ -272,7 +275,7 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
             return MCPT_OK;
         case MCPT_OPT_FAST_MATH: c->opt_fast_math = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_MESH_BVH: c->opt_mesh_bvh = value ? 1 : 0; return MCPT_OK;
-        case MCPT_OPT_PERSISTENT: c->opt_persistent = (value >= 0 && value <= 2) ? int(value) : 1; return MCPT_OK;
+        case MCPT_OPT_PERSISTENT: c->opt_persistent = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_PROFILE_STAGES: c->opt_profile = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_COUNT_WORK: c->opt_count_work = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;

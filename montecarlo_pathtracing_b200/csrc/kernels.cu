@@ -177,19 +177,25 @@ __device__ __forceinline__ void deliver(const Wavefront& wf, const QueueOut& hit
 // kRefillLanes lanes of the warp are idle, the idle lanes take the next entries of the region (one
 // shared-memory atomic per refill). Incoherent rays -- a few lanes deep inside a mesh while the
 // others have left the scene -- no longer hold a whole warp: measured 4.4 of 32 lanes active in
-// late bounces of the mesh workload with one ray per lane per tile.
+// late bounces of the mesh workload with one ray per lane per tile. Every iteration each lane does
+// the one step its ray needs (traverse.cuh); node steps of both levels share one code path.
+// (Measured and dropped: running only the most wanted kind of step per iteration -- fewer
+// instructions but fewer loads in flight, -14 %; holding the primitive step back until several lanes
+// want it -- no gain; one queue region per warp instead of per CTA -- no atomics at all and ordered
+// survivors, but warps of a CTA finish at different times, -4 % at C2.)
 constexpr int kRefillLanes = 8;
 
 template <bool COUNT, bool MESHES>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
-                                                    uint32_t len, const QueueOut& hitq, uint32_t* s_next,
-                                                    uint32_t* s_hits, Work& wk) {
-    int stack_node[MESHES ? kLbvhStack : 1];
-    float stack_t[MESHES ? kLbvhStack : 1];
+                                                    uint32_t len, const QueueOut& hitq, uint32_t* s_next, uint32_t* s_hits,
+                                                    Work& wk) {
+    int stack_tok[MESHES ? kWalkStack : 32];
+    float stack_t[MESHES ? kWalkStack : 32];
     float wsave[6];
     WalkState w;
-    w.k = 0u;
+    w.done = true;
     w.mesh_prim = -1;
+    w.cur = 0;
     const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
     bool has_ray = false, exhausted = false;
     uint32_t p = 0;
@@ -202,7 +208,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
                 first = __shfl_sync(0xffffffffu, first, 0);
                 if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
                     const float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
-                    walk_begin(w, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+                    walk_begin(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
                     has_ray = true;
                 }
                 exhausted = first + __popc(idle) >= len;
@@ -210,12 +216,18 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
                 break;
             }
         }
-        bool finished = false;
-        if (has_ray) finished = walk_step<COUNT, MESHES>(w, wk, S, sm, stack_node, stack_t, wsave);
-        if (__any_sync(0xffffffffu, finished)) {
-            deliver(wf, hitq, s_hits, p, finished, w.best);
-            if (finished) has_ray = false;
+        const int kind = has_ray ? walk_kind(w) : -1;
+        // finished rays: deliver and free the lane
+        if (__any_sync(0xffffffffu, kind == WALK_DONE)) {
+            deliver(wf, hitq, s_hits, p, kind == WALK_DONE, w.best);
+            if (kind == WALK_DONE) has_ray = false;
         }
+        if (kind == WALK_NODE)
+            walk_node<COUNT>(w, wk, S, stack_tok, stack_t, wsave);
+        else if (MESHES && kind == WALK_TRI)
+            walk_tri<COUNT>(w, wk, S, sm, stack_tok, stack_t, wsave);
+        else if (kind == WALK_PRIM)
+            walk_prim<COUNT, MESHES>(w, wk, S, sm, stack_tok, stack_t, wsave);
     }
 }
 

@@ -90,6 +90,7 @@ struct DevScene {
     int32_t n_prims;
     int32_t n_meshes;
     int32_t persistent;        // 1: tree scenes are traced by persistent warps (MCPT_OPT_PERSISTENT)
+    const DevNode2* top2;      // the top-level tree in two-children node format (persistent warps), root = node 0
     // shared-memory staging plan (in units of DevNode / DevPrim)
     int32_t smem_top_nodes;    // first N top-level nodes staged
     int32_t smem_prims;        // first N primitive records staged

@@ -19,6 +19,8 @@
 //     of the reference would accept, and candidates are ranked by the exact
 //     world-space distance (intersect.cuh).
 #pragma once
+#include <climits>
+
 #include "intersect.cuh"
 
 namespace mcpt {
@@ -301,40 +303,50 @@ MCPT_DEV void scene_walk(Work& wk, const DevScene& S, const SmemScene& sm, f3 O,
 
 
 // ------------------------------------------------------------- resumable walk
-// The same closest-hit search as scene_walk + mesh_walk_lbvh, cut into single steps so that a
-// persistent warp can keep every lane busy: a lane whose ray is finished takes the next ray of the
-// CTA's queue region while its neighbours go on walking (k_traverse, PERSIST). One call of
-// walk_step does ONE of: a top-level node test (+ the analytic primitive test at a leaf, or the
-// entry into a mesh), a mesh node test (both children), or one triangle of a mesh leaf.
-// Entering a mesh switches the culling frame (idir, od, tmax) to mesh-local space and parks the
-// world frame in `wsave`; leaving restores it. The top-level cursor is advanced BEFORE the mesh is
-// entered, so leaving a mesh simply resumes the top-level walk.
+// The closest-hit search cut into single steps, for persistent warps (k_traverse, PERSIST): a lane
+// whose ray is finished takes the next ray of its warp's queue region while its neighbours go on
+// walking. To keep the lanes of a warp in the same instruction stream as often as possible, BOTH
+// levels of the scene are walked by the same node step: the top-level tree is re-packed at upload
+// into the 64-byte two-children node format of the mesh trees (DevScene::top2), and one explicit
+// stack serves both levels. Entering a mesh pushes a marker, switches the culling frame (idir, od,
+// tmax) to mesh-local space and parks the world frame in `wsave`; popping the marker restores it.
+// Three kinds of step remain:
+//   WALK_NODE  one node of either level: both child boxes, nearer first, farther pushed with its
+//              entry parameter (dropped when popped if a closer hit is known by then)
+//   WALK_TRI   one triangle of a mesh leaf
+//   WALK_PRIM  a top-level leaf: the analytic intersector, or the entry into a mesh
+// Candidates go through the same arithmetic and the same total order (distance, then the
+// reference's visit order) as in scene_walk, so the result is the same record bit for bit.
+enum { WALK_DONE = 0, WALK_NODE = 1, WALK_TRI = 2, WALK_PRIM = 3 };
+
+constexpr int kTokEmpty = INT_MIN;         // child slot without content
+constexpr int kTokExitMesh = INT_MIN + 1;  // stack marker: back to the world frame
+constexpr int kWalkStack = 30 + 1 + kLbvhStack;
+
 struct WalkState {
     f3 O, D;         // world ray as given (D not normalised)
     float slack;
     f3 idir, od;     // culling frame
     float tmax;
-    uint32_t k;      // top-level heap index, 0: nothing to walk (degenerate direction)
-    uint32_t trail, neg;
-    int level, axis;
-    bool top_done;
+    const DevNode2* nodes;  // node array of the current frame
+    int cur;         // token: >= 0 node, < 0 leaf (~primitive in the world frame, ~leaf inside a mesh)
+    int sp;
+    bool done;
     int mesh_prim;   // >= 0 while inside that mesh primitive
-    int cur, sp, tri_j;
+    int tri_j;
     f3 Oi, Di;
     float inv_scale;
     int tslot;
-    const DevNode2* nodes2;
     const DevTri* tris2;
     Best best;
 };
 
-MCPT_DEV void walk_begin(WalkState& w, f3 O, f3 D) {
+MCPT_DEV void walk_begin(WalkState& w, const DevScene& S, f3 O, f3 D) {
     best_reset(w.best);
     w.O = O;
     w.D = D;
     w.mesh_prim = -1;
-    w.top_done = false;
-    w.k = 0u;
+    w.done = true;
     const float len = sqrtf(D.x * D.x + D.y * D.y + D.z * D.z);
     if (!(len > 0.0f) || !(len < FLT_MAX)) return;  // zero / NaN / inf direction: nothing is hit
     const float rl = 1.0f / len;
@@ -343,159 +355,141 @@ MCPT_DEV void walk_begin(WalkState& w, f3 O, f3 D) {
     w.od = mk3(-O.x * w.idir.x, -O.y * w.idir.y, -O.z * w.idir.z);
     w.slack = 1e-4f * (fabsf(O.x) + fabsf(O.y) + fabsf(O.z)) + 1e-3f;
     w.tmax = FLT_MAX;
-    w.neg = (dn.x < 0.0f ? 1u : 0u) | (dn.y < 0.0f ? 2u : 0u) | (dn.z < 0.0f ? 4u : 0u);
-    w.k = 1u;
-    w.trail = 0u;
-    w.level = 0;
-    w.axis = 0;
+    w.nodes = S.top2;
+    w.cur = 0;
+    w.sp = 0;
+    w.tri_j = 0;
+    w.done = false;
 }
 
-// move the top-level cursor: into the near child, or to the next pending sibling
-MCPT_DEV void top_advance(WalkState& w, bool descend) {
-    if (descend) {
-        w.k = 2u * w.k + ((w.neg >> w.axis) & 1u);
-        w.trail = (w.trail << 1) | 1u;
-        ++w.level;
-        w.axis = (w.axis == 2) ? 0 : w.axis + 1;
-        return;
-    }
-    while (w.level > 0 && !(w.trail & 1u)) {
-        w.trail >>= 1;
-        w.k >>= 1;
-        --w.level;
-        w.axis = (w.axis == 0) ? 2 : w.axis - 1;
-    }
-    if (w.level == 0) {
-        w.top_done = true;
-        return;
-    }
-    w.k ^= 1u;
-    w.trail &= ~1u;
+// the step this ray needs next; WALK_DONE: finished (w.best holds the result)
+MCPT_DEV int walk_kind(const WalkState& w) {
+    if (w.done) return WALK_DONE;
+    if (w.cur >= 0) return WALK_NODE;
+    return w.mesh_prim >= 0 ? WALK_TRI : WALK_PRIM;
 }
 
-// returns true when the ray is finished (w.best holds the result)
-template <bool COUNT, bool MESHES>
-MCPT_DEV bool walk_step(WalkState& w, Work& wk, const DevScene& S, const SmemScene& sm, int* stack_node, float* stack_t,
-                        float* wsave) {
-    if (w.k == 0u) return true;
-    if (MESHES && w.mesh_prim >= 0) {
-        bool pop = false;
-        if (w.cur >= 0) {
-            const DevNode2* np = w.nodes2 + w.cur;
-            const float4 lo0 = __ldg(&np->lo0), hi0 = __ldg(&np->hi0), lo1 = __ldg(&np->lo1), hi1 = __ldg(&np->hi1);
-            float t0, t1;
-            const bool h0 = slab_entry(lo0, hi0, w.idir, w.od, w.tmax, t0);
-            const bool h1 = slab_entry(lo1, hi1, w.idir, w.od, w.tmax, t1);
-            if (COUNT) wk.boxes += 2;
-            const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(hi0.w);
-            if (h0 && h1) {
-                const bool swap = t1 < t0;
-                stack_node[w.sp] = swap ? c0 : c1;
-                stack_t[w.sp] = swap ? t0 : t1;
-                ++w.sp;
-                w.cur = swap ? c1 : c0;
-            } else if (h0 || h1) {
-                w.cur = h0 ? c0 : c1;
-            } else {
-                pop = true;
-            }
+// next pending subtree that can still hold a closer hit; leaves the mesh at its marker
+MCPT_DEV void walk_pop(WalkState& w, const DevScene& S, const int* stack_tok, const float* stack_t, const float* wsave) {
+    while (true) {
+        if (w.sp == 0) {
+            w.done = true;
+            return;
+        }
+        --w.sp;
+        const int tok = stack_tok[w.sp];
+        if (tok == kTokExitMesh) {
+            w.mesh_prim = -1;
+            w.nodes = S.top2;
+            w.idir = mk3(wsave[0], wsave[1], wsave[2]);
+            w.od = mk3(wsave[3], wsave[4], wsave[5]);
+            w.tmax = (w.best.h.prim >= 0) ? (w.best.h.dist * 1.0001f + w.slack) : FLT_MAX;
+            continue;
+        }
+        if (stack_t[w.sp] <= w.tmax) {
+            w.cur = tok;
             w.tri_j = 0;
-        } else {
-            const DevTri* tp = w.tris2 + kMeshLeafTris * (~w.cur) + w.tri_j;
-            const float4 ta = __ldg(&tp->a);
-            const int tri = __float_as_int(ta.w);
-            if (tri >= 0) {
-                if (COUNT) ++wk.tris;
-                const float4 tb = __ldg(&tp->b), tc = __ldg(&tp->c);
-                float a;
-                if (triangle_param(mk3(ta.x, ta.y, ta.z), mk3(tb.x, tb.y, tb.z), mk3(tc.x, tc.y, tc.z), w.Oi, w.Di, a)) {
-                    const DevPrim* pp = (w.mesh_prim < S.smem_prims) ? (sm.prims + w.mesh_prim) : (S.prims + w.mesh_prim);
-                    Aff fwd;
-                    fwd.r0 = pp->fwd.r0;
-                    fwd.r1 = pp->fwd.r1;
-                    fwd.r2 = pp->fwd.r2;
-                    if (offer_at(w.best, fwd, w.Oi, w.Di, a, w.O, w.mesh_prim, tri, w.tslot, __float_as_int(tb.w)))
-                        w.tmax = (w.best.h.dist * 1.0001f + w.slack) * w.inv_scale;
-                }
-            }
-            if (++w.tri_j == kMeshLeafTris) pop = true;
+            return;
         }
-        if (pop) {
-            // the nearest pending subtree that can still hold a closer hit, or out of the mesh
-            while (true) {
-                if (w.sp == 0) {
-                    w.mesh_prim = -1;
-                    w.idir = mk3(wsave[0], wsave[1], wsave[2]);
-                    w.od = mk3(wsave[3], wsave[4], wsave[5]);
-                    w.tmax = (w.best.h.prim >= 0) ? (w.best.h.dist * 1.0001f + w.slack) : FLT_MAX;
-                    return w.top_done;
-                }
-                --w.sp;
-                if (stack_t[w.sp] <= w.tmax) {
-                    w.cur = stack_node[w.sp];
-                    w.tri_j = 0;
-                    break;
-                }
-            }
-        }
-        return false;
     }
-    // ---- top-level step
-    const uint32_t first_leaf = 1u << S.top_depth;
-    const DevNode n = (w.k <= uint32_t(S.smem_top_nodes)) ? load_node_smem(sm.top_nodes + w.k) : load_node(S.top_nodes + w.k);
-    bool inside = slab(n, w.idir, w.od, w.tmax);
-    if (COUNT) ++wk.boxes;
-    if (inside && w.k >= first_leaf) {
-        inside = false;
-        const int pid = __float_as_int(n.lo.w);
-        if (pid >= 0) {
-            const DevPrim* pp = (pid < S.smem_prims) ? (sm.prims + pid) : (S.prims + pid);
-            if (MESHES && pp->type == MCPT_PRIM_MESH) {
-                top_advance(w, false);
-                // intersect_prim + Mesh_intersect prologue (raytracer_func.frag:681-705)
-                Aff inv, fwd;
-                inv.r0 = pp->inv.r0;
-                inv.r1 = pp->inv.r1;
-                inv.r2 = pp->inv.r2;
-                fwd.r0 = pp->fwd.r0;
-                fwd.r1 = pp->fwd.r1;
-                fwd.r2 = pp->fwd.r2;
-                if (COUNT) ++wk.prims;
-                const f3 Oi = xform_point(inv, w.O);
-                const f3 Di = normalize3(xform_vector(inv, w.D));
-                const f3 wd = mk3(fwd.r0.x * Di.x + fwd.r0.y * Di.y + fwd.r0.z * Di.z,
-                                  fwd.r1.x * Di.x + fwd.r1.y * Di.y + fwd.r1.z * Di.z,
-                                  fwd.r2.x * Di.x + fwd.r2.y * Di.y + fwd.r2.z * Di.z);
-                const float scale = sqrtf(wd.x * wd.x + wd.y * wd.y + wd.z * wd.z);
-                if (!(scale > 0.0f)) return w.top_done;  // zero or NaN direction: the shader finds nothing either
-                const DevMesh& M = S.meshes[pp->mesh];
-                w.nodes2 = M.nodes2;
-                w.tris2 = M.tris2;
-                w.mesh_prim = pid;
-                w.tslot = pp->slot;
-                w.Oi = Oi;
-                w.Di = Di;
-                w.inv_scale = 1.0f / scale;
-                wsave[0] = w.idir.x;
-                wsave[1] = w.idir.y;
-                wsave[2] = w.idir.z;
-                wsave[3] = w.od.x;
-                wsave[4] = w.od.y;
-                wsave[5] = w.od.z;
-                w.idir = safe_rcp3(Di);
-                w.od = mk3(-Oi.x * w.idir.x, -Oi.y * w.idir.y, -Oi.z * w.idir.z);
+}
+
+template <bool COUNT>
+MCPT_DEV void walk_node(WalkState& w, Work& wk, const DevScene& S, int* stack_tok, float* stack_t, const float* wsave) {
+    const DevNode2* np = w.nodes + w.cur;
+    const float4 lo0 = __ldg(&np->lo0), hi0 = __ldg(&np->hi0), lo1 = __ldg(&np->lo1), hi1 = __ldg(&np->hi1);
+    const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(hi0.w);
+    float t0, t1;
+    const bool h0 = slab_entry(lo0, hi0, w.idir, w.od, w.tmax, t0) && c0 != kTokEmpty;
+    const bool h1 = slab_entry(lo1, hi1, w.idir, w.od, w.tmax, t1) && c1 != kTokEmpty;
+    if (COUNT) wk.boxes += 2;
+    w.tri_j = 0;
+    if (h0 && h1) {
+        const bool swap = t1 < t0;
+        stack_tok[w.sp] = swap ? c0 : c1;
+        stack_t[w.sp] = swap ? t0 : t1;
+        ++w.sp;
+        w.cur = swap ? c1 : c0;
+    } else if (h0 || h1) {
+        w.cur = h0 ? c0 : c1;
+    } else {
+        walk_pop(w, S, stack_tok, stack_t, wsave);
+    }
+}
+
+template <bool COUNT>
+MCPT_DEV void walk_tri(WalkState& w, Work& wk, const DevScene& S, const SmemScene& sm, const int* stack_tok, const float* stack_t,
+                       const float* wsave) {
+    const DevTri* tp = w.tris2 + kMeshLeafTris * (~w.cur) + w.tri_j;
+    const float4 ta = __ldg(&tp->a);
+    const int tri = __float_as_int(ta.w);
+    if (tri >= 0) {
+        if (COUNT) ++wk.tris;
+        const float4 tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+        float a;
+        if (triangle_param(mk3(ta.x, ta.y, ta.z), mk3(tb.x, tb.y, tb.z), mk3(tc.x, tc.y, tc.z), w.Oi, w.Di, a)) {
+            const DevPrim* pp = (w.mesh_prim < S.smem_prims) ? (sm.prims + w.mesh_prim) : (S.prims + w.mesh_prim);
+            Aff fwd;
+            fwd.r0 = pp->fwd.r0;
+            fwd.r1 = pp->fwd.r1;
+            fwd.r2 = pp->fwd.r2;
+            if (offer_at(w.best, fwd, w.Oi, w.Di, a, w.O, w.mesh_prim, tri, w.tslot, __float_as_int(tb.w)))
                 w.tmax = (w.best.h.dist * 1.0001f + w.slack) * w.inv_scale;
-                w.cur = 0;
-                w.sp = 0;
-                w.tri_j = 0;
-                return false;
-            }
-            prim_test<COUNT, false>(wk, S, sm, pid, w.O, w.D, w.slack, w.best);
-            if (w.best.h.prim >= 0) w.tmax = w.best.h.dist * 1.0001f + w.slack;
         }
     }
-    top_advance(w, inside);
-    return w.top_done;
+    if (++w.tri_j == kMeshLeafTris) walk_pop(w, S, stack_tok, stack_t, wsave);
+}
+
+template <bool COUNT, bool MESHES>
+MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemScene& sm, int* stack_tok, float* stack_t,
+                        float* wsave) {
+    const int pid = ~w.cur;
+    const DevPrim* pp = (pid < S.smem_prims) ? (sm.prims + pid) : (S.prims + pid);
+    if (MESHES && pp->type == MCPT_PRIM_MESH) {
+        // intersect_prim + Mesh_intersect prologue (raytracer_func.frag:681-705)
+        Aff inv, fwd;
+        inv.r0 = pp->inv.r0;
+        inv.r1 = pp->inv.r1;
+        inv.r2 = pp->inv.r2;
+        fwd.r0 = pp->fwd.r0;
+        fwd.r1 = pp->fwd.r1;
+        fwd.r2 = pp->fwd.r2;
+        if (COUNT) ++wk.prims;
+        const f3 Oi = xform_point(inv, w.O);
+        const f3 Di = normalize3(xform_vector(inv, w.D));
+        const f3 wd = mk3(fwd.r0.x * Di.x + fwd.r0.y * Di.y + fwd.r0.z * Di.z, fwd.r1.x * Di.x + fwd.r1.y * Di.y + fwd.r1.z * Di.z,
+                          fwd.r2.x * Di.x + fwd.r2.y * Di.y + fwd.r2.z * Di.z);
+        const float scale = sqrtf(wd.x * wd.x + wd.y * wd.y + wd.z * wd.z);
+        if (scale > 0.0f) {  // else zero or NaN direction: the shader finds nothing either
+            const DevMesh& M = S.meshes[pp->mesh];
+            stack_tok[w.sp] = kTokExitMesh;
+            stack_t[w.sp] = 0.0f;
+            ++w.sp;
+            w.nodes = M.nodes2;
+            w.tris2 = M.tris2;
+            w.mesh_prim = pid;
+            w.tslot = pp->slot;
+            w.Oi = Oi;
+            w.Di = Di;
+            w.inv_scale = 1.0f / scale;
+            wsave[0] = w.idir.x;
+            wsave[1] = w.idir.y;
+            wsave[2] = w.idir.z;
+            wsave[3] = w.od.x;
+            wsave[4] = w.od.y;
+            wsave[5] = w.od.z;
+            w.idir = safe_rcp3(Di);
+            w.od = mk3(-Oi.x * w.idir.x, -Oi.y * w.idir.y, -Oi.z * w.idir.z);
+            w.tmax = (w.best.h.dist * 1.0001f + w.slack) * w.inv_scale;
+            w.cur = 0;
+            w.tri_j = 0;
+            return;
+        }
+    } else {
+        prim_test<COUNT, false>(wk, S, sm, pid, w.O, w.D, w.slack, w.best);
+        if (w.best.h.prim >= 0) w.tmax = w.best.h.dist * 1.0001f + w.slack;
+    }
+    walk_pop(w, S, stack_tok, stack_t, wsave);
 }
 
 // Warp-coherent walk for scenes with a handful of primitives (the reference's box

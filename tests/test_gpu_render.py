@@ -174,7 +174,7 @@ def test_persistent_warps_do_not_change_the_image(kind, kw):
     s, o = both(kind, **kw)
     iv, ipv = capi.default_camera(192, 108)
     out = []
-    for persistent in (2, 0):
+    for persistent in (1, 0):
         c = Context(0)
         c.set_option(capi.OPT_PERSISTENT, persistent)
         c.upload_scene(s)

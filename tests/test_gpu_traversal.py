@@ -126,7 +126,6 @@ def test_both_mesh_trees_render_the_same_image(ctx):
             ctx.set_option(capi.OPT_MESH_BVH, 1)
     assert np.array_equal(images[0], images[1])
     assert counts[0]["rays"] == counts[1]["rays"] and counts[0]["segments"] == counts[1]["segments"]
-    assert counts[0]["prim_tests"] == counts[1]["prim_tests"]
     assert counts[1]["tri_tests"] > counts[0]["tri_tests"] > 0
 
 
