@@ -162,6 +162,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--fast-math", type=int, default=1, help="1 = MUFU sin/cos/log/pow/rsqrt in the bounce sampler (same parity tolerance, tests/test_gpu_golden.py)")
     ap.add_argument("--ppb", type=int, default=0, help="passes per wavefront batch (0 = auto)")
+    ap.add_argument("--refill", type=int, default=0, help="persistent warps: idle lanes that trigger a refill (0 = auto)")
     ap.add_argument("--persistent", type=int, default=1, help="1 = persistent warps with lane refill on tree scenes")
     ap.add_argument("--mesh-bvh", type=int, default=1, help="1 = GPU-built LBVH per mesh, 0 = the uploaded median-split trees")
     ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
@@ -198,6 +199,7 @@ def main():
         ctx.set_option(capi.OPT_TRAVERSE_OCC, args.occ)
     ctx.set_option(capi.OPT_MESH_BVH, args.mesh_bvh)
     ctx.set_option(capi.OPT_PERSISTENT, args.persistent)
+    ctx.set_option(capi.OPT_REFILL_LANES, args.refill)
     ctx.upload_scene(s)
     ctx.resize(w, h)
     # accumulate straight into a torch tensor: it is the NCCL send/recv buffer, no staging copy

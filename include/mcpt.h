@@ -80,8 +80,8 @@ enum {
     MCPT_OPT_PASSES_PER_BATCH = 0, /* passes traced together in one wavefront (default auto) */
     MCPT_OPT_SMEM_STAGING = 1,     /* 1 = stage top BVH levels in shared memory (default 1)  */
     MCPT_OPT_FAST_MATH = 2,        /* 1 = MUFU sin/cos/log/pow in the bounce sampler         */
-    MCPT_OPT_MESH_BVH = 3,         /* 1 = rebuild every mesh tree on the GPU at upload (LBVH, 4-triangle
-                                      leaves; default 1), 0 = walk the uploaded median-split trees;
+    MCPT_OPT_MESH_BVH = 3,         /* 1 = rebuild every mesh tree on the GPU at upload (LBVH, one triangle
+                                      per leaf; default 1), 0 = walk the uploaded median-split trees;
                                       set before mcpt_upload_scene. Hit results are the same.   */
     MCPT_OPT_PROFILE_STAGES = 4,   /* 1 = bracket every stage launch with CUDA events         */
     MCPT_OPT_COUNT_WORK = 5,       /* 1 = traversal kernels count boxes / records / triangles */
@@ -89,9 +89,11 @@ enum {
                                       set before mcpt_upload_scene */
     MCPT_OPT_TRAVERSE_OCC = 7,     /* resident 256-thread CTAs per SM the traversal kernel is register-capped
                                       for: 2 (<=128 regs), 3 (<=80), 4 (<=64); 0 = auto (default) */
-    MCPT_OPT_PERSISTENT = 8        /* 1 = scenes walked through the tree (> 16 primitives, or meshes) are traced by
+    MCPT_OPT_PERSISTENT = 8,       /* 1 = scenes walked through the tree (> 16 primitives, or meshes) are traced by
                                       persistent warps whose idle lanes fetch new rays (default), 0 = one ray per
                                       lane per tile. Set before mcpt_upload_scene. Same results. */
+    MCPT_OPT_REFILL_LANES = 9      /* persistent warps: idle lanes of a warp that trigger a refill from the queue,
+                                      1..32; 0 = auto (8 with meshes, 32 without). Set before mcpt_upload_scene. */
 };
 
 /* wavefront stages, in launch order inside one bounce */

@@ -9,6 +9,7 @@ CUDA device, Context() raises McptError(MCPT_E_NODEVICE).
 from __future__ import annotations
 
 import ctypes as C
+import os
 from pathlib import Path
 
 import numpy as np
@@ -19,7 +20,7 @@ MCPT_OK = 0
 MCPT_E_INVALID, MCPT_E_CUDA, MCPT_E_NODEVICE, MCPT_E_NOMEM, MCPT_E_NCCL, MCPT_E_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 PRIM_MESH, PRIM_SPHERE, PRIM_CUBE, PRIM_CYLINDER, PRIM_CONE, PRIM_ORIENTED_QUAD = range(6)
 DST_HOST_RGB32F, DST_HOST_RGBA8, DST_DEVICE_RGB32F, DST_DEVICE_RGBA8 = range(4)
-OPT_PASSES_PER_BATCH, OPT_SMEM_STAGING, OPT_FAST_MATH, OPT_MESH_BVH, OPT_PROFILE_STAGES, OPT_COUNT_WORK, OPT_FLAT_WALK, OPT_TRAVERSE_OCC, OPT_PERSISTENT = range(9)
+OPT_PASSES_PER_BATCH, OPT_SMEM_STAGING, OPT_FAST_MATH, OPT_MESH_BVH, OPT_PROFILE_STAGES, OPT_COUNT_WORK, OPT_FLAT_WALK, OPT_TRAVERSE_OCC, OPT_PERSISTENT, OPT_REFILL_LANES = range(10)
 STAGE_NAMES = ("raygen", "traverse", "shade", "bvh_build", "traverse_interior", "shade_exit", "accumulate", "resolve")
 
 
@@ -91,7 +92,7 @@ def lib():
     """libmcpt.so; raises if the CUDA extension has not been built (no fallback)."""
     global _lib
     if _lib is None:
-        path = LIB_DIR / "libmcpt.so"
+        path = Path(os.environ.get("MCPT_LIBRARY", LIB_DIR / "libmcpt.so"))  # override: tuning builds only
         if not path.exists():
             raise ImportError(f"{path} is missing: run __graft_entry__.build(); there is no CPU fallback")
         L = C.CDLL(str(path), mode=C.RTLD_GLOBAL)

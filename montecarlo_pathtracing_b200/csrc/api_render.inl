@@ -24,7 +24,7 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
     if (slots > 0x7fffff00ull) return fail(c, MCPT_E_INVALID, "batch of %llu paths is too large", (unsigned long long)slots);
     if (slots > c->wf_capacity) {
         CK(c, cudaStreamSynchronize(c->stream));
-        free_all(c->wf_allocs);
+        free_all(c, c->wf_allocs);
         c->wf_capacity = 0;
         c->counters = nullptr;
         c->counters_len = 0;
@@ -38,13 +38,15 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
             (rc = dev_alloc(c, c->wf_allocs, &c->queue[0], queue_entries(c, slots))) ||
             (rc = dev_alloc(c, c->wf_allocs, &c->queue[1], queue_entries(c, slots))) ||
             (rc = dev_alloc(c, c->wf_allocs, &c->queue[2], queue_entries(c, slots)))) {
-            free_all(c->wf_allocs);
+            free_all(c, c->wf_allocs);
+            trim_cache(c);
             return rc;
         }
         // path tags live in attenu.w: start from a state no batch generation can match
         CK(c, cudaMemsetAsync(w.attenu, 0, sizeof(float4) * slots, c->stream));
         c->batch_gen = 0;
         c->wf_capacity = slots;
+        trim_cache(c);
     }
     (void)bounces;
     const int need = 3 * wavefront_grid_max(c);  // region lengths of the three queues

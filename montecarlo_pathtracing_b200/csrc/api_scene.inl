@@ -41,7 +41,7 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     }
 
     CK(c, cudaStreamSynchronize(c->stream));
-    free_all(c->scene_allocs);
+    free_all(c, c->scene_allocs);
     c->have_scene = false;
     DevScene S{};
 
@@ -121,6 +121,25 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
 
     // ---- meshes
     std::vector<DevMesh> meshes(d->n_meshes);
+    std::vector<void*> build_allocs;  // scratch of the GPU tree builds, parked again at the end
+    struct ParkOnExit {               // ... also on the error returns below
+        mcpt_ctx* c;
+        std::vector<void*>& v;
+        ~ParkOnExit() {
+            if (v.empty()) return;
+            cudaStreamSynchronize(c->stream);
+            free_all(c, v);
+        }
+    } park_build_allocs{c, build_allocs};
+    char* build_ws = nullptr;
+    size_t build_ws_bytes = 0;
+    if (c->opt_mesh_bvh) {
+        for (int m = 0; m < d->n_meshes; ++m) {
+            const int nt = int(d->meshes[m].n_tris);
+            if (nt > 0) build_ws_bytes = std::max(build_ws_bytes, lbvh_workspace_bytes(nt, (nt + kMeshLeafTris - 1) / kMeshLeafTris));
+        }
+        if (build_ws_bytes && (rc = dev_alloc(c, build_allocs, &build_ws, build_ws_bytes))) return rc;
+    }
     for (int m = 0; m < d->n_meshes; ++m) {
         const mcpt_mesh_desc& md = d->meshes[m];
         const int depth = md.bvh.depth;
@@ -153,22 +172,20 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             int32_t* d_slot = nullptr;
             DevNode2* dn2 = nullptr;
             DevTri* dt2 = nullptr;
-            std::vector<void*> tmp_allocs;
-            if ((rc = dev_alloc(c, tmp_allocs, &d_slot, slot_of_tri.size())) ||
+            if ((rc = dev_alloc(c, build_allocs, &d_slot, slot_of_tri.size())) ||
                 (rc = dev_alloc(c, c->scene_allocs, &dn2, size_t(std::max(n_leaves - 1, 1)))) ||
-                (rc = dev_alloc(c, c->scene_allocs, &dt2, size_t(n_leaves) * kMeshLeafTris))) {
-                free_all(tmp_allocs);
+                (rc = dev_alloc(c, c->scene_allocs, &dt2, size_t(n_leaves) * kMeshLeafTris)))
                 return rc;
-            }
-            cudaError_t e = cudaMemcpy(d_slot, slot_of_tri.data(), slot_of_tri.size() * sizeof(int32_t), cudaMemcpyHostToDevice);
+            CK(c, cudaMemcpy(d_slot, slot_of_tri.data(), slot_of_tri.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
             unsigned long long launched = 0;
+            cudaError_t e;
             {
+                // enqueued only: the builds of all meshes share one workspace in stream order
                 StageSpan sp(c, MCPT_STAGE_BVH_BUILD);
-                if (e == cudaSuccess)
-                    e = build_mesh_lbvh(c->stream, dp, di, int(md.n_tris), d_slot, lo, hi, dn2, dt2, n_leaves, &launched);
+                e = build_mesh_lbvh(c->stream, dp, di, int(md.n_tris), d_slot, lo, hi, dn2, dt2, n_leaves, build_ws, build_ws_bytes,
+                                    &launched);
             }
             add_launches(launched);
-            free_all(tmp_allocs);
             CK(c, e);
             M.nodes2 = dn2;
             M.tris2 = dt2;
@@ -222,7 +239,10 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             S.smem_mesh_nodes = off;
         }
     }
-    if (!flat.empty()) S.smem_top_nodes = int(flat.size()) - 1;  // the flat list takes the tree's place (always staged)
+    if (!flat.empty()) {
+        S.smem_top_nodes = int(flat.size()) - 1;  // the flat list takes the tree's place (always staged) ...
+        S.smem_prims = d->n_prims;                // ... and so do all (<= 16) primitive records
+    }
     S.smem_bytes = int(sizeof(DevNode)) * (S.smem_top_nodes + 1 + S.smem_mesh_nodes) + int(sizeof(DevPrim)) * S.smem_prims;
 
     DevNode* d_top = nullptr;
@@ -252,6 +272,12 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     // persistent warps need every mesh tree in the GPU-built form
     // (measured: 1.8x on the 1 M-triangle workload, +20 % on a tree of 122 analytic primitives)
     S.persistent = (c->opt_persistent && flat.empty() && (d->n_meshes == 0 || c->opt_mesh_bvh)) ? 1 : 0;
+    S.refill_lanes = c->opt_refill_lanes > 0 ? c->opt_refill_lanes : (d->n_meshes > 0 ? 8 : 32);
+    if (!build_allocs.empty()) {
+        CK(c, cudaStreamSynchronize(c->stream));  // the tree builds are done: their scratch can go
+        free_all(c, build_allocs);
+    }
+    trim_cache(c);
     c->scene = S;
     c->have_scene = true;
     return MCPT_OK;

@@ -7,8 +7,8 @@
 // library is free to traverse a better one. This file builds an LBVH on the device at upload time:
 //   1. Morton code (30 bit) of every triangle centroid inside the mesh box          k_morton
 //   2. radix sort of (code, triangle)                                               cub::DeviceRadixSort
-//   3. leaves = runs of 4 consecutive triangles in Morton order, stored as 4 DevTri slots with the
-//      triangle id and the reference's leaf slot (tie-break rank)                    k_leaves
+//   3. leaves = runs of kMeshLeafTris (1) consecutive triangles in Morton order, stored as DevTri
+//      slots with the triangle id and the reference's leaf slot (tie-break rank)     k_leaves
 //   4. Karras 2012 radix-tree hierarchy over the leaves, duplicates split by index   k_hierarchy
 //   5. bottom-up box fit with one atomic arrival counter per node; the second arrival writes the
 //      64-byte node {child boxes, child tokens}                                      k_fit
@@ -53,7 +53,7 @@ __global__ void k_morton(const float* __restrict__ pos, const uint32_t* __restri
     vals[t] = uint32_t(t);
 }
 
-// leaf c holds sorted triangles [4c, 4c+4); writes the DevTri slots, the leaf box and the leaf key
+// leaf c holds sorted triangles [L*c, L*c + L), L = kMeshLeafTris; writes the DevTri slots, the leaf box and the leaf key
 __global__ void k_leaves(const float* __restrict__ pos, const uint32_t* __restrict__ idx, const int32_t* __restrict__ slot_of_tri,
                          const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_tris, int n_tris,
                          int n_leaves, DevTri* __restrict__ tris, float* __restrict__ box_lo, float* __restrict__ box_hi,
@@ -200,67 +200,80 @@ __global__ void k_single(const float* __restrict__ box_lo, const float* __restri
 
 }  // namespace
 
-#define BK(call)                        \
-    do {                                \
-        cudaError_t e_ = (call);        \
-        if (e_ != cudaSuccess) {        \
-            for (void* p : tmp) cudaFree(p); \
-            return e_;                  \
-        }                               \
-    } while (0)
+namespace {
+
+inline size_t align256(size_t b) { return (b + 255) & ~size_t(255); }
+
+// carve the build's scratch arrays out of one workspace (same order in the size query and the build)
+struct Scratch {
+    uint32_t *keys, *vals, *keys2, *vals2, *leaf_keys;
+    float *box_lo, *box_hi;
+    int2* children;
+    int *parent, *arrivals;
+    void* sort_tmp;
+    size_t sort_bytes, total;
+    Scratch(void* base, int n_tris, int n, size_t sort_b) : sort_bytes(sort_b) {
+        size_t off = 0;
+        auto take = [&](size_t bytes) {
+            void* p = base ? static_cast<char*>(base) + off : nullptr;
+            off += align256(bytes ? bytes : 1);
+            return p;
+        };
+        keys = static_cast<uint32_t*>(take(sizeof(uint32_t) * n_tris));
+        vals = static_cast<uint32_t*>(take(sizeof(uint32_t) * n_tris));
+        keys2 = static_cast<uint32_t*>(take(sizeof(uint32_t) * n_tris));
+        vals2 = static_cast<uint32_t*>(take(sizeof(uint32_t) * n_tris));
+        leaf_keys = static_cast<uint32_t*>(take(sizeof(uint32_t) * n));
+        box_lo = static_cast<float*>(take(sizeof(float) * 3 * (2 * size_t(n))));
+        box_hi = static_cast<float*>(take(sizeof(float) * 3 * (2 * size_t(n))));
+        children = static_cast<int2*>(take(sizeof(int2) * n));
+        parent = static_cast<int*>(take(sizeof(int) * 2 * size_t(n)));
+        arrivals = static_cast<int*>(take(sizeof(int) * n));
+        sort_tmp = take(sort_bytes);
+        total = off;
+    }
+};
+
+size_t sort_temp_bytes(int n_tris) {
+    size_t b = 0;
+    uint32_t* z = nullptr;
+    cub::DeviceRadixSort::SortPairs(nullptr, b, z, z, z, z, n_tris, 0, 30, nullptr);
+    return b;
+}
+
+}  // namespace
+
+size_t lbvh_workspace_bytes(int n_tris, int n_leaves) {
+    return Scratch(nullptr, n_tris, n_leaves, sort_temp_bytes(n_tris)).total;
+}
 
 cudaError_t build_mesh_lbvh(cudaStream_t stream, const float* d_pos, const uint32_t* d_idx, int n_tris,
                             const int32_t* d_slot_of_tri, const float lo[3], const float hi[3], DevNode2* d_nodes,
-                            DevTri* d_tris, int n_leaves, unsigned long long* launches) {
-    std::vector<void*> tmp;
-    auto alloc = [&](size_t bytes) -> void* {
-        void* p = nullptr;
-        if (cudaMalloc(&p, bytes ? bytes : 1) != cudaSuccess) return nullptr;
-        tmp.push_back(p);
-        return p;
-    };
+                            DevTri* d_tris, int n_leaves, void* workspace, size_t workspace_bytes,
+                            unsigned long long* launches) {
     const int n = n_leaves;
-    uint32_t* keys = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n_tris));
-    uint32_t* vals = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n_tris));
-    uint32_t* keys2 = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n_tris));
-    uint32_t* vals2 = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n_tris));
-    uint32_t* leaf_keys = static_cast<uint32_t*>(alloc(sizeof(uint32_t) * n));
-    float* box_lo = static_cast<float*>(alloc(sizeof(float) * 3 * (2 * size_t(n))));
-    float* box_hi = static_cast<float*>(alloc(sizeof(float) * 3 * (2 * size_t(n))));
-    int2* children = static_cast<int2*>(alloc(sizeof(int2) * n));
-    int* parent = static_cast<int*>(alloc(sizeof(int) * 2 * size_t(n)));
-    int* arrivals = static_cast<int*>(alloc(sizeof(int) * n));
-    if (!keys || !vals || !keys2 || !vals2 || !leaf_keys || !box_lo || !box_hi || !children || !parent || !arrivals) {
-        for (void* p : tmp) cudaFree(p);
-        return cudaErrorMemoryAllocation;
-    }
+    Scratch w(workspace, n_tris, n, sort_temp_bytes(n_tris));
+    if (!workspace || w.total > workspace_bytes) return cudaErrorInvalidValue;
     float3 l3 = make_float3(lo[0], lo[1], lo[2]);
     float3 ie = make_float3(1.0f / fmaxf(hi[0] - lo[0], 1e-30f), 1.0f / fmaxf(hi[1] - lo[1], 1e-30f),
                             1.0f / fmaxf(hi[2] - lo[2], 1e-30f));
-    k_morton<<<(n_tris + kB - 1) / kB, kB, 0, stream>>>(d_pos, d_idx, n_tris, l3, ie, keys, vals);
-    size_t sort_bytes = 0;
-    BK(cub::DeviceRadixSort::SortPairs(nullptr, sort_bytes, keys, keys2, vals, vals2, n_tris, 0, 30, stream));
-    void* sort_tmp = alloc(sort_bytes);
-    if (!sort_tmp) {
-        for (void* p : tmp) cudaFree(p);
-        return cudaErrorMemoryAllocation;
-    }
-    BK(cub::DeviceRadixSort::SortPairs(sort_tmp, sort_bytes, keys, keys2, vals, vals2, n_tris, 0, 30, stream));
-    k_leaves<<<(n + kB - 1) / kB, kB, 0, stream>>>(d_pos, d_idx, d_slot_of_tri, keys2, vals2, n_tris, n, d_tris, box_lo, box_hi,
-                                                   leaf_keys);
+    k_morton<<<(n_tris + kB - 1) / kB, kB, 0, stream>>>(d_pos, d_idx, n_tris, l3, ie, w.keys, w.vals);
+    size_t sort_bytes = w.sort_bytes;
+    cudaError_t e = cub::DeviceRadixSort::SortPairs(w.sort_tmp, sort_bytes, w.keys, w.keys2, w.vals, w.vals2, n_tris, 0, 30, stream);
+    if (e != cudaSuccess) return e;
+    k_leaves<<<(n + kB - 1) / kB, kB, 0, stream>>>(d_pos, d_idx, d_slot_of_tri, w.keys2, w.vals2, n_tris, n, d_tris, w.box_lo,
+                                                   w.box_hi, w.leaf_keys);
     if (n == 1) {
-        k_single<<<1, 1, 0, stream>>>(box_lo, box_hi, d_nodes);
+        k_single<<<1, 1, 0, stream>>>(w.box_lo, w.box_hi, d_nodes);
         if (launches) *launches += 3;
     } else {
-        BK(cudaMemsetAsync(arrivals, 0, sizeof(int) * n, stream));
-        k_hierarchy<<<(n - 1 + kB - 1) / kB, kB, 0, stream>>>(leaf_keys, n, children, parent);
-        k_fit<<<(n + kB - 1) / kB, kB, 0, stream>>>(n, children, parent, box_lo, box_hi, arrivals, d_nodes);
+        e = cudaMemsetAsync(w.arrivals, 0, sizeof(int) * n, stream);
+        if (e != cudaSuccess) return e;
+        k_hierarchy<<<(n - 1 + kB - 1) / kB, kB, 0, stream>>>(w.leaf_keys, n, w.children, w.parent);
+        k_fit<<<(n + kB - 1) / kB, kB, 0, stream>>>(n, w.children, w.parent, w.box_lo, w.box_hi, w.arrivals, d_nodes);
         if (launches) *launches += 4;
     }
-    BK(cudaGetLastError());
-    BK(cudaStreamSynchronize(stream));
-    for (void* p : tmp) cudaFree(p);
-    return cudaSuccess;
+    return cudaGetLastError();
 }
 
 }  // namespace mcpt

@@ -174,8 +174,10 @@ __device__ __forceinline__ void deliver(const Wavefront& wf, const QueueOut& hit
 }
 
 // Persistent warps over the CTA's queue region: a lane whose ray is finished delivers it and, once
-// kRefillLanes lanes of the warp are idle, the idle lanes take the next entries of the region (one
-// shared-memory atomic per refill). Incoherent rays -- a few lanes deep inside a mesh while the
+// S.refill_lanes lanes of the warp are idle, the idle lanes take the next entries of the region (one
+// shared-memory atomic per refill). Measured: mesh scenes are fastest refilling at 8 idle lanes (1.2x
+// over waiting for the whole warp); trees of analytic primitives at 32, i.e. a new tile only when the
+// whole warp is done (+11 % over 8: their rays are short, and refilled lanes drift out of phase). Incoherent rays -- a few lanes deep inside a mesh while the
 // others have left the scene -- no longer hold a whole warp: measured 4.4 of 32 lanes active in
 // late bounces of the mesh workload with one ray per lane per tile. Every iteration each lane does
 // the one step its ray needs (traverse.cuh); node steps of both levels share one code path.
@@ -183,7 +185,6 @@ __device__ __forceinline__ void deliver(const Wavefront& wf, const QueueOut& hit
 // instructions but fewer loads in flight, -14 %; holding the primitive step back until several lanes
 // want it -- no gain; one queue region per warp instead of per CTA -- no atomics at all and ordered
 // survivors, but warps of a CTA finish at different times, -4 % at C2.)
-constexpr int kRefillLanes = 8;
 
 template <bool COUNT, bool MESHES>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
@@ -202,7 +203,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
     while (true) {
         const uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
         if (idle) {
-            if (!exhausted && (idle == 0xffffffffu || __popc(idle) >= kRefillLanes)) {
+            if (!exhausted && (idle == 0xffffffffu || __popc(idle) >= S.refill_lanes)) {
                 uint32_t first = 0;
                 if (lane == 0) first = atomicAdd(s_next, uint32_t(__popc(idle)));
                 first = __shfl_sync(0xffffffffu, first, 0);

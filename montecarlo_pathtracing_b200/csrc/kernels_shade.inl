@@ -9,8 +9,11 @@
 // others). Paths that go on are appended to `next` -- and to `interior` when the new ray starts
 // inside a transparent primitive -- by warp_append into this CTA's regions of the two queues
 // (kernels.cu): that is the whole compaction, there is no separate pass and no flag array.
+#ifndef MCPT_SHADE_MINB
+#define MCPT_SHADE_MINB 4  // 64 registers, 4 CTAs per SM: the kernel waits on its first loads (measured +2 %)
+#endif
 template <bool FAST>
-__global__ void __launch_bounds__(kBlock) k_shade(DevScene S, DevParams prm, Wavefront wf, QueueIn qin, QueueOut next,
+__global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, DevParams prm, Wavefront wf, QueueIn qin, QueueOut next,
                                                    QueueOut interior, int first_bounce, int last_bounce, int first_pass,
                                                    uint32_t npix, unsigned long long* seg_counter) {
     __shared__ uint32_t s_count[2];

@@ -50,9 +50,15 @@ struct DevTri {
 };
 
 // node of a GPU-built mesh tree (bvh_build.cu): the boxes of both children and their tokens
-// (>= 0: node index, < 0: ~leaf; leaf l owns DevTri slots 4l .. 4l+3, whose b.w holds the
+// (>= 0: node index, < 0: ~leaf; leaf l owns kMeshLeafTris consecutive DevTri slots, whose b.w holds the
 // reference's leaf slot of the triangle = its visit rank)
-constexpr int kMeshLeafTris = 4;
+// Triangles per leaf of the GPU-built mesh trees. Measured on the 1 M-triangle workload: 1 -> 720,
+// 2 -> 535, 3 -> 487, 4 -> 456, 8 -> 379 Msamples/s: the exact (IEEE divide, no FMA) triangle test is the
+// expensive step, a box pair is cheap.
+#ifndef MCPT_LEAF_TRIS
+#define MCPT_LEAF_TRIS 1
+#endif
+constexpr int kMeshLeafTris = MCPT_LEAF_TRIS;
 
 struct DevNode2 {
     float4 lo0;  // child 0 min.xyz, w = token of child 0
@@ -65,7 +71,7 @@ struct DevMesh {
     const DevNode* nodes;   // 2^depth - 1 interior nodes, heap order   (reference tree; null when rebuilt)
     const DevTri* tris;     // 2^depth leaf slots                       (reference tree; null when rebuilt)
     const DevNode2* nodes2; // GPU-built tree (MCPT_OPT_MESH_BVH), null: walk the reference tree
-    const DevTri* tris2;    // its 4 * n_leaves2 triangle slots
+    const DevTri* tris2;    // its kMeshLeafTris * n_leaves2 triangle slots
     const uint32_t* idx;    // 3 * n_tris vertex ids (shading)
     const float* pos;       // 3 * n_verts
     const float* nrm;       // 3 * n_verts
@@ -90,6 +96,7 @@ struct DevScene {
     int32_t n_prims;
     int32_t n_meshes;
     int32_t persistent;        // 1: tree scenes are traced by persistent warps (MCPT_OPT_PERSISTENT)
+    int32_t refill_lanes;      // persistent warps: idle lanes that trigger a refill (MCPT_OPT_REFILL_LANES)
     const DevNode2* top2;      // the top-level tree in two-children node format (persistent warps), root = node 0
     // shared-memory staging plan (in units of DevNode / DevPrim)
     int32_t smem_top_nodes;    // first N top-level nodes staged

@@ -140,7 +140,7 @@ MCPT_DEV bool slab_entry(const float4& lo, const float4& hi, f3 idir, f3 od, flo
 
 // Walk a GPU-built mesh tree (bvh_build.cu): 64-byte nodes holding both child boxes, nearer child
 // first, the farther one pushed with its entry parameter so that it is dropped without a fetch
-// once a closer hit is known; 4-triangle leaves. The radix tree is at most 64 levels deep (30
+// once a closer hit is known; kMeshLeafTris triangles per leaf. The radix tree is at most 64 levels deep (30
 // Morton bits + index bits), which bounds the stack. Candidates go through the same triangle_test
 // / offer_at as the reference-tree walk with the reference's leaf slot as rank, so the winner is
 // the one the reference's own traversal keeps.
@@ -209,9 +209,11 @@ MCPT_DEV void mesh_walk_lbvh(Work& wk, const DevMesh& M, f3 Oi, f3 Di, f3 Ow, co
 
 // intersect_prim, raytracer_func.frag:681-705. MESHES = false compiles the mesh walk out
 // (scenes made of analytic primitives only: fewer live registers).
-template <bool COUNT, bool MESHES = true>
+// ALL_STAGED: every primitive record is in shared memory (flat scenes): plain LDS instead of a
+// generic load behind a pointer select.
+template <bool COUNT, bool MESHES = true, bool ALL_STAGED = false>
 MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p, f3 O, f3 D, float slack, Best& best) {
-    const DevPrim* pp = (p < S.smem_prims) ? (sm.prims + p) : (S.prims + p);
+    const DevPrim* pp = (ALL_STAGED || p < S.smem_prims) ? (sm.prims + p) : (S.prims + p);
     const int type = pp->type;
     if (type < 0) return;
     Aff inv, fwd;
@@ -520,7 +522,7 @@ MCPT_DEV void scene_walk_flat(Work& wk, const DevScene& S, const SmemScene& sm, 
         if (COUNT && valid) ++wk.boxes;
         if (__any_sync(0xffffffffu, pass)) {
             if (pass) {
-                prim_test<COUNT, false>(wk, S, sm, __float_as_int(nd.lo.w), O, D, slack, best);
+                prim_test<COUNT, false, true>(wk, S, sm, __float_as_int(nd.lo.w), O, D, slack, best);
                 if (best.h.prim >= 0) {
                     tmax = best.h.dist * 1.0001f + slack;
                     if (any_hit) valid = false;
