@@ -306,13 +306,22 @@ def main():
     rays = st["rays"]
     # algorithmic bytes per traversed ray: 32 B ray (origin+direction float4) read, 24 B hit
     # record written, 4 B queue index read; scene data of the repo scenes is served from
-    # shared memory (0 B). Mesh scenes add 32 B per interior node + 48 B per triangle slot.
+    # shared memory (0 B). Mesh scenes add 64 B per node pair + 48 B per triangle (L2-resident).
     bytes_per_ray = 60.0
     alg_bytes = rays * bytes_per_ray
     achieved = alg_bytes / (trav_ms * 1e-3) / 1e9 if trav_ms > 0 else 0.0
+    # DRAM traffic per launch from the committed ncu --set full capture (bytes per ray of the
+    # first-bounce launch of this workload x the rays of an average launch); null if not captured
+    traffic, traffic_src = None, None
+    tf = ROOT / "profiles" / "r01_traffic.json"
+    if tf.exists():
+        t = json.loads(tf.read_text()).get(args.workload)
+        if t:
+            traffic = t["dram_bytes_per_ray"] * rays / max(trav_launches, 1)
+            traffic_src = t["source"]
     roofline = {
         "kernel": "k_traverse", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
-        "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+        "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
         "launches": trav_launches, "avg_launch_ms": trav_ms / max(trav_launches, 1),
         "bytes_per_ray": bytes_per_ray, "rays_per_launch": rays / max(trav_launches, 1),
         "share_of_kernel_time": trav_ms / total_kernel_ms if total_kernel_ms else None,

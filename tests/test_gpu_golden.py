@@ -151,6 +151,7 @@ def test_converges_to_the_reference_16k_spp_image(ctx, sid):
             ref = cv["image"].astype(np.float64)
             rmse = float(np.sqrt(np.mean((img - ref) ** 2)))
             dlum = abs(img.mean() - ref.mean()) / ref.mean()
+            print(f"scene {sid}, {spp} passes from {first}: RMSE {rmse:.3e}, mean luminance off by {dlum:.3e}")
             assert rmse <= limit, (first, rmse)
             assert dlum <= 5e-3, (first, dlum)
     finally:
