@@ -126,7 +126,9 @@ __device__ __forceinline__ void flush_work(const Work& wk, unsigned long long* w
 // append needs no global atomic and no barrier -- a warp ballots, lane 0 bumps the CTA's counter in
 // shared memory, and the lanes write at region base + offset + rank. (One same-address global atomic
 // per warp serialises at the L2, one per block needs two barriers per tile; both were measured at
-// +30 % on the traversal kernel.) A region can never overflow: what a CTA appends is a subset of what
+// +30 % on the traversal kernel. Also measured: one ordered segment per warp inside the region,
+// appended without any atomic and consumed through a prefix of the eight segment lengths -- survivors
+// stay in path order, but every kernel got 5..15 % slower.) A region can never overflow: what a CTA appends is a subset of what
 // it read, and the first bounce hands CTA b the tiles b, b + G, b + 2G ... of the batch, at most
 // `cap` slots. Region lengths live in counts[b]; every CTA writes its own before it exits.
 __device__ __forceinline__ uint32_t queue_len(const QueueIn& q) {
