@@ -103,7 +103,7 @@ enum {
     MCPT_STAGE_SHADE = 2,
     MCPT_STAGE_BVH_BUILD = 3,      /* upload-time mesh tree build (MCPT_OPT_MESH_BVH) */
     MCPT_STAGE_TRAVERSE_INTERIOR = 4,
-    MCPT_STAGE_SHADE_EXIT = 5,
+    MCPT_STAGE_SHADE_EXIT = 5,     /* scenes with meshes only; elsewhere the interior traversal builds the exit rays */
     MCPT_STAGE_ACCUMULATE = 6,
     MCPT_STAGE_RESOLVE = 7,
     MCPT_STAGE_COUNT = 8

@@ -3,7 +3,7 @@
 // Owns all device memory of a context: the re-packed scene (layout.cuh), the
 // accumulation buffer, and the SoA wavefront state sized for a batch of passes.
 // mcpt_render() drives the wavefront: for each batch of passes
-//   raygen -> { traverse -> shade -> compact -> [traverse -> shade_exit] } x bounces -> accumulate
+//   raygen -> { traverse -> shade -> [traverse of the interior rays] } x bounces -> accumulate
 // with queue lengths kept on the device.
 #include <cuda_runtime.h>
 #include <dlfcn.h>

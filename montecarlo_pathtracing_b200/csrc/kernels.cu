@@ -159,20 +159,46 @@ __device__ __forceinline__ void warp_append(uint32_t* s_count, const QueueOut& q
     if (take) q.items[size_t(blockIdx.x) * q.cap + off + __popc(m & ((1u << lane) - 1u))] = p;
 }
 
-// Where the closest-hit search of one bounce delivers its result. With a hit queue (the main
-// traversal of the Monte Carlo mode) the rays that hit something are appended to it, so the shading
-// kernel only ever sees hits, and a ray that leaves the scene needs nothing at all: its path simply
-// stays as it is, and k_accumulate evaluates the fake sky (tp/montecarlo.frag:118-119) from the
-// path's last total / attenuation / direction. No dependent load sits between two walks of a warp.
-// Without a hit queue (interior rays, debug shaders) every ray's record goes to hit_a / hit_b.
-__device__ __forceinline__ void deliver(const Wavefront& wf, const QueueOut& hitq, uint32_t* s_count, uint32_t p, bool valid,
-                                        const Best& best) {
+// Where the closest-hit search of one bounce delivers its result.
+//  * Main traversal of the Monte Carlo mode (hit queue): the rays that hit something get their record
+//    in hit_a / hit_b and are appended to the queue, so the shading kernel only ever sees hits; a ray
+//    that leaves the scene needs nothing at all: its path simply stays as it is, and k_accumulate
+//    evaluates the fake sky (tp/montecarlo.frag:118-119) from the path's last total / attenuation /
+//    direction. No dependent load sits between two walks of a warp.
+//  * Interior rays (exit_mode): the second half of the transparent cases (tp/montecarlo.frag:150-152,
+//    163-165) is done right here -- take N, P of the hit (or keep the entry hit's N, P when nothing
+//    was hit: intersection_info writes nothing for shape -1) and leave through
+//    refract(D, -N, 1 / refract_ind). This used to be a kernel of its own (k_shade_exit: 2.1 ms per C2
+//    step at 14 % issue utilisation, waiting on its loads); here the loads overlap other warps' walks.
+//  * Debug shaders (no queue, no exit): every ray's record goes to hit_a / hit_b.
+struct HitSink {
+    QueueOut hitq;
+    int exit_mode;
+    int flat_face;
+    float refract_ind;
+};
+
+__device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, const HitSink& sink, uint32_t* s_count, uint32_t p,
+                                        bool valid, const Best& best) {
+    if (sink.exit_mode) {
+        if (valid) {
+            const float4 d4 = wf.ray_d[p];
+            const float4 n4 = wf.keep_n[p], p4 = wf.keep_p[p];
+            f3 N = mk3(n4.x, n4.y, n4.z), P = mk3(p4.x, p4.y, p4.z);
+            intersection_info(S, best.h.prim, best.h.sub, best.h.pl, sink.flat_face, N, P);
+            const f3 nO = P + N * MCPT_BIAS;
+            const f3 nD = refract3(mk3(d4.x, d4.y, d4.z), -N, 1.0f / sink.refract_ind);
+            wf.ray_o[p] = make_float4(nO.x, nO.y, nO.z, 0.0f);
+            wf.ray_d[p] = make_float4(nD.x, nD.y, nD.z, d4.w);  // w: the path's RNG draw count
+        }
+        return;
+    }
     const bool hit = valid && best.h.prim >= 0;
-    if (hit || (valid && !hitq.items)) {
+    if (hit || (valid && !sink.hitq.items)) {
         wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
         wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
     }
-    if (hitq.items) warp_append(s_count, hitq, hit, p);
+    if (sink.hitq.items) warp_append(s_count, sink.hitq, hit, p);
 }
 
 // Persistent warps over the CTA's queue region: a lane whose ray is finished delivers it and, once
@@ -190,7 +216,7 @@ __device__ __forceinline__ void deliver(const Wavefront& wf, const QueueOut& hit
 
 template <bool COUNT, bool MESHES>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
-                                                    uint32_t len, const QueueOut& hitq, uint32_t* s_next, uint32_t* s_hits,
+                                                    uint32_t len, const HitSink& sink, uint32_t* s_next, uint32_t* s_hits,
                                                     Work& wk) {
     int stack_tok[MESHES ? kWalkStack : 32];
     float stack_t[MESHES ? kWalkStack : 32];
@@ -228,12 +254,23 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
         const int kind = has_ray ? walk_kind(w) : -1;  // WALK_POP: a dead entry was dropped, pop again next time
         // finished rays: deliver and free the lane
         if (__any_sync(0xffffffffu, kind == WALK_DONE)) {
-            deliver(wf, hitq, s_hits, p, kind == WALK_DONE, w.best);
+            deliver(S, wf, sink, s_hits, p, kind == WALK_DONE, w.best);
             if (kind == WALK_DONE) has_ray = false;
         }
-        if (kind == WALK_NODE)
+#ifndef MCPT_NODE_STEPS
+#define MCPT_NODE_STEPS 4  // node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 922*, 6 -> 906*, 8 -> 874* Msamples/s (*: with the exit fused, -5 %)
+#endif
+#ifndef MCPT_NODE_POPS
+#define MCPT_NODE_POPS 0
+#endif
+        if (kind == WALK_NODE) {
             walk_node<COUNT>(w, wk, S, stack_tok, stack_t, wsave);
-        else if (MESHES && kind == WALK_TRI)
+#pragma unroll
+            for (int r = 1; r < MCPT_NODE_STEPS; ++r) {
+                if (MCPT_NODE_POPS && w.cur == kTokPop && !w.done) walk_pop_one(w, S, stack_tok, stack_t, wsave);
+                if (w.cur >= 0 && !w.done) walk_node<COUNT>(w, wk, S, stack_tok, stack_t, wsave);
+            }
+        } else if (MESHES && kind == WALK_TRI)
             walk_tri<COUNT>(w, wk, S, sm, stack_tok, stack_t, wsave);
         else if (kind == WALK_PRIM)
             walk_prim<COUNT, MESHES>(w, wk, S, sm, stack_tok, stack_t, wsave);
@@ -244,19 +281,19 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
 // persistent warps with per-lane refill (tree scenes; mesh trees must be the GPU-built ones).
 // Every lane of a warp stays in the loop together (warp-uniform trip count).
 template <bool COUNT, int MINB, bool FLAT, bool MESHES, bool PERSIST>
-__global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront wf, QueueIn qin, QueueOut hitq,
+__global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront wf, QueueIn qin, HitSink sink,
                                                             unsigned long long* ray_counter, unsigned long long* work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     __shared__ uint32_t s_hits, s_next;
     const uint32_t len = queue_len(qin);
     if (len == 0) {
-        if (threadIdx.x == 0 && hitq.items) hitq.counts[blockIdx.x] = 0u;
+        if (threadIdx.x == 0 && sink.hitq.items) sink.hitq.counts[blockIdx.x] = 0u;
         return;
     }
     if (threadIdx.x == 0) s_hits = s_next = 0u;
     SmemScene sm = stage_scene(S, smem_raw);  // ends with a barrier
     Work wk;
-    if (PERSIST) traverse_persistent<COUNT, MESHES>(S, sm, wf, qin, len, hitq, &s_next, &s_hits, wk);
+    if (PERSIST) traverse_persistent<COUNT, MESHES>(S, sm, wf, qin, len, sink, &s_next, &s_hits, wk);
     for (uint32_t base = 0; !PERSIST && base < len; base += kBlock) {
         uint32_t p;
         const bool valid = queue_item(qin, base + threadIdx.x, len, p);
@@ -272,7 +309,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
             else if (valid)
                 scene_walk<COUNT, MESHES>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
         }
-        deliver(wf, hitq, &s_hits, p, valid, best);
+        deliver(S, wf, sink, &s_hits, p, valid, best);
     }
     if (ray_counter && threadIdx.x == 0) {
         // rays this CTA traced: its region length, or its share of the identity queue (last tile cut at n)
@@ -284,18 +321,18 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
         atomicAdd(ray_counter, rays);
     }
     if (COUNT) flush_work(wk, work);
-    if (hitq.items) {
+    if (sink.hitq.items) {
         __syncthreads();
-        if (threadIdx.x == 0) hitq.counts[blockIdx.x] = s_hits;
+        if (threadIdx.x == 0) sink.hitq.counts[blockIdx.x] = s_hits;
     }
 }
 
 template <bool COUNT, int MINB>
-static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const QueueOut& hitq,
+static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const HitSink& sink,
                                  unsigned long long* ray_counter, unsigned long long* work) {
     const int grid = lc.grid;
 #define MCPT_TRAVERSE(FLAT, MESHES, PERSIST) \
-    k_traverse<COUNT, MINB, FLAT, MESHES, PERSIST><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, hitq, ray_counter, work)
+    k_traverse<COUNT, MINB, FLAT, MESHES, PERSIST><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink, ray_counter, work)
     if (S.n_flat > 0)
         MCPT_TRAVERSE(true, false, false);
     else if (S.n_meshes == 0) {
@@ -309,15 +346,21 @@ static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefro
 }
 
 void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const QueueOut& hitq,
-                     unsigned long long* ray_counter, unsigned long long* work) {
+                     const DevParams* exit_prm, unsigned long long* ray_counter, unsigned long long* work) {
+    HitSink sink{hitq, 0, 0, 1.0f};
+    if (exit_prm) {
+        sink.exit_mode = 1;
+        sink.flat_face = exit_prm->flat_face;
+        sink.refract_ind = exit_prm->refract_ind;
+    }
     if (work)
-        launch_traverse_kind<true, 2>(lc, S, wf, qin, hitq, ray_counter, work);
+        launch_traverse_kind<true, 2>(lc, S, wf, qin, sink, ray_counter, work);
     else if (lc.traverse_occ >= 4)
-        launch_traverse_kind<false, 4>(lc, S, wf, qin, hitq, ray_counter, nullptr);
+        launch_traverse_kind<false, 4>(lc, S, wf, qin, sink, ray_counter, nullptr);
     else if (lc.traverse_occ == 3)
-        launch_traverse_kind<false, 3>(lc, S, wf, qin, hitq, ray_counter, nullptr);
+        launch_traverse_kind<false, 3>(lc, S, wf, qin, sink, ray_counter, nullptr);
     else
-        launch_traverse_kind<false, 2>(lc, S, wf, qin, hitq, ray_counter, nullptr);
+        launch_traverse_kind<false, 2>(lc, S, wf, qin, sink, ray_counter, nullptr);
     ++g_launches;
 }
 

@@ -2,7 +2,7 @@
 //
 // One bounce of the wavefront is the kernel chain
 //   traverse (ends the misses, queues the hits) -> shade (appends the survivors to the next
-//   queues) -> [traverse -> shade_exit on interior rays]
+//   queues) -> [traverse of the interior rays, which also builds their exit rays]
 // run over device-resident queues whose lengths never leave the GPU; raygen
 // opens a batch of passes and accumulate closes it.
 #pragma once
@@ -39,8 +39,9 @@ struct LaunchCfg {
 void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,
                    int n_passes, uint32_t npix);
 // hitq.items != null: rays that hit something are appended to hitq; the others are already settled
+// exit_prm != null: interior rays -- the kernel finishes the transparent case itself (new ray through the exit hit)
 void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const QueueOut& hitq,
-                     unsigned long long* ray_counter, unsigned long long* work);
+                     const DevParams* exit_prm, unsigned long long* ray_counter, unsigned long long* work);
 void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin,
                   const QueueOut& next, const QueueOut& interior, bool first_bounce, bool last_bounce, int first_pass,
                   uint32_t npix, bool fast_math, unsigned long long* seg_counter);

@@ -1,0 +1,7 @@
+set -x
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest32.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest32.log
+timeout 300 python bench.py --steps 10 --no-cpu-baseline > gpurun_out/r32_c2.json 2>> gpurun_out/r32.err
+timeout 300 python bench.py --steps 10 --no-cpu-baseline --workload c1 > gpurun_out/r32_c1.json 2>> gpurun_out/r32.err
+timeout 300 python bench.py --steps 5 --no-cpu-baseline --workload c5 > gpurun_out/r32_c5.json 2>> gpurun_out/r32.err
+timeout 300 python bench.py --steps 5 --no-cpu-baseline --workload mesh > gpurun_out/r32_mesh.json 2>> gpurun_out/r32.err
+timeout 600 python -m pytest tests/test_gpu_golden.py -m gpu -x -q -s -k converges > gpurun_out/r32_converge.log 2>&1
