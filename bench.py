@@ -35,6 +35,7 @@ WORKLOADS = {
     "c2": ("c2", {}, 1920, 1080, 64, 8, 1.5, "BASELINE config 2: repo scene 6, 1920x1080, 64 spp, IOR 1.5, roughness 0.5, light 0.4, 8 bounces"),
     "c5": ("c5", {}, 1920, 1080, 64, 16, 1.5, "BASELINE config 5 (divergence stress) at 64 spp per step: all transparent+reflective, roughness 0.1, 16 bounces, 1080p"),
     "mesh": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 1920, 1080, 16, 8, 1.5, "BASELINE config 3 at 16 spp per step: 16 meshes x 65536 triangles, 1080p, 8 bounces"),
+    "c4": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 3840, 2160, 4, 8, 1.5, "BASELINE config 4 at 4 spp per step: 16 meshes x 65536 triangles, 3840x2160, 8 bounces"),
 }
 
 
@@ -130,7 +131,7 @@ def run_reference(args):
     cores = o.set_threads(len(os.sched_getaffinity(0)))
     # bounded sample per step: a band of rows at 1 spp, sized for ~2-4 s on this machine
     # bounded sample per step: the full frame at 1 spp (mesh workload: every 8th of the rows)
-    rows = h if args.workload != "mesh" else max(8, h // 8)
+    rows = h if args.workload not in ("mesh", "c4") else max(8, h // 8)
     y0 = (h - rows) // 2
     acc = np.zeros((h, w, 3), np.float32)
     for i in range(args.warmup):
@@ -335,7 +336,7 @@ def main():
         o = oracle_for(s, raw)
         o.set_uniforms(bounces, ior, DATE, 0, iv, ipv)
         cores = o.set_threads(len(os.sched_getaffinity(0)))
-        rows = h if args.workload != "mesh" else max(8, h // 8)
+        rows = h if args.workload not in ("mesh", "c4") else max(8, h // 8)
         y0 = (h - rows) // 2
         acc = np.zeros((h, w, 3), np.float32)
         t0 = time.perf_counter()

@@ -11,6 +11,14 @@ int upload_vec(mcpt_ctx* c, const std::vector<T>& h, T** out) {
     return MCPT_OK;
 }
 
+template <class T>
+int upload_raw(mcpt_ctx* c, const T* h, size_t count, T** out) {
+    int rc = dev_alloc(c, c->scene_allocs, out, count);
+    if (rc) return rc;
+    if (count) CK(c, cudaMemcpy(*out, h, count * sizeof(T), cudaMemcpyHostToDevice));
+    return MCPT_OK;
+}
+
 int validate_bvh(mcpt_ctx* c, const mcpt_bvh_desc& b, int n_items, const char* what) {
     if (!b.bb || !b.ind) return fail(c, MCPT_E_INVALID, "%s: null BVH arrays", what);
     if (b.depth < 1 || b.depth > 29) return fail(c, MCPT_E_INVALID, "%s: BVH depth %d out of range [1,29]", what, b.depth);
@@ -144,13 +152,14 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         const mcpt_mesh_desc& md = d->meshes[m];
         const int depth = md.bvh.depth;
         const uint32_t first_leaf = 1u << depth;
-        std::vector<uint32_t> idx(md.tri_idx, md.tri_idx + 3 * size_t(md.n_tris));
-        std::vector<float> pos(md.pos, md.pos + 3 * size_t(md.n_verts)), nrm(md.nrm, md.nrm + 3 * size_t(md.n_verts));
         DevMesh& M = meshes[m];
         std::memset(&M, 0, sizeof M);
         uint32_t* di = nullptr;
         float *dp = nullptr, *dnr = nullptr;
-        if ((rc = upload_vec(c, idx, &di)) || (rc = upload_vec(c, pos, &dp)) || (rc = upload_vec(c, nrm, &dnr))) return rc;
+        // straight from the caller's arrays (no host-side copies)
+        if ((rc = upload_raw(c, md.tri_idx, 3 * size_t(md.n_tris), &di)) || (rc = upload_raw(c, md.pos, 3 * size_t(md.n_verts), &dp)) ||
+            (rc = upload_raw(c, md.nrm, 3 * size_t(md.n_verts), &dnr)))
+            return rc;
         M.idx = di;
         M.pos = dp;
         M.nrm = dnr;
@@ -165,8 +174,8 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
             for (size_t v = 0; v < size_t(md.n_verts); ++v)
                 for (int k = 0; k < 3; ++k) {
-                    lo[k] = std::min(lo[k], pos[3 * v + k]);
-                    hi[k] = std::max(hi[k], pos[3 * v + k]);
+                    lo[k] = std::min(lo[k], md.pos[3 * v + k]);
+                    hi[k] = std::max(hi[k], md.pos[3 * v + k]);
                 }
             const int n_leaves = int((md.n_tris + kMeshLeafTris - 1) / kMeshLeafTris);
             int32_t* d_slot = nullptr;

@@ -258,18 +258,16 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
             if (kind == WALK_DONE) has_ray = false;
         }
 #ifndef MCPT_NODE_STEPS
-#define MCPT_NODE_STEPS 4  // node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 922*, 6 -> 906*, 8 -> 874* Msamples/s (*: with the exit fused, -5 %)
-#endif
-#ifndef MCPT_NODE_POPS
-#define MCPT_NODE_POPS 0
+#define MCPT_NODE_STEPS 4  // node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 946, 6 -> 930, 8 -> 900 Msamples/s
 #endif
         if (kind == WALK_NODE) {
+            // a run of node steps: the lanes at a triangle or a primitive wait, but the dispatch, the
+            // ballots and the rarer step kinds are paid once per run (popping inside the run as well
+            // was measured: -7 %)
             walk_node<COUNT>(w, wk, S, stack_tok, stack_t, wsave);
 #pragma unroll
-            for (int r = 1; r < MCPT_NODE_STEPS; ++r) {
-                if (MCPT_NODE_POPS && w.cur == kTokPop && !w.done) walk_pop_one(w, S, stack_tok, stack_t, wsave);
-                if (w.cur >= 0 && !w.done) walk_node<COUNT>(w, wk, S, stack_tok, stack_t, wsave);
-            }
+            for (int r = 1; r < MCPT_NODE_STEPS; ++r)
+                if (w.cur >= 0) walk_node<COUNT>(w, wk, S, stack_tok, stack_t, wsave);
         } else if (MESHES && kind == WALK_TRI)
             walk_tri<COUNT>(w, wk, S, sm, stack_tok, stack_t, wsave);
         else if (kind == WALK_PRIM)

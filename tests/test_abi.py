@@ -103,3 +103,14 @@ def test_default_camera_matches_the_viewer_maths():
     P[2, 2], P[2, 3], P[3, 2] = (zn + zf) / (zn - zf), 2 * zn * zf / (zn - zf), -1
     assert np.allclose(iv, np.linalg.inv(V), rtol=1e-5, atol=1e-4)
     assert np.allclose(ipv, np.linalg.inv(P @ V), rtol=1e-4, atol=1e-3)
+
+
+def test_python_constants_mirror_the_header_enums():
+    """capi.OPT_* / STAGE_NAMES are hand-written mirrors of the enums in include/mcpt.h."""
+    txt = (ROOT / "include" / "mcpt.h").read_text()
+    opts = dict(re.findall(r"MCPT_OPT_(\w+)\s*=\s*(\d+)", txt))
+    assert len(opts) >= 10
+    for name, value in opts.items():
+        assert getattr(capi, "OPT_" + name) == int(value), name
+    stages = {int(v): n.lower() for n, v in re.findall(r"MCPT_STAGE_(\w+)\s*=\s*(\d+)", txt) if n != "COUNT"}
+    assert tuple(stages[i] for i in range(len(stages))) == tuple(capi.STAGE_NAMES)
