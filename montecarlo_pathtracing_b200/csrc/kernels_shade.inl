@@ -9,11 +9,7 @@
 // others). Paths that go on are appended to `next` -- and to `interior` when the new ray starts
 // inside a transparent primitive -- by warp_append into this CTA's regions of the two queues
 // (kernels.cu): that is the whole compaction, there is no separate pass and no flag array.
-#ifndef MCPT_SHADE_PREFETCH
-#define MCPT_SHADE_PREFETCH 1
-#endif
-__device__ __forceinline__ void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
-
+// (Measured and dropped: prefetch.global.L2 of the next path's state at the end of an iteration, +3 % time.)
 #ifndef MCPT_SHADE_MINB
 #define MCPT_SHADE_MINB 4  // 64 registers, 4 CTAs per SM: the kernel waits on its first loads (measured +2 %)
 // (Measured and dropped: compiling the FAST instantiation with FMA contraction. 48 % of its instructions
@@ -38,13 +34,6 @@ __global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, D
     unsigned int my_segments = 0;
     for (uint32_t base = 0; base < len; base += kBlock) {
         uint32_t kind = 0, p;  // kind: 0 ended, 1 goes on, 2 goes on after an interior traversal
-#if MCPT_SHADE_PREFETCH
-        // the path this thread shades in its NEXT iteration: fetch its queue entry now, and pull its state
-        // towards the L2 once this iteration's work is done (after the first bounce the kernel waits on
-        // its gathers: 11 long-scoreboard stalls per issue, ncu)
-        uint32_t p_ahead;
-        const bool ahead = queue_item(qin, base + kBlock + threadIdx.x, len, p_ahead);
-#endif
         if (queue_item(qin, base + threadIdx.x, len, p)) {
             const float4 ha = wf.hit_a[p];
             const int2 hb = wf.hit_b[p];
@@ -113,17 +102,6 @@ __global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, D
             warp_append(&s_count[0], next, kind != 0u, p);
             warp_append(&s_count[1], interior, kind == 2u, p);
         }
-#if MCPT_SHADE_PREFETCH
-        if (ahead) {
-            prefetch_l2(wf.hit_a + p_ahead);
-            prefetch_l2(wf.hit_b + p_ahead);
-            prefetch_l2(wf.ray_d + p_ahead);
-            if (!first_bounce) {
-                prefetch_l2(wf.total + p_ahead);
-                prefetch_l2(wf.attenu + p_ahead);
-            }
-        }
-#endif
     }
     if (seg_counter) {
         // one atomic per warp
