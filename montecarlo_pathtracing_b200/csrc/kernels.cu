@@ -91,7 +91,8 @@ __global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam
             dir = d1 * (1.0f - v) + d2 * (1.0f - u) + d3 * ((u + v) - 1.0f);
         dir = normalize3(dir);
         // attenuation 0.8, total 0 and the RNG seed of a fresh path are implied (k_shade first bounce,
-        // k_accumulate): nothing else is initialised here
+        // k_accumulate): nothing else is initialised here. (Leaving out the origin too -- it is the
+        // camera's for every primary ray -- saved 32 B per path and no time: measured, dropped.)
         wf.ray_o[p] = make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f);
         wf.ray_d[p] = make_float4(dir.x, dir.y, dir.z, 0.0f);
     }

@@ -4,19 +4,21 @@
 // (bvh_gpu/gpu_bvh_scene.cpp:121-187) and pays 5-9 dependent texel fetches per
 // candidate primitive. Here the same information is re-packed once at upload:
 //
-//  * BVH nodes: 32 bytes = two float4 {min.xyz, aux0} {max.xyz, aux1}, in the
-//    reference's implicit heap order (node k has children 2k+1, 2k+2) so the tree
-//    needs no child pointers and traversal needs no stack in memory: a 32-bit
-//    trail of "sibling still pending" bits plus the heap index is the whole state.
-//    Boxes are inflated by a few ulps so the (FMA, non-exact) slab test stays
-//    conservative. Leaf-level nodes of the top-level tree carry the primitive id
-//    in aux0.
+//  * BVH nodes, two forms. DevNode, 32 bytes = two float4 {min.xyz, aux0} {max.xyz, aux1}, in the
+//    reference's implicit heap order (node k has children 2k, 2k+1, 1-based): no child pointers, and
+//    a walk needs no stack in memory -- a 32-bit trail of "sibling still pending" bits plus the heap
+//    index is the whole state; leaf-level nodes of the top-level tree carry the primitive id in aux0
+//    (flat list of small scenes, one-ray-per-lane tree walk, mcpt_trace_rays). DevNode2, 64 bytes =
+//    both child boxes + two child tokens: the mesh trees built on the GPU at upload (bvh_build.cu)
+//    and the top-level tree re-packed into the same form, walked with one explicit stack by the
+//    persistent warps. Boxes are inflated by a few ulps so the (FMA, non-exact) slab test stays
+//    conservative.
 //  * primitive records: 128 bytes = inverse transform (3 rows), forward transform
 //    (3 rows), {type, mesh id, leaf slot}, instead of the 256-byte PrimData.
 //  * triangles: 48 bytes per LEAF SLOT (three float4: A,B,C with the triangle id
-//    in A.w), stored in leaf-slot order so that the leaf level needs neither the
-//    index table nor the three scattered vertex fetches of read_triangle_pos
-//    (shaders/raytracer_func.frag:144-152).
+//    in A.w, the reference's leaf slot in B.w for the GPU-built trees), stored in leaf order so
+//    that the leaf level needs neither the index table nor the three scattered vertex fetches of
+//    read_triangle_pos (shaders/raytracer_func.frag:144-152).
 //  * shading tables: colour + material float4 per primitive; per-mesh vertex
 //    positions/normals/indices for the smooth-normal reconstruction.
 #pragma once

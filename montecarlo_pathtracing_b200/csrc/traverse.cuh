@@ -4,24 +4,26 @@
 //
 // Design (B200): the reference walks the tree with an int[29] stack in local
 // memory, visits children in fixed left/right order and pays two dependent texel
-// fetches plus three vector divides per box. Here
-//   * the tree keeps the reference's implicit heap order, so the walk needs no
-//     stack at all: the node's heap index plus a 32-bit trail ("a sibling is still
-//     pending at this level") live in two registers per thread — nothing to spill,
-//     nothing to diverge on in memory;
-//   * children are visited near-first using the split axis that the builder cycles
-//     per level (bvh_gpu/bvh.cpp:45-51), and the far sibling is tested only when
-//     it is popped, against the by-then shorter ray;
-//   * a node is 32 bytes, fetched as two 16-byte vector loads; both children of a
-//     node share one 64-byte segment; the top levels come from shared memory;
-//   * the slab test runs on precomputed reciprocals with FMAs. It only culls:
-//     boxes are inflated at upload so it never rejects a box the exact arithmetic
-//     of the reference would accept, and candidates are ranked by the exact
-//     world-space distance (intersect.cuh).
+// fetches plus three vector divides per box. Here there are three walkers, chosen
+// per scene at upload (all rank candidates by the exact world-space distance of
+// intersect.cuh with the reference's visit order as tie-break, so they return the
+// same record bit for bit):
+//   * scene_walk_flat -- <= 16 analytic primitives: the leaf boxes as one list in
+//     shared memory, stepped through by all lanes of a warp together;
+//   * the resumable walk (walk_begin / walk_node / walk_tri / walk_prim) -- every
+//     other scene, under persistent warps (k_traverse, PERSIST): both levels in the
+//     64-byte two-children node format, nearer child first, the farther one pushed
+//     with its entry parameter on one explicit stack;
+//   * scene_walk + mesh_walk / mesh_walk_lbvh -- one ray per lane over the
+//     reference's implicit heap order, which needs no stack at all: the node's heap
+//     index plus a 32-bit trail ("a sibling is still pending at this level") live in
+//     two registers per thread; children are visited near-first using the split axis
+//     that the builder cycles per level (bvh_gpu/bvh.cpp:45-51). Used by
+//     mcpt_trace_rays and when MCPT_OPT_PERSISTENT / MCPT_OPT_MESH_BVH are off.
+// The slab test runs on precomputed (approximate) reciprocals with FMAs. It only
+// culls: boxes are inflated at upload so it never rejects a box the exact arithmetic
+// of the reference would accept.
 #pragma once
-#ifndef MCPT_FLAT_VARIANT
-#define MCPT_FLAT_VARIANT 0
-#endif
 #include <climits>
 
 #include "intersect.cuh"
@@ -530,24 +532,7 @@ MCPT_DEV void scene_walk_flat(Work& wk, const DevScene& S, const SmemScene& sm, 
     float tmax = FLT_MAX;
     const int n = S.n_flat;
     for (int i = 0; i < n; ++i) {
-#if MCPT_FLAT_VARIANT == 1
-        DevNode nd;
-        {
-            const volatile float* nf = reinterpret_cast<const volatile float*>(sm.top_nodes + i);
-            nd.lo = make_float4(nf[0], nf[1], nf[2], nf[3]);
-            nd.hi = make_float4(nf[4], nf[5], nf[6], 0.0f);
-        }
-#elif MCPT_FLAT_VARIANT == 2
-        DevNode nd;
-        {
-            const float2* nf = reinterpret_cast<const float2*>(sm.top_nodes + i);
-            const float2 a = nf[0], b = nf[1], c = nf[2], d = nf[3];
-            nd.lo = make_float4(a.x, a.y, b.x, b.y);
-            nd.hi = make_float4(c.x, c.y, d.x, 0.0f);
-        }
-#else
         const DevNode nd = sm.top_nodes[i];  // flat list is staged where the tree would be
-#endif
         const bool pass = valid && slab(nd, idir, od, tmax);
         if (COUNT && valid) ++wk.boxes;
         if (__any_sync(0xffffffffu, pass)) {

@@ -187,3 +187,62 @@ def test_persistent_warps_do_not_change_the_image(kind, kw):
     assert np.array_equal(out[0][0], out[1][0])
     assert out[0][1]["rays"] == out[1][1]["rays"] and out[0][1]["segments"] == out[1][1]["segments"]
     assert out[0][0][..., :3].mean() > 0.01
+
+
+def test_reupload_and_resize_give_the_same_bits():
+    """A context that has held other scenes and sizes (parked and reused allocations, regrown wavefront,
+    stale path tags in the reused buffers) renders exactly what a fresh context renders."""
+    s2, _ = both(2)
+    sm, _ = both("mesh", n_meshes=2, tris_log2=8)
+    s7, _ = both(7)
+
+    def render(c, s, w, h, spp):
+        iv, ipv = capi.default_camera(w, h)
+        c.upload_scene(s)
+        c.resize(w, h)
+        c.set_camera(iv, ipv)
+        c.set_params(nb_bounces=6, refract_ind=1.5, date=float(DATE))
+        c.clear()
+        c.render(0, spp)
+        return c.read_accum()
+
+    fresh = Context(0)
+    want = render(fresh, s2, 64, 48, 5)
+    fresh.close()
+    c = Context(0)
+    render(c, sm, 200, 100, 3)
+    render(c, s7, 96, 54, 2)
+    render(c, sm, 64, 48, 4)
+    got = render(c, s2, 64, 48, 5)
+    again = render(c, s2, 64, 48, 5)
+    c.close()
+    assert np.array_equal(want, got) and np.array_equal(want, again)
+
+
+def test_two_contexts_on_their_own_streams_do_not_interfere():
+    import torch
+    s2, _ = both(2)
+    s6, _ = both("c2")
+    iv, ipv = capi.default_camera(128, 72)
+    ctxs, streams = [], []
+    for s in (s2, s6):
+        c = Context(0)
+        st = torch.cuda.Stream()
+        c.set_stream(st.cuda_stream)
+        c.upload_scene(s)
+        c.resize(128, 72)
+        c.set_camera(iv, ipv)
+        c.set_params(nb_bounces=6, refract_ind=1.5, date=float(DATE))
+        ctxs.append(c)
+        streams.append(st)
+    for k in range(4):                       # interleaved, asynchronous launches
+        for c in ctxs:
+            c.render(2 * k, 2)
+    both_imgs = [c.read_accum() for c in ctxs]
+    for c in ctxs:
+        c.clear()
+        c.render(0, 8)                       # the same eight passes in one call, one context at a time
+        c.synchronize()
+    for c, img in zip(ctxs, both_imgs):
+        assert np.array_equal(c.read_accum(), img)
+        c.close()
