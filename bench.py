@@ -248,6 +248,13 @@ def main():
     barrier()
     stages = ctx.stage_times()
     ctx.set_option(capi.OPT_PROFILE_STAGES, 0)
+    # algorithmic work of one step: the counting instantiation of the traversal kernels (untimed)
+    ctx.set_option(capi.OPT_COUNT_WORK, 1)
+    ctx.reset_stats()
+    step()
+    barrier()
+    work = ctx.stats()
+    ctx.set_option(capi.OPT_COUNT_WORK, 0)
     ctx.reset_stats()
     if world > 1:
         t = torch.tensor([ms], device="cuda")
@@ -330,6 +337,36 @@ def main():
         "dominant_stage": dominant,
         "note": "repo scenes fit in shared memory: the kernel is FP32-issue bound, not HBM bound; see profiles/ for the ncu issue-slot figures",
     }
+
+    # FP32 issue roofline: flops = 24 N_box + (42 + F_type) N_record + 46 N_tri
+    # + 60 N_hit + 230 N_segment, FMA = 2, counted by the kernels themselves in the untimed counting
+    # step above. F_type is averaged over the scene's analytic records (the counters are not split
+    # by type). Peak = SMs x 128 FP32 lanes x 2 x the SM clock sampled under load.
+    f_type = {capi.PRIM_SPHERE: 34.0, capi.PRIM_CUBE: 48.0, capi.PRIM_CYLINDER: 58.0, capi.PRIM_CONE: 66.0,
+              capi.PRIM_ORIENTED_QUAD: 14.0, capi.PRIM_MESH: 0.0}
+    types = [int(t) for t in s.prim_data()[:, 48]]   # PrimData texel 12 .x = type code
+    f_avg = sum(f_type.get(t, 0.0) for t in types) / max(len(types), 1)
+    trav_flops = 24.0 * work["boxes"] + (42.0 + f_avg) * work["prim_tests"] + 46.0 * work["tri_tests"]
+    step_flops = trav_flops + (60.0 + 230.0) * work["segments"]
+    sm_count = torch.cuda.get_device_properties(local).multi_processor_count
+    clk = (clocks or {}).get("sm_mhz") or sm_max or 1965.0
+    fp32_peak = sm_count * 128 * 2 * clk * 1e6 / 1e12
+    trav_ms_step = trav_ms / args.steps
+    roofline["fp32"] = {
+        "unit": "TFLOP/s", "peak": fp32_peak, "peak_source": f"{sm_count} SMs x 128 lanes x 2 x {clk:.0f} MHz (clock under load)",
+        "traverse": {"achieved": trav_flops / (trav_ms_step * 1e-3) / 1e12 if trav_ms_step > 0 else None,
+                     "flops_per_ray": trav_flops / max(work["rays"], 1)},
+        "step": {"achieved": step_flops / (ms / args.steps * 1e-3) / 1e12, "flops_per_path": step_flops / max(work["paths"], 1)},
+        "work_per_step": {k: int(work[k]) for k in ("paths", "rays", "segments", "boxes", "prim_tests", "tri_tests")},
+        "f_type_avg": f_avg,
+    }
+    roofline["fp32"]["traverse"]["frac"] = (roofline["fp32"]["traverse"]["achieved"] or 0.0) / fp32_peak
+    roofline["fp32"]["step"]["frac"] = roofline["fp32"]["step"]["achieved"] / fp32_peak
+    # SURVEY 8(d) byte formula for the whole step (every stage, wavefront state included):
+    # 32 N_node + 36 N_tri + 96 N_ray + 32 N_path (primitive records are served from shared memory)
+    step_bytes = 32.0 * work["boxes"] * (1.0 if s.nb_meshes else 0.0) + 36.0 * work["tri_tests"] + 96.0 * work["rays"] + 32.0 * work["paths"]
+    roofline["step_bytes_survey"] = {"bytes_per_step": step_bytes, "achieved": step_bytes / (ms / args.steps * 1e-3) / 1e9,
+                                     "unit": "GB/s", "frac": step_bytes / (ms / args.steps * 1e-3) / 1e9 / peak}
 
     cpu = None
     if not args.no_cpu_baseline:

@@ -219,8 +219,7 @@ template <bool COUNT, bool MESHES>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
                                                     uint32_t len, const HitSink& sink, uint32_t* s_next, uint32_t* s_hits,
                                                     Work& wk) {
-    int stack_tok[MESHES ? kWalkStack : 32];
-    float stack_t[MESHES ? kWalkStack : 32];
+    MCPT_WALK_STACK_DECL(st, (MESHES ? kWalkStack : 32));
     float wsave[6];
     WalkState w;
     w.done = true;
@@ -251,7 +250,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
 #endif
 #pragma unroll 1
         for (int r = 0; r < MCPT_POPS_PER_ITER && has_ray && w.cur == kTokPop && !w.done; ++r)
-            walk_pop_one(w, S, stack_tok, stack_t, wsave);
+            walk_pop_one(w, S, st, wsave);
         const int kind = has_ray ? walk_kind(w) : -1;  // WALK_POP: a dead entry was dropped, pop again next time
         // finished rays: deliver and free the lane
         if (__any_sync(0xffffffffu, kind == WALK_DONE)) {
@@ -265,14 +264,14 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
             // a run of node steps: the lanes at a triangle or a primitive wait, but the dispatch, the
             // ballots and the rarer step kinds are paid once per run (popping inside the run as well
             // was measured: -7 %)
-            walk_node<COUNT>(w, wk, S, stack_tok, stack_t, wsave);
+            walk_node<COUNT>(w, wk, S, st, wsave);
 #pragma unroll
             for (int r = 1; r < MCPT_NODE_STEPS; ++r)
-                if (w.cur >= 0) walk_node<COUNT>(w, wk, S, stack_tok, stack_t, wsave);
+                if (w.cur >= 0) walk_node<COUNT>(w, wk, S, st, wsave);
         } else if (MESHES && kind == WALK_TRI)
-            walk_tri<COUNT>(w, wk, S, sm, stack_tok, stack_t, wsave);
+            walk_tri<COUNT>(w, wk, S, sm, st, wsave);
         else if (kind == WALK_PRIM)
-            walk_prim<COUNT, MESHES>(w, wk, S, sm, stack_tok, stack_t, wsave);
+            walk_prim<COUNT, MESHES>(w, wk, S, sm, st, wsave);
     }
 }
 

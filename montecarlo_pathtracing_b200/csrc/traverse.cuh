@@ -340,6 +340,38 @@ constexpr int kTokExitMesh = INT_MIN + 1;  // stack marker: back to the world fr
 constexpr int kTokPop = INT_MIN + 2;       // w.cur: the next thing to do is to take an entry off the stack
 constexpr int kWalkStack = 30 + 1 + kLbvhStack;
 
+// The explicit stack of the resumable walk lives in local memory. MCPT_STACK64 (default): one 8-byte
+// entry {token, entry parameter} -- one local load per pop, one store per push; 0: two 4-byte arrays.
+#ifndef MCPT_STACK64
+#define MCPT_STACK64 1
+#endif
+#if MCPT_STACK64
+struct WalkStack {
+    int2* e;
+    MCPT_DEV void put(int i, int tok, float t) const { e[i] = make_int2(tok, __float_as_int(t)); }
+    MCPT_DEV void get(int i, int& tok, float& t) const {
+        const int2 v = e[i];
+        tok = v.x;
+        t = __int_as_float(v.y);
+    }
+};
+#define MCPT_WALK_STACK_DECL(name, n) int2 name##_e[n]; WalkStack name{name##_e}
+#else
+struct WalkStack {
+    int* tok_;
+    float* t_;
+    MCPT_DEV void put(int i, int tok, float t) const {
+        tok_[i] = tok;
+        t_[i] = t;
+    }
+    MCPT_DEV void get(int i, int& tok, float& t) const {
+        tok = tok_[i];
+        t = t_[i];
+    }
+};
+#define MCPT_WALK_STACK_DECL(name, n) int name##_tok[n]; float name##_t[n]; WalkStack name{name##_tok, name##_t}
+#endif
+
 struct WalkState {
     f3 O, D;         // world ray as given (D not normalised)
     float slack;
@@ -392,27 +424,29 @@ MCPT_DEV int walk_kind(const WalkState& w) {
 // One entry per iteration of the warp's loop, not a loop of its own: a lane that has several dead
 // entries to drop would otherwise hold the other 31 (measured: 20 % of the kernel's instructions at
 // 2.5 active lanes).
-MCPT_DEV void walk_pop_one(WalkState& w, const DevScene& S, const int* stack_tok, const float* stack_t, const float* wsave) {
+MCPT_DEV void walk_pop_one(WalkState& w, const DevScene& S, const WalkStack& st, const float* wsave) {
     if (w.sp == 0) {
         w.done = true;
         return;
     }
     --w.sp;
-    const int tok = stack_tok[w.sp];
+    int tok;
+    float tok_t;
+    st.get(w.sp, tok, tok_t);
     if (tok == kTokExitMesh) {
         w.mesh_prim = -1;
         w.nodes = S.top2;
         w.idir = mk3(wsave[0], wsave[1], wsave[2]);
         w.od = mk3(wsave[3], wsave[4], wsave[5]);
         w.tmax = (w.best.h.prim >= 0) ? (w.best.h.dist * 1.0001f + w.slack) : FLT_MAX;
-    } else if (stack_t[w.sp] <= w.tmax) {
+    } else if (tok_t <= w.tmax) {
         w.cur = tok;
         w.tri_j = 0;
     }
 }
 
 template <bool COUNT>
-MCPT_DEV void walk_node(WalkState& w, Work& wk, const DevScene& S, int* stack_tok, float* stack_t, const float* wsave) {
+MCPT_DEV void walk_node(WalkState& w, Work& wk, const DevScene& S, const WalkStack& st, const float* wsave) {
     const DevNode2* np = w.nodes + w.cur;
     const float4 lo0 = __ldg(&np->lo0), hi0 = __ldg(&np->hi0), lo1 = __ldg(&np->lo1), hi1 = __ldg(&np->hi1);
     const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(hi0.w);
@@ -423,8 +457,7 @@ MCPT_DEV void walk_node(WalkState& w, Work& wk, const DevScene& S, int* stack_to
     w.tri_j = 0;
     if (h0 && h1) {
         const bool swap = t1 < t0;
-        stack_tok[w.sp] = swap ? c0 : c1;
-        stack_t[w.sp] = swap ? t0 : t1;
+        st.put(w.sp, swap ? c0 : c1, swap ? t0 : t1);
         ++w.sp;
         w.cur = swap ? c1 : c0;
     } else if (h0 || h1) {
@@ -435,8 +468,7 @@ MCPT_DEV void walk_node(WalkState& w, Work& wk, const DevScene& S, int* stack_to
 }
 
 template <bool COUNT>
-MCPT_DEV void walk_tri(WalkState& w, Work& wk, const DevScene& S, const SmemScene& sm, const int* stack_tok, const float* stack_t,
-                       const float* wsave) {
+MCPT_DEV void walk_tri(WalkState& w, Work& wk, const DevScene& S, const SmemScene& sm, const WalkStack& st, const float* wsave) {
     const DevTri* tp = w.tris2 + kMeshLeafTris * (~w.cur) + w.tri_j;
     const float4 ta = __ldg(&tp->a);
     const int tri = __float_as_int(ta.w);
@@ -458,8 +490,7 @@ MCPT_DEV void walk_tri(WalkState& w, Work& wk, const DevScene& S, const SmemScen
 }
 
 template <bool COUNT, bool MESHES>
-MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemScene& sm, int* stack_tok, float* stack_t,
-                        float* wsave) {
+MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemScene& sm, const WalkStack& st, float* wsave) {
     const int pid = ~w.cur;
     const DevPrim* pp = (pid < S.smem_prims) ? (sm.prims + pid) : (S.prims + pid);
     if (MESHES && pp->type == MCPT_PRIM_MESH) {
@@ -479,8 +510,7 @@ MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemSce
         const float scale = sqrtf(wd.x * wd.x + wd.y * wd.y + wd.z * wd.z);
         if (scale > 0.0f) {  // else zero or NaN direction: the shader finds nothing either
             const DevMesh& M = S.meshes[pp->mesh];
-            stack_tok[w.sp] = kTokExitMesh;
-            stack_t[w.sp] = 0.0f;
+            st.put(w.sp, kTokExitMesh, 0.0f);
             ++w.sp;
             w.nodes = M.nodes2;
             w.tris2 = M.tris2;
