@@ -246,3 +246,35 @@ def test_two_contexts_on_their_own_streams_do_not_interfere():
     for c, img in zip(ctxs, both_imgs):
         assert np.array_equal(c.read_accum(), img)
         c.close()
+
+
+@pytest.mark.gpu
+def test_headless_render_tool_writes_the_back_buffer_and_reports_convergence(tmp_path):
+    """montecarlo_pathtracing_b200/render.py: the viewer's call sequence replayed headless,
+    PNG of the clamped 8-bit back buffer + float PFM, RMSE / mean luminance against the reference's
+    16k-spp image of scene 6 (tests/golden/converged6.npz). 1024 passes: Monte Carlo noise only."""
+    import json
+    from pathlib import Path
+    from montecarlo_pathtracing_b200 import imageio, render
+    gold = Path(__file__).parent / "golden" / "converged6.npz"
+    png, pfm = tmp_path / "s6.png", tmp_path / "s6.pfm"
+    import contextlib
+    import io
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        render.main(["--scene", "6", "--width", "64", "--height", "48", "--spp", "1024", "--bounces", "8", "--ior", "1.5",
+                     "--ref", str(gold), "--out", str(png), "--pfm", str(pfm)])
+    rep = json.loads(buf.getvalue().strip().splitlines()[-1])
+    assert rep["non_finite_pixels"] == 0
+    assert rep["vs_ref"]["rmse"] <= 3e-2 and rep["vs_ref"]["luminance_rel_err"] <= 5e-3, rep["vs_ref"]
+    img = imageio.read_pfm(pfm)
+    assert img.shape == (48, 64, 3)
+    assert np.array_equal(imageio.read_png(png), imageio.to_rgba8(img)[::-1, :, :3])
+    # the progressive curve falls as passes accumulate
+    buf = io.StringIO()
+    with contextlib.redirect_stdout(buf):
+        render.main(["--scene", "6", "--width", "64", "--height", "48", "--bounces", "8", "--ior", "1.5", "--ref", str(gold),
+                     "--curve", "4,64,1024"])
+    curve = json.loads(buf.getvalue().strip().splitlines()[-1])["curve"]
+    assert [c["spp"] for c in curve] == [4, 64, 1024]
+    assert curve[0]["rmse"] > curve[1]["rmse"] > curve[2]["rmse"]
