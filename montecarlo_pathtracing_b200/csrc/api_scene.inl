@@ -121,6 +121,45 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         std::memcpy(&N.hi0.w, &tok[1], sizeof(int));
     }
 
+    // ---- and with every second level folded away (DevNode4, MCPT_WIDE): the node of heap index k at an
+    // even level holds its grandchildren 4k .. 4k+3 (its children 2k, 2k+1 where those are leaves); stored
+    // at k-1 like top2, the entries of odd levels stay unused
+    std::vector<DevNode4> top4(std::max<uint32_t>(t_first_leaf - 1, 1u));
+    {
+        auto slot = [&](DevNode4& N, int j, uint32_t ch) {
+            int tok = INT_MIN;  // kTokEmpty
+            DevNode b = empty_node();
+            if (ch < t_first_leaf) {
+                tok = int(ch - 1);
+                b = top[ch];
+            } else {
+                const int prim = d->root.ind[ch - t_first_leaf];
+                if (prim >= 0) {
+                    tok = ~prim;
+                    b = top[ch];
+                }
+            }
+            (&N.lox.x)[j] = b.lo.x; (&N.loy.x)[j] = b.lo.y; (&N.loz.x)[j] = b.lo.z;
+            (&N.hix.x)[j] = b.hi.x; (&N.hiy.x)[j] = b.hi.y; (&N.hiz.x)[j] = b.hi.z;
+            (&N.tok.x)[j] = tok;
+        };
+        for (DevNode4& N : top4) {
+            std::memset(&N, 0, sizeof N);
+            N.tok = make_int4(INT_MIN, INT_MIN, INT_MIN, INT_MIN);
+        }
+        if (td == 0) {
+            slot(top4[0], 0, 1u);  // a single leaf slot: the root is that leaf
+        }
+        for (int level = 0; level < td; level += 2)
+            for (uint32_t k = 1u << level; k < (2u << level); ++k) {
+                DevNode4& N = top4[k - 1];
+                if (level + 1 < td)
+                    for (int j = 0; j < 4; ++j) slot(N, j, 4 * k + uint32_t(j));
+                else
+                    for (int j = 0; j < 2; ++j) slot(N, j, 2 * k + uint32_t(j));
+            }
+    }
+
     // ---- small scenes: flat list of leaf boxes for the warp-coherent walk
     std::vector<DevNode> flat;
     if (c->opt_flat_walk && d->n_prims > 0 && d->n_prims <= 16 && d->n_meshes == 0)
@@ -180,9 +219,11 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             const int n_leaves = int((md.n_tris + kMeshLeafTris - 1) / kMeshLeafTris);
             int32_t* d_slot = nullptr;
             DevNode2* dn2 = nullptr;
+            DevNode4* dn4 = nullptr;
             DevTri* dt2 = nullptr;
             if ((rc = dev_alloc(c, build_allocs, &d_slot, slot_of_tri.size())) ||
                 (rc = dev_alloc(c, c->scene_allocs, &dn2, size_t(std::max(n_leaves - 1, 1)))) ||
+                (rc = dev_alloc(c, c->scene_allocs, &dn4, size_t(std::max(n_leaves - 1, 1)))) ||
                 (rc = dev_alloc(c, c->scene_allocs, &dt2, size_t(n_leaves) * kMeshLeafTris)))
                 return rc;
             CK(c, cudaMemcpy(d_slot, slot_of_tri.data(), slot_of_tri.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
@@ -191,12 +232,13 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             {
                 // enqueued only: the builds of all meshes share one workspace in stream order
                 StageSpan sp(c, MCPT_STAGE_BVH_BUILD);
-                e = build_mesh_lbvh(c->stream, dp, di, int(md.n_tris), d_slot, lo, hi, dn2, dt2, n_leaves, build_ws, build_ws_bytes,
+                e = build_mesh_lbvh(c->stream, dp, di, int(md.n_tris), d_slot, lo, hi, dn2, dn4, dt2, n_leaves, build_ws, build_ws_bytes,
                                     &launched);
             }
             add_launches(launched);
             CK(c, e);
             M.nodes2 = dn2;
+            M.nodes4 = dn4;
             M.tris2 = dt2;
             M.n_leaves2 = n_leaves;
             continue;
@@ -261,8 +303,10 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     float* d_leaf_bb = nullptr;
     DevNode* d_flat = nullptr;
     DevNode2* d_top2 = nullptr;
-    if ((rc = upload_vec(c, top2, &d_top2))) return rc;
+    DevNode4* d_top4 = nullptr;
+    if ((rc = upload_vec(c, top2, &d_top2)) || (rc = upload_vec(c, top4, &d_top4))) return rc;
     S.top2 = d_top2;
+    S.top4 = d_top4;
     if ((rc = upload_vec(c, top, &d_top)) || (rc = upload_vec(c, prims, &d_prims)) || (rc = upload_vec(c, color, &d_color)) ||
         (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)) || (rc = upload_vec(c, leaf_bb, &d_leaf_bb)) ||
         (rc = upload_vec(c, flat, &d_flat)))

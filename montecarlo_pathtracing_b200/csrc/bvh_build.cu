@@ -12,12 +12,14 @@
 //   4. Karras 2012 radix-tree hierarchy over the leaves, duplicates split by index   k_hierarchy
 //   5. bottom-up box fit with one atomic arrival counter per node; the second arrival writes the
 //      64-byte node {child boxes, child tokens}                                      k_fit
+//   6. every second level folded into four-children nodes for the persistent walk   k_collapse4
 // Boxes are widened like the top-level ones (pack_node, api.cu) so that the FMA slab test of the
 // traversal only culls.
 #include <cub/device/device_radix_sort.cuh>
 #include <cuda_runtime.h>
 
 #include <cfloat>
+#include <climits>
 #include <cstdint>
 
 #include "bvh_build.cuh"
@@ -198,6 +200,77 @@ __global__ void k_single(const float* __restrict__ box_lo, const float* __restri
     nodes[0] = N;
 }
 
+// Fold every second level of the fitted two-children tree into its parent (DevNode4, layout.cuh): a node
+// at even depth becomes a four-children node holding its grandchildren (or a child, where that child
+// is a leaf). Nodes at odd depth are not written: the wide walk never visits them. The boxes are the
+// already widened ones of nodes2.
+constexpr int kTokEmptyBuild = INT_MIN;  // = kTokEmpty (traverse.cuh)
+
+struct Slot4 {
+    float lo[3], hi[3];
+    int tok;
+};
+
+__device__ __forceinline__ void write_node4(DevNode4* __restrict__ out, const Slot4* s, int n_slots) {
+    float lo[3][4], hi[3][4];
+    int tok[4];
+    for (int j = 0; j < 4; ++j) {
+        const bool used = j < n_slots;
+        for (int k = 0; k < 3; ++k) {
+            lo[k][j] = used ? s[j].lo[k] : FLT_MAX;  // an unused slot is rejected by its token (the walk checks it)
+            hi[k][j] = used ? s[j].hi[k] : -FLT_MAX;
+        }
+        tok[j] = used ? s[j].tok : kTokEmptyBuild;
+    }
+    DevNode4 N;
+    N.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]);
+    N.loy = make_float4(lo[1][0], lo[1][1], lo[1][2], lo[1][3]);
+    N.loz = make_float4(lo[2][0], lo[2][1], lo[2][2], lo[2][3]);
+    N.hix = make_float4(hi[0][0], hi[0][1], hi[0][2], hi[0][3]);
+    N.hiy = make_float4(hi[1][0], hi[1][1], hi[1][2], hi[1][3]);
+    N.hiz = make_float4(hi[2][0], hi[2][1], hi[2][2], hi[2][3]);
+    N.tok = make_int4(tok[0], tok[1], tok[2], tok[3]);
+    N.pad = make_int4(0, 0, 0, 0);
+    *out = N;
+}
+
+__device__ __forceinline__ int unpack2(const DevNode2& N, Slot4* s) {
+    s[0].lo[0] = N.lo0.x; s[0].lo[1] = N.lo0.y; s[0].lo[2] = N.lo0.z;
+    s[0].hi[0] = N.hi0.x; s[0].hi[1] = N.hi0.y; s[0].hi[2] = N.hi0.z;
+    s[1].lo[0] = N.lo1.x; s[1].lo[1] = N.lo1.y; s[1].lo[2] = N.lo1.z;
+    s[1].hi[0] = N.hi1.x; s[1].hi[1] = N.hi1.y; s[1].hi[2] = N.hi1.z;
+    s[0].tok = __float_as_int(N.lo0.w);
+    s[1].tok = __float_as_int(N.hi0.w);
+    return 2;
+}
+
+__global__ void k_collapse4(int n, const int* __restrict__ parent, const DevNode2* __restrict__ nodes2, DevNode4* __restrict__ nodes4) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int depth = 0;
+    for (int a = parent[i]; a >= 0; a = parent[a]) ++depth;
+    if (depth & 1) return;
+    Slot4 ch[2], out[4];
+    unpack2(nodes2[i], ch);
+    int m = 0;
+    for (int j = 0; j < 2; ++j) {
+        if (ch[j].tok >= 0) {
+            unpack2(nodes2[ch[j].tok], out + m);
+            m += 2;
+        } else {
+            out[m++] = ch[j];
+        }
+    }
+    write_node4(nodes4 + i, out, m);
+}
+
+// single-leaf mesh: one wide node with that leaf as its only child
+__global__ void k_single4(const DevNode2* __restrict__ nodes2, DevNode4* __restrict__ nodes4) {
+    Slot4 ch[2];
+    unpack2(nodes2[0], ch);
+    write_node4(nodes4, ch, 1);
+}
+
 }  // namespace
 
 namespace {
@@ -249,7 +322,7 @@ size_t lbvh_workspace_bytes(int n_tris, int n_leaves) {
 
 cudaError_t build_mesh_lbvh(cudaStream_t stream, const float* d_pos, const uint32_t* d_idx, int n_tris,
                             const int32_t* d_slot_of_tri, const float lo[3], const float hi[3], DevNode2* d_nodes,
-                            DevTri* d_tris, int n_leaves, void* workspace, size_t workspace_bytes,
+                            DevNode4* d_nodes4, DevTri* d_tris, int n_leaves, void* workspace, size_t workspace_bytes,
                             unsigned long long* launches) {
     const int n = n_leaves;
     Scratch w(workspace, n_tris, n, sort_temp_bytes(n_tris));
@@ -265,13 +338,15 @@ cudaError_t build_mesh_lbvh(cudaStream_t stream, const float* d_pos, const uint3
                                                    w.box_hi, w.leaf_keys);
     if (n == 1) {
         k_single<<<1, 1, 0, stream>>>(w.box_lo, w.box_hi, d_nodes);
-        if (launches) *launches += 3;
+        k_single4<<<1, 1, 0, stream>>>(d_nodes, d_nodes4);
+        if (launches) *launches += 4;
     } else {
         e = cudaMemsetAsync(w.arrivals, 0, sizeof(int) * n, stream);
         if (e != cudaSuccess) return e;
         k_hierarchy<<<(n - 1 + kB - 1) / kB, kB, 0, stream>>>(w.leaf_keys, n, w.children, w.parent);
         k_fit<<<(n + kB - 1) / kB, kB, 0, stream>>>(n, w.children, w.parent, w.box_lo, w.box_hi, w.arrivals, d_nodes);
-        if (launches) *launches += 4;
+        k_collapse4<<<(n - 1 + kB - 1) / kB, kB, 0, stream>>>(n, w.parent, d_nodes, d_nodes4);
+        if (launches) *launches += 5;
     }
     return cudaGetLastError();
 }

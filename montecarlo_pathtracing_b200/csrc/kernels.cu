@@ -219,7 +219,8 @@ template <bool COUNT, bool MESHES>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
                                                     uint32_t len, const HitSink& sink, uint32_t* s_next, uint32_t* s_hits,
                                                     Work& wk) {
-    MCPT_WALK_STACK_DECL(st, (MESHES ? kWalkStack : 32));
+    constexpr bool WIDE = MESHES && (MCPT_WIDE != 0);
+    MCPT_WALK_STACK_DECL(st, (MESHES ? (WIDE ? kWalkStackWide : kWalkStack) : 32));
     float wsave[6];
     WalkState w;
     w.done = true;
@@ -237,7 +238,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
                 first = __shfl_sync(0xffffffffu, first, 0);
                 if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
                     const float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
-                    walk_begin(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+                    walk_begin<WIDE>(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
                     has_ray = true;
                 }
                 exhausted = first + __popc(idle) >= len;
@@ -250,7 +251,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
 #endif
 #pragma unroll 1
         for (int r = 0; r < MCPT_POPS_PER_ITER && has_ray && w.cur == kTokPop && !w.done; ++r)
-            walk_pop_one(w, S, st, wsave);
+            walk_pop_one<WIDE>(w, S, st, wsave);
         const int kind = has_ray ? walk_kind(w) : -1;  // WALK_POP: a dead entry was dropped, pop again next time
         // finished rays: deliver and free the lane
         if (__any_sync(0xffffffffu, kind == WALK_DONE)) {
@@ -258,20 +259,20 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
             if (kind == WALK_DONE) has_ray = false;
         }
 #ifndef MCPT_NODE_STEPS
-#define MCPT_NODE_STEPS 4  // node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 946, 6 -> 930, 8 -> 900 Msamples/s
+#define MCPT_NODE_STEPS (WIDE ? 2 : 4)  // (four-children nodes: 1 -> 930, 2 -> 1003, 3 -> 996 Msamples/s.) Two-children node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 946, 6 -> 930, 8 -> 900 Msamples/s
 #endif
         if (kind == WALK_NODE) {
             // a run of node steps: the lanes at a triangle or a primitive wait, but the dispatch, the
             // ballots and the rarer step kinds are paid once per run (popping inside the run as well
             // was measured: -7 %)
-            walk_node<COUNT>(w, wk, S, st, wsave);
+            walk_node<COUNT, WIDE>(w, wk, S, st, wsave);
 #pragma unroll
             for (int r = 1; r < MCPT_NODE_STEPS; ++r)
-                if (w.cur >= 0) walk_node<COUNT>(w, wk, S, st, wsave);
+                if (w.cur >= 0) walk_node<COUNT, WIDE>(w, wk, S, st, wsave);
         } else if (MESHES && kind == WALK_TRI)
             walk_tri<COUNT>(w, wk, S, sm, st, wsave);
         else if (kind == WALK_PRIM)
-            walk_prim<COUNT, MESHES>(w, wk, S, sm, st, wsave);
+            walk_prim<COUNT, MESHES, WIDE>(w, wk, S, sm, st, wsave);
     }
 }
 

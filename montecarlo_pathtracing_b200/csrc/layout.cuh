@@ -69,11 +69,25 @@ struct DevNode2 {
     float4 hi1;  // child 1 max.xyz
 };
 
+// Four-children node of the persistent walk (MCPT_WIDE): every second level of a two-children tree is
+// folded into its parent, so a ray takes half as many dependent node fetches, loop iterations and
+// stack operations for the same boxes. 128 bytes = one L2 line, boxes stored per component so that one
+// float4 feeds the same slab plane of all four children. Child j: token tok[j] (>= 0 node index,
+// < 0 ~leaf, kTokEmpty: no child).
+struct DevNode4 {
+    float4 lox, loy, loz;  // min of children 0..3
+    float4 hix, hiy, hiz;  // max of children 0..3
+    int4 tok;
+    int4 pad;
+};
+static_assert(sizeof(DevNode4) == 128, "DevNode4 must be 128 bytes");
+
 struct DevMesh {
     const DevNode* nodes;   // 2^depth - 1 interior nodes, heap order   (reference tree; null when rebuilt)
     const DevTri* tris;     // 2^depth leaf slots                       (reference tree; null when rebuilt)
     const DevNode2* nodes2; // GPU-built tree (MCPT_OPT_MESH_BVH), null: walk the reference tree
     const DevTri* tris2;    // its kMeshLeafTris * n_leaves2 triangle slots
+    const DevNode4* nodes4; // the same tree with every second level folded away (indexed like nodes2, sparse)
     const uint32_t* idx;    // 3 * n_tris vertex ids (shading)
     const float* pos;       // 3 * n_verts
     const float* nrm;       // 3 * n_verts
@@ -83,6 +97,7 @@ struct DevMesh {
     int32_t smem_nodes;     // number of staged nodes (2^L - 1)
     int32_t n_leaves2;
     int32_t pad;
+    int64_t pad2;
 };
 
 struct DevScene {
@@ -100,6 +115,7 @@ struct DevScene {
     int32_t persistent;        // 1: tree scenes are traced by persistent warps (MCPT_OPT_PERSISTENT)
     int32_t refill_lanes;      // persistent warps: idle lanes that trigger a refill (MCPT_OPT_REFILL_LANES)
     const DevNode2* top2;      // the top-level tree in two-children node format (persistent warps), root = node 0
+    const DevNode4* top4;      // ... and in four-children format (MCPT_WIDE), root = node 0
     // shared-memory staging plan (in units of DevNode / DevPrim)
     int32_t smem_top_nodes;    // first N top-level nodes staged
     int32_t smem_prims;        // first N primitive records staged

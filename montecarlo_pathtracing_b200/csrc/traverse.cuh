@@ -338,6 +338,17 @@ enum { WALK_DONE = 0, WALK_NODE = 1, WALK_TRI = 2, WALK_PRIM = 3, WALK_POP = 4 }
 constexpr int kTokEmpty = INT_MIN;         // child slot without content
 constexpr int kTokExitMesh = INT_MIN + 1;  // stack marker: back to the world frame
 constexpr int kTokPop = INT_MIN + 2;       // w.cur: the next thing to do is to take an entry off the stack
+// MCPT_WIDE (default 1): on scenes with meshes the persistent walk steps through four-children nodes
+// (DevNode4: every second level of both trees folded away at upload) -- half as many dependent node
+// fetches, loop iterations and stack operations per ray: +5 % on the 1 M-triangle workload (1003 vs 955
+// Msamples/s). Trees of analytic primitives stay on two-children nodes (measured: -6 % with wide nodes on
+// the divergence-stress scene; their rays are short and the primitive step dominates).
+#ifndef MCPT_WIDE
+#define MCPT_WIDE 1
+#endif
+// wide: up to three siblings are pushed per level: 15 levels of the top-level tree (depth <= 30), the
+// mesh-exit marker, 32 levels of a radix tree (<= 64 two-children levels)
+constexpr int kWalkStackWide = 3 * 15 + 1 + 3 * (kLbvhStack / 2);
 constexpr int kWalkStack = 30 + 1 + kLbvhStack;
 
 // The explicit stack of the resumable walk lives in local memory. MCPT_STACK64 (default): one 8-byte
@@ -377,7 +388,7 @@ struct WalkState {
     float slack;
     f3 idir, od;     // culling frame
     float tmax;
-    const DevNode2* nodes;  // node array of the current frame
+    const void* nodes;  // node array of the current frame (DevNode2 or DevNode4)
     int cur;         // token: >= 0 node, < 0 leaf (~primitive in the world frame, ~leaf inside a mesh)
     int sp;
     bool done;
@@ -390,6 +401,7 @@ struct WalkState {
     Best best;
 };
 
+template <bool WIDE>
 MCPT_DEV void walk_begin(WalkState& w, const DevScene& S, f3 O, f3 D) {
     best_reset(w.best);
     w.O = O;
@@ -404,7 +416,7 @@ MCPT_DEV void walk_begin(WalkState& w, const DevScene& S, f3 O, f3 D) {
     w.od = mk3(-O.x * w.idir.x, -O.y * w.idir.y, -O.z * w.idir.z);
     w.slack = 1e-4f * (fabsf(O.x) + fabsf(O.y) + fabsf(O.z)) + 1e-3f;
     w.tmax = FLT_MAX;
-    w.nodes = S.top2;
+    w.nodes = WIDE ? (const void*)S.top4 : (const void*)S.top2;
     w.cur = 0;
     w.sp = 0;
     w.tri_j = 0;
@@ -424,6 +436,7 @@ MCPT_DEV int walk_kind(const WalkState& w) {
 // One entry per iteration of the warp's loop, not a loop of its own: a lane that has several dead
 // entries to drop would otherwise hold the other 31 (measured: 20 % of the kernel's instructions at
 // 2.5 active lanes).
+template <bool WIDE>
 MCPT_DEV void walk_pop_one(WalkState& w, const DevScene& S, const WalkStack& st, const float* wsave) {
     if (w.sp == 0) {
         w.done = true;
@@ -435,7 +448,7 @@ MCPT_DEV void walk_pop_one(WalkState& w, const DevScene& S, const WalkStack& st,
     st.get(w.sp, tok, tok_t);
     if (tok == kTokExitMesh) {
         w.mesh_prim = -1;
-        w.nodes = S.top2;
+        w.nodes = WIDE ? (const void*)S.top4 : (const void*)S.top2;
         w.idir = mk3(wsave[0], wsave[1], wsave[2]);
         w.od = mk3(wsave[3], wsave[4], wsave[5]);
         w.tmax = (w.best.h.prim >= 0) ? (w.best.h.dist * 1.0001f + w.slack) : FLT_MAX;
@@ -445,9 +458,54 @@ MCPT_DEV void walk_pop_one(WalkState& w, const DevScene& S, const WalkStack& st,
     }
 }
 
+// one child of a four-children node: entry parameter of the conservative slab test, +inf if culled
+MCPT_DEV float slab_entry4(float lx, float ly, float lz, float hx, float hy, float hz, int tok, f3 idir, f3 od, float tmax) {
+    const float tx0 = __fmaf_rn(lx, idir.x, od.x), tx1 = __fmaf_rn(hx, idir.x, od.x);
+    const float ty0 = __fmaf_rn(ly, idir.y, od.y), ty1 = __fmaf_rn(hy, idir.y, od.y);
+    const float tz0 = __fmaf_rn(lz, idir.z, od.z), tz1 = __fmaf_rn(hz, idir.z, od.z);
+    const float tn = fmaxf(fmaxf(fminf(tx0, tx1), fminf(ty0, ty1)), fmaxf(fminf(tz0, tz1), 0.0f));
+    const float tf = fminf(fminf(fmaxf(tx0, tx1), fmaxf(ty0, ty1)), fminf(fmaxf(tz0, tz1), tmax));
+    return (tn <= tf && tok != kTokEmpty) ? tn : __int_as_float(0x7f800000);
+}
+MCPT_DEV void order2(float& ta, int& ca, float& tb, int& cb) {
+    const bool sw = tb < ta;
+    const float t = sw ? ta : tb;
+    const int c = sw ? ca : cb;
+    ta = sw ? tb : ta;
+    ca = sw ? cb : ca;
+    tb = t;
+    cb = c;
+}
+
+// One four-children node: the nearest child that can hold a closer hit becomes the current token, the
+// others are pushed farthest first with their entry parameters.
 template <bool COUNT>
-MCPT_DEV void walk_node(WalkState& w, Work& wk, const DevScene& S, const WalkStack& st, const float* wsave) {
-    const DevNode2* np = w.nodes + w.cur;
+MCPT_DEV void walk_node4(WalkState& w, Work& wk, const DevScene& S, const WalkStack& st, const float* wsave) {
+    const DevNode4* np = static_cast<const DevNode4*>(w.nodes) + w.cur;
+    const float4 lox = __ldg(&np->lox), loy = __ldg(&np->loy), loz = __ldg(&np->loz);
+    const float4 hix = __ldg(&np->hix), hiy = __ldg(&np->hiy), hiz = __ldg(&np->hiz);
+    const int4 tok = __ldg(&np->tok);
+    int c0 = tok.x, c1 = tok.y, c2 = tok.z, c3 = tok.w;
+    float t0 = slab_entry4(lox.x, loy.x, loz.x, hix.x, hiy.x, hiz.x, c0, w.idir, w.od, w.tmax);
+    float t1 = slab_entry4(lox.y, loy.y, loz.y, hix.y, hiy.y, hiz.y, c1, w.idir, w.od, w.tmax);
+    float t2 = slab_entry4(lox.z, loy.z, loz.z, hix.z, hiy.z, hiz.z, c2, w.idir, w.od, w.tmax);
+    float t3 = slab_entry4(lox.w, loy.w, loz.w, hix.w, hiy.w, hiz.w, c3, w.idir, w.od, w.tmax);
+    if (COUNT) wk.boxes += 4;
+    w.tri_j = 0;
+    order2(t0, c0, t1, c1);
+    order2(t2, c2, t3, c3);
+    order2(t0, c0, t2, c2);
+    order2(t1, c1, t3, c3);
+    order2(t1, c1, t2, c2);
+    const float inf = __int_as_float(0x7f800000);
+    if (t3 < inf) st.put(w.sp++, c3, t3);
+    if (t2 < inf) st.put(w.sp++, c2, t2);
+    if (t1 < inf) st.put(w.sp++, c1, t1);
+    w.cur = (t0 < inf) ? c0 : kTokPop;
+}
+template <bool COUNT>
+MCPT_DEV void walk_node2(WalkState& w, Work& wk, const DevScene& S, const WalkStack& st, const float* wsave) {
+    const DevNode2* np = static_cast<const DevNode2*>(w.nodes) + w.cur;
     const float4 lo0 = __ldg(&np->lo0), hi0 = __ldg(&np->hi0), lo1 = __ldg(&np->lo1), hi1 = __ldg(&np->hi1);
     const int c0 = __float_as_int(lo0.w), c1 = __float_as_int(hi0.w);
     float t0, t1;
@@ -465,6 +523,14 @@ MCPT_DEV void walk_node(WalkState& w, Work& wk, const DevScene& S, const WalkSta
     } else {
         w.cur = kTokPop;
     }
+}
+
+template <bool COUNT, bool WIDE>
+MCPT_DEV void walk_node(WalkState& w, Work& wk, const DevScene& S, const WalkStack& st, const float* wsave) {
+    if (WIDE)
+        walk_node4<COUNT>(w, wk, S, st, wsave);
+    else
+        walk_node2<COUNT>(w, wk, S, st, wsave);
 }
 
 template <bool COUNT>
@@ -489,7 +555,7 @@ MCPT_DEV void walk_tri(WalkState& w, Work& wk, const DevScene& S, const SmemScen
     if (++w.tri_j == kMeshLeafTris) w.cur = kTokPop;
 }
 
-template <bool COUNT, bool MESHES>
+template <bool COUNT, bool MESHES, bool WIDE>
 MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemScene& sm, const WalkStack& st, float* wsave) {
     const int pid = ~w.cur;
     const DevPrim* pp = (pid < S.smem_prims) ? (sm.prims + pid) : (S.prims + pid);
@@ -512,7 +578,7 @@ MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemSce
             const DevMesh& M = S.meshes[pp->mesh];
             st.put(w.sp, kTokExitMesh, 0.0f);
             ++w.sp;
-            w.nodes = M.nodes2;
+            w.nodes = WIDE ? (const void*)M.nodes4 : (const void*)M.nodes2;
             w.tris2 = M.tris2;
             w.mesh_prim = pid;
             w.tslot = pp->slot;
