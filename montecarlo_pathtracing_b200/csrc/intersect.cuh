@@ -82,7 +82,16 @@ MCPT_DEV bool origin_inside_leaf_box(const float* __restrict__ bb, f3 O) {
 }
 
 // raytracer_func.frag:398-441
-MCPT_DEV void sphere_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot) {
+// The intersectors only find the candidate parameters (a1 first, then a2, in shader order); prim_test
+// offers them in ONE place after its type switch, so the closest-hit registers are updated by a single
+// copy of offer_at instead of one inlined copy per primitive type.
+struct Cand {
+    float a1, a2;
+    int cl;        // face id `dir` of the candidate(s)
+    bool c1, c2;
+};
+
+MCPT_DEV void sphere_test(Cand& k, f3 O, f3 D) {
     float OO = dot3(O, O);
     float OD = dot3(O, D);
     float D2 = dot3(D, D);
@@ -91,31 +100,34 @@ MCPT_DEV void sphere_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, 
         float sq = sqrtf(delta4);
         float a = -(OD + sq) / D2;
         if (a > MCPT_EPSILON) {
-            offer_at(b, fwd, O, D, a, Ow, prim, 0, tslot, 0);
+            k.a1 = a;
+            k.c1 = true;
             // The far root loses against the near one under the shader's strict '<' whenever the
             // two are separated by more than rounding noise; it is evaluated only when they are not.
             if (a > 1e-3f && 2.0f * sq > 1e-3f * (a * D2)) return;
         }
         a = -(OD - sq) / D2;
-        if (a > MCPT_EPSILON) offer_at(b, fwd, O, D, a, Ow, prim, 0, tslot, 0);
+        if (a > MCPT_EPSILON) {
+            k.a2 = a;
+            k.c2 = true;
+        }
     }
 }
 
 // raytracer_func.frag:443-470. One-sided (D.z < -EPSILON); note there is no
 // a > 0 test in the shader, so there is none here.
-MCPT_DEV void quad_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot, const float* leaf_bb) {
+MCPT_DEV void quad_test(Cand& k, f3 O, f3 D, f3 Ow, const float* leaf_bb) {
     if (D.z > -MCPT_EPSILON) return;
     float a = -O.z / D.z;
     if (!(a > 0.0f) && !origin_inside_leaf_box(leaf_bb, Ow)) return;  // hit behind the origin
     f3 Pl = O + D * a;
     if (fabsf(Pl.x) > 1.0f || fabsf(Pl.y) > 1.0f) return;
-    f3 Pg = xform_point(fwd, Pl);
-    float dist = distance3(Ow, Pg);
-    offer(b, dist, Pl, prim, 0, tslot, 0);
+    k.a1 = a;  // offer_at rebuilds Pl = O + D * a with the same two roundings
+    k.c1 = true;
 }
 
 // raytracer_func.frag:472-512: nearest of the six faces, face id -> dir
-MCPT_DEV void cube_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot) {
+MCPT_DEV void cube_test(Cand& k, f3 O, f3 D) {
     float al = MCPT_FLT_MAX;
     int cl = 0;
 #pragma unroll
@@ -134,11 +146,15 @@ MCPT_DEV void cube_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, in
             }
         }
     }
-    if (al < MCPT_FLT_MAX) offer_at(b, fwd, O, D, al, Ow, prim, cl, tslot, 0);
+    if (al < MCPT_FLT_MAX) {
+        k.a1 = al;
+        k.cl = cl;
+        k.c1 = true;
+    }
 }
 
 // raytracer_func.frag:515-577: caps z = -1 (dir 0), z = +1 (dir 1), side (dir 2)
-MCPT_DEV void cylinder_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot) {
+MCPT_DEV void cylinder_test(Cand& k, f3 O, f3 D) {
     int cl = -1;
     float al = MCPT_FLT_MAX;
     if (fabsf(D.z) > MCPT_EPSILON) {
@@ -173,13 +189,17 @@ MCPT_DEV void cylinder_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim
             }
         }
     }
-    if (al < MCPT_FLT_MAX) offer_at(b, fwd, O, D, al, Ow, prim, cl, tslot, 0);
+    if (al < MCPT_FLT_MAX) {
+        k.a1 = al;
+        k.cl = cl;
+        k.c1 = true;
+    }
 }
 
 // raytracer_func.frag:579-640: cap z = -1 (dir 0) and the quadric with k = 0.8,
 // apex at z = +1 (dir 2); as in the shader the quadric roots are not tested for
 // positivity.
-MCPT_DEV void cone_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, int tslot, const float* leaf_bb) {
+MCPT_DEV void cone_test(Cand& k, f3 O, f3 D, f3 Ow, const float* leaf_bb) {
     int cl = -1;
     float tl = MCPT_FLT_MAX;
     if (fabsf(D.z) > MCPT_EPSILON) {
@@ -212,7 +232,9 @@ MCPT_DEV void cone_test(Best& b, const Aff& fwd, f3 O, f3 D, f3 Ow, int prim, in
     }
     if (tl < MCPT_FLT_MAX) {
         if (!(tl > 0.0f) && !origin_inside_leaf_box(leaf_bb, Ow)) return;  // hit behind the origin
-        offer_at(b, fwd, O, D, tl, Ow, prim, cl, tslot, 0);
+        k.a1 = tl;
+        k.cl = cl;
+        k.c1 = true;
     }
 }
 

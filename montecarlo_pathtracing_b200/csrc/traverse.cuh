@@ -241,6 +241,10 @@ MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p,
     if (COUNT) ++wk.prims;
     f3 Oi = xform_point(inv, O);
     f3 Di = normalize3(xform_vector(inv, D));
+    Cand k;
+    k.a1 = k.a2 = 0.0f;
+    k.cl = 0;
+    k.c1 = k.c2 = false;
     switch (type) {
         case MCPT_PRIM_MESH:
             if (MESHES) {
@@ -251,13 +255,15 @@ MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p,
                     mesh_walk<COUNT>(wk, M, sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
             }
             break;
-        case MCPT_PRIM_SPHERE: sphere_test(best, fwd, Oi, Di, O, p, tslot); break;
-        case MCPT_PRIM_CUBE: cube_test(best, fwd, Oi, Di, O, p, tslot); break;
-        case MCPT_PRIM_CYLINDER: cylinder_test(best, fwd, Oi, Di, O, p, tslot); break;
-        case MCPT_PRIM_CONE: cone_test(best, fwd, Oi, Di, O, p, tslot, S.leaf_bb + 6 * p); break;
-        case MCPT_PRIM_ORIENTED_QUAD: quad_test(best, fwd, Oi, Di, O, p, tslot, S.leaf_bb + 6 * p); break;
+        case MCPT_PRIM_SPHERE: sphere_test(k, Oi, Di); break;
+        case MCPT_PRIM_CUBE: cube_test(k, Oi, Di); break;
+        case MCPT_PRIM_CYLINDER: cylinder_test(k, Oi, Di); break;
+        case MCPT_PRIM_CONE: cone_test(k, Oi, Di, O, S.leaf_bb + 6 * p); break;
+        case MCPT_PRIM_ORIENTED_QUAD: quad_test(k, Oi, Di, O, S.leaf_bb + 6 * p); break;
         default: break;
     }
+    if (k.c1) offer_at(best, fwd, Oi, Di, k.a1, O, p, k.cl, tslot, 0);
+    if (k.c2) offer_at(best, fwd, Oi, Di, k.a2, O, p, k.cl, tslot, 0);
 }
 
 // traverse_all_bvh, raytracer_func.frag:777-781. D need not be unit length.
