@@ -30,11 +30,8 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
         c->counters_len = 0;
         Wavefront& w = c->wf;
         int rc;
-        if ((rc = dev_alloc(c, c->wf_allocs, &w.ray_o, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.ray_d, slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &w.hit_a, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.hit_b, slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &w.attenu, slots)) || (rc = dev_alloc(c, c->wf_allocs, &w.total, slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &w.keep_n, slots)) ||
-            (rc = dev_alloc(c, c->wf_allocs, &w.keep_p, slots)) ||
+        char* records = nullptr;
+        if ((rc = dev_alloc(c, c->wf_allocs, &records, size_t(slots) * kPathRecordBytes)) ||
             (rc = dev_alloc(c, c->wf_allocs, &c->queue[0], queue_entries(c, slots))) ||
             (rc = dev_alloc(c, c->wf_allocs, &c->queue[1], queue_entries(c, slots))) ||
             (rc = dev_alloc(c, c->wf_allocs, &c->queue[2], queue_entries(c, slots)))) {
@@ -43,7 +40,9 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
             return rc;
         }
         // path tags live in attenu.w: start from a state no batch generation can match
-        CK(c, cudaMemsetAsync(w.attenu, 0, sizeof(float4) * slots, c->stream));
+        w.rec = records;
+        w.plane = size_t(slots) * 32;
+        CK(c, cudaMemsetAsync(w.rec, 0, size_t(slots) * kPathRecordBytes, c->stream));
         c->batch_gen = 0;
         c->wf_capacity = slots;
         trim_cache(c);
@@ -190,7 +189,7 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
         const uint32_t slots = npix * uint32_t(nb);
         // a fresh generation per batch: stale tags of earlier batches never match (layout.cuh)
         if (++c->batch_gen >= 0x7ffffff0u) {
-            CK(c, cudaMemsetAsync(c->wf.attenu, 0, sizeof(float4) * c->wf_capacity, c->stream));
+            CK(c, cudaMemsetAsync(c->wf.rec, 0, size_t(c->wf_capacity) * kPathRecordBytes, c->stream));
             c->batch_gen = 1;
         }
         c->prm.batch = c->batch_gen;

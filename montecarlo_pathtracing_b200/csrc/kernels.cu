@@ -93,8 +93,7 @@ __global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam
         // attenuation 0.8, total 0 and the RNG seed of a fresh path are implied (k_shade first bounce,
         // k_accumulate): nothing else is initialised here. (Leaving out the origin too -- it is the
         // camera's for every primary ray -- saved 32 B per path and no time: measured, dropped.)
-        wf.ray_o[p] = make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f);
-        wf.ray_d[p] = make_float4(dir.x, dir.y, dir.z, 0.0f);
+        wf.store_ray(p, make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f), make_float4(dir.x, dir.y, dir.z, 0.0f));
     }
 }
 
@@ -183,21 +182,20 @@ __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, 
                                         bool valid, const Best& best) {
     if (sink.exit_mode) {
         if (valid) {
-            const float4 d4 = wf.ray_d[p];
-            const float4 n4 = wf.keep_n[p], p4 = wf.keep_p[p];
+            const float4 d4 = wf.load_ray_d(p);
+            float4 n4, p4;
+            wf.load_keep(p, n4, p4);
             f3 N = mk3(n4.x, n4.y, n4.z), P = mk3(p4.x, p4.y, p4.z);
             intersection_info(S, best.h.prim, best.h.sub, best.h.pl, sink.flat_face, N, P);
             const f3 nO = P + N * MCPT_BIAS;
             const f3 nD = refract3(mk3(d4.x, d4.y, d4.z), -N, 1.0f / sink.refract_ind);
-            wf.ray_o[p] = make_float4(nO.x, nO.y, nO.z, 0.0f);
-            wf.ray_d[p] = make_float4(nD.x, nD.y, nD.z, d4.w);  // w: the path's RNG draw count
+            wf.store_ray(p, make_float4(nO.x, nO.y, nO.z, 0.0f), make_float4(nD.x, nD.y, nD.z, d4.w));  // w: the path's RNG draw count
         }
         return;
     }
     const bool hit = valid && best.h.prim >= 0;
     if (hit || (valid && !sink.hitq.items)) {
-        wf.hit_a[p] = make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist);
-        wf.hit_b[p] = make_int2(best.h.prim, best.h.sub);
+        wf.store_hit(p, make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist), make_int2(best.h.prim, best.h.sub));
     }
     if (sink.hitq.items) warp_append(s_count, sink.hitq, hit, p);
 }
@@ -237,7 +235,8 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
                 if (lane == 0) first = atomicAdd(s_next, uint32_t(__popc(idle)));
                 first = __shfl_sync(0xffffffffu, first, 0);
                 if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
-                    const float4 o4 = wf.ray_o[p], d4 = wf.ray_d[p];
+                    float4 o4, d4;
+                    wf.load_ray(p, o4, d4);
                     walk_begin<WIDE>(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
                     has_ray = true;
                 }
@@ -299,10 +298,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
         Best best;
         {
             float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
-            if (valid) {
-                o4 = wf.ray_o[p];
-                d4 = wf.ray_d[p];
-            }
+            if (valid) wf.load_ray(p, o4, d4);
             if (FLAT)
                 scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
             else if (valid)

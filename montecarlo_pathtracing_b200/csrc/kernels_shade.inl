@@ -35,11 +35,14 @@ __global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, D
     for (uint32_t base = 0; base < len; base += kBlock) {
         uint32_t kind = 0, p;  // kind: 0 ended, 1 goes on, 2 goes on after an interior traversal
         if (queue_item(qin, base + threadIdx.x, len, p)) {
-            const float4 ha = wf.hit_a[p];
-            const int2 hb = wf.hit_b[p];
-            const float4 d4 = wf.ray_d[p];
-            float4 o4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-            if (!FAST) o4 = wf.ray_o[p];  // only E = normalize(O - P) needs it (see bounce())
+            float4 ha;
+            int2 hb;
+            wf.load_hit(p, ha, hb);
+            float4 o4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d4;
+            if (FAST)
+                d4 = wf.load_ray_d(p);
+            else
+                wf.load_ray(p, o4, d4);  // only E = normalize(O - P) needs the origin (see bounce())
             const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
             const uint32_t n_draws = first_bounce ? 0u : __float_as_uint(d4.w);
             if (prm.mode != 0) {
@@ -58,15 +61,14 @@ __global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, D
                         res = mk3(col.x * r, col.y * r, col.z * r);
                     }
                 }
-                wf.total[p] = make_float4(res.x, res.y, res.z, 0.0f);
-                wf.attenu[p] = make_float4(0.0f, 0.0f, 0.0f, tag_ended);
+                wf.store_rad(p, make_float4(0.0f, 0.0f, 0.0f, tag_ended), make_float4(res.x, res.y, res.z, 0.0f));
             } else {
                 // a fresh path starts with total = 0 and attenuation 0.8 (tp/montecarlo.frag:105-107)
                 f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
                 if (!first_bounce) {
-                    const float4 t4 = wf.total[p];
+                    float4 a4, t4;
+                    wf.load_rad(p, a4, t4);
                     total = mk3(t4.x, t4.y, t4.z);
-                    const float4 a4 = wf.attenu[p];
                     attenu = mk3(a4.x, a4.y, a4.z);
                 }
                 ++my_segments;
@@ -78,22 +80,17 @@ __global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, D
                 const float4 col = __ldg(S.color + hb.x);
                 BounceOut bo = bounce<FAST>(O, D, N, P, mat, col, attenu, total, seed, prm.refract_ind);
                 if (bo.kind == 0) {
-                    wf.total[p] = make_float4(total.x, total.y, total.z, 0.0f);
-                    wf.attenu[p] = make_float4(0.0f, 0.0f, 0.0f, tag_ended);
+                    wf.store_rad(p, make_float4(0.0f, 0.0f, 0.0f, tag_ended), make_float4(total.x, total.y, total.z, 0.0f));
                 } else if (last_bounce) {
                     // a path still alive after the last iteration returns vec3(0) (tp/montecarlo.frag:178)
-                    wf.total[p] = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
-                    wf.attenu[p] = make_float4(0.0f, 0.0f, 0.0f, tag_ended);
+                    wf.store_rad(p, make_float4(0.0f, 0.0f, 0.0f, tag_ended), make_float4(0.0f, 0.0f, 0.0f, 0.0f));
                 } else {
                     const uint32_t nd = n_draws + draws_between(seed0, seed);
-                    wf.ray_o[p] = make_float4(bo.nO.x, bo.nO.y, bo.nO.z, 0.0f);
-                    wf.ray_d[p] = make_float4(bo.nD.x, bo.nD.y, bo.nD.z, __uint_as_float(nd));
-                    wf.attenu[p] = make_float4(bo.new_att.x, bo.new_att.y, bo.new_att.z, tag_alive);
-                    wf.total[p] = make_float4(total.x, total.y, total.z, 0.0f);
-                    if (bo.kind == 2) {
-                        wf.keep_n[p] = make_float4(N.x, N.y, N.z, 0.0f);
-                        wf.keep_p[p] = make_float4(P.x, P.y, P.z, 0.0f);
-                    }
+                    wf.store_ray(p, make_float4(bo.nO.x, bo.nO.y, bo.nO.z, 0.0f),
+                                 make_float4(bo.nD.x, bo.nD.y, bo.nD.z, __uint_as_float(nd)));
+                    wf.store_rad(p, make_float4(bo.new_att.x, bo.new_att.y, bo.new_att.z, tag_alive),
+                                 make_float4(total.x, total.y, total.z, 0.0f));
+                    if (bo.kind == 2) wf.store_keep(p, make_float4(N.x, N.y, N.z, 0.0f), make_float4(P.x, P.y, P.z, 0.0f));
                     kind = uint32_t(bo.kind);
                 }
             }
@@ -144,16 +141,16 @@ __global__ void __launch_bounds__(kBlock) k_shade_exit(DevScene S, DevParams prm
     for (uint32_t i = threadIdx.x; i < len; i += kBlock) {
         uint32_t p;
         if (!queue_item(qin, i, len, p)) continue;
-        const float4 ha = wf.hit_a[p];
-        const int2 hb = wf.hit_b[p];
-        const float4 d4 = wf.ray_d[p];
-        const float4 n4 = wf.keep_n[p], p4 = wf.keep_p[p];
+        float4 ha, n4, p4;
+        int2 hb;
+        wf.load_hit(p, ha, hb);
+        const float4 d4 = wf.load_ray_d(p);
+        wf.load_keep(p, n4, p4);
         f3 N = mk3(n4.x, n4.y, n4.z), P = mk3(p4.x, p4.y, p4.z);
         intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
         f3 nO = P + N * MCPT_BIAS;
         f3 nD = refract3(mk3(d4.x, d4.y, d4.z), -N, 1.0f / prm.refract_ind);
-        wf.ray_o[p] = make_float4(nO.x, nO.y, nO.z, 0.0f);
-        wf.ray_d[p] = make_float4(nD.x, nD.y, nD.z, d4.w);  // w: the path's RNG draw count
+        wf.store_ray(p, make_float4(nO.x, nO.y, nO.z, 0.0f), make_float4(nD.x, nD.y, nD.z, d4.w));  // w: the path's RNG draw count
     }
 }
 
@@ -175,20 +172,19 @@ __global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __r
         float4 a = accum[pix];
         for (int k = 0; k < n_passes; ++k) {
             const uint64_t p = uint64_t(k) * npix + pix;
-            const float4 a4 = wf.attenu[p];
+            float4 a4, t4;
+            wf.load_rad(p, a4, t4);
             const uint32_t tag = __float_as_uint(a4.w);
             f3 r;
             if (tag == 2u * batch + 1u) {
-                const float4 t4 = wf.total[p];
                 r = mk3(t4.x, t4.y, t4.z);
             } else {
                 f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
                 if (tag == 2u * batch) {
-                    const float4 t4 = wf.total[p];
                     total = mk3(t4.x, t4.y, t4.z);
                     attenu = mk3(a4.x, a4.y, a4.z);
                 }
-                const float4 d4 = wf.ray_d[p];
+                const float4 d4 = wf.load_ray_d(p);
                 r = sky(total, attenu, mk3(d4.x, d4.y, d4.z));
             }
             a.x += r.x;

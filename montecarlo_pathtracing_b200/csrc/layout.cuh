@@ -146,17 +146,80 @@ struct DevParams {
     uint32_t batch;    // generation of the batch being traced (path tags, see Wavefront::attenu)
 };
 
-// SoA wavefront state, one entry per path slot
+// Wavefront state: one 128-byte record per path slot, four 32-byte sectors, each moved by ONE 256-bit
+// load or store (LDG / STG.E.ENL2.256 on sm_100a) so that every access of a stage is a whole sector:
+//   sector 0  ray     origin.xyz | direction.xyz, w = number of RNG draws the path has consumed (uint bits)
+//                     read by k_traverse, written by k_raygen / k_shade / the exit of interior rays
+//   sector 1  hit     pl.xyz, dist | prim, sub        written by k_traverse, read by k_shade
+//   sector 2  rad     attenuation.xyz, w = path tag | radiance gathered so far (`total`)
+//                     tag (uint bits): 2*batch: alive, 2*batch + 1: ended, the value random_path returns is
+//                     `total`; anything else: never shaded in this batch. k_shade, k_accumulate
+//   sector 3  keep    N | P of the entry hit (interior rays): written by k_shade, read where they exit
+// After the first bounce paths are reached through index queues. With one array per field (the layout this
+// replaces) every 16-byte access of a scattered path moved a 32-byte sector of which half belonged to a
+// neighbour, and a path's state sat in seven DRAM pages: k_shade 11.6 -> 10.1 ms per C2 step with records.
+constexpr size_t kPathRecordBytes = 128;
+struct alignas(32) PathSector {
+    float4 a, b;
+};
+#ifndef MCPT_PATH_INTERLEAVED
+#define MCPT_PATH_INTERLEAVED 0  // 1: the four sectors of a path side by side (one 128-byte record per path)
+#endif
 struct Wavefront {
-    float4* ray_o;     // origin.xyz
-    float4* ray_d;     // direction.xyz, w = number of RNG draws the path has consumed (uint bits)
-    float4* hit_a;     // pl.xyz, dist
-    int2* hit_b;       // prim, sub
-    float4* attenu;    // attenuation.xyz, w = path tag (uint bits): 2*batch: alive, 2*batch + 1: ended, the value
-                       // random_path returns is `total`; anything else: never shaded in this batch
-    float4* total;     // radiance gathered so far .xyz
-    float4* keep_n;    // N of the entry hit (interior rays)
-    float4* keep_p;    // P of the entry hit (interior rays)
+    char* rec;        // 128 bytes per slot
+    size_t plane;     // bytes between the sector arrays (0 when interleaved)
+    __device__ __forceinline__ PathSector* sec(size_t p, int s) const {
+#if MCPT_PATH_INTERLEAVED
+        return reinterpret_cast<PathSector*>(rec + p * kPathRecordBytes + 32 * s);
+#else
+        return reinterpret_cast<PathSector*>(rec + plane * s + p * 32);
+#endif
+    }
+    __device__ __forceinline__ void load_ray(size_t p, float4& o, float4& d) const {
+        const PathSector v = *sec(p, 0);
+        o = v.a;
+        d = v.b;
+    }
+    __device__ __forceinline__ float4 load_ray_d(size_t p) const { return sec(p, 0)->b; }
+    __device__ __forceinline__ void store_ray(size_t p, float4 o, float4 d) const {
+        PathSector v;
+        v.a = o;
+        v.b = d;
+        *sec(p, 0) = v;
+    }
+    __device__ __forceinline__ void load_hit(size_t p, float4& ha, int2& hb) const {
+        const PathSector v = *sec(p, 1);
+        ha = v.a;
+        hb = make_int2(__float_as_int(v.b.x), __float_as_int(v.b.y));
+    }
+    __device__ __forceinline__ void store_hit(size_t p, float4 ha, int2 hb) const {
+        PathSector v;
+        v.a = ha;
+        v.b = make_float4(__int_as_float(hb.x), __int_as_float(hb.y), 0.0f, 0.0f);
+        *sec(p, 1) = v;
+    }
+    __device__ __forceinline__ void load_rad(size_t p, float4& attenu, float4& total) const {
+        const PathSector v = *sec(p, 2);
+        attenu = v.a;
+        total = v.b;
+    }
+    __device__ __forceinline__ void store_rad(size_t p, float4 attenu, float4 total) const {
+        PathSector v;
+        v.a = attenu;
+        v.b = total;
+        *sec(p, 2) = v;
+    }
+    __device__ __forceinline__ void load_keep(size_t p, float4& n, float4& pt) const {
+        const PathSector v = *sec(p, 3);
+        n = v.a;
+        pt = v.b;
+    }
+    __device__ __forceinline__ void store_keep(size_t p, float4 n, float4 pt) const {
+        PathSector v;
+        v.a = n;
+        v.b = pt;
+        *sec(p, 3) = v;
+    }
 };
 
 }  // namespace mcpt

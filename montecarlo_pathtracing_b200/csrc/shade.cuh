@@ -213,29 +213,33 @@ MCPT_DEV BounceOut bounce(f3 O, f3 D, f3 N, f3 P, float4 mat, float4 col, f3 att
         return out;
     }
     f3 mixed = mix3(attenu, c3, mat.x);
+    // Which of the four material cases (tp/montecarlo.frag:139-172) applies is decided first, so that the
+    // reflective and the transparent formulas -- and the second random_ray -- exist once in the code,
+    // not once per case that uses them. The draw order is the shader's: the reflect / refract choice of
+    // the transparent+reflective case comes before the draws of the reflected ray.
+    bool reflective = false, interior = false, refract_entry = false;
     if (mat.x > 0.0f && col.w == 1.0f) {
+        reflective = true;
+    } else if (col.w < 1.0f && mat.x == 0.0f) {
+        interior = true;
+        refract_entry = true;
+    } else if (col.w < 1.0f && mat.x > 0.0f) {
+        float r = random_float(seed);
+        if (r > 0.5f)
+            reflective = true;
+        else
+            interior = true;  // D is not refracted on entry (:160-165)
+    }
+    if (reflective) {
         out.new_att = c3 * attenu + attenu * col.w * rs * spec * mixed;
         out.nO = P + N * MCPT_BIAS;
         out.nD = random_ray<FAST>(reflect3(D, N), 1.0f - mat.x * mat.y, seed);
         out.kind = 1;
-    } else if (col.w < 1.0f && mat.x == 0.0f) {
+    } else if (interior) {
         out.new_att = c3 * attenu + attenu * (1.0f - col.w) * (1.0f - rs) * spec * mixed;
         out.nO = P - N * MCPT_BIAS;
-        out.nD = refract3(D, N, refract_ind);
+        out.nD = refract_entry ? refract3(D, N, refract_ind) : D;
         out.kind = 2;
-    } else if (col.w < 1.0f && mat.x > 0.0f) {
-        float r = random_float(seed);
-        if (r > 0.5f) {
-            out.new_att = c3 * attenu + attenu * col.w * rs * spec * mixed;
-            out.nO = P + N * MCPT_BIAS;
-            out.nD = random_ray<FAST>(reflect3(D, N), 1.0f - mat.x * mat.y, seed);
-            out.kind = 1;
-        } else {
-            out.new_att = c3 * attenu + attenu * (1.0f - col.w) * (1.0f - rs) * spec * mixed;
-            out.nO = P - N * MCPT_BIAS;
-            out.nD = D;
-            out.kind = 2;
-        }
     } else {
         out.new_att = c3 * attenu + attenu * spec * mixed;
         out.nO = P + N * MCPT_BIAS;
