@@ -179,7 +179,7 @@ struct HitSink {
 };
 
 __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, const HitSink& sink, uint32_t* s_count, uint32_t p,
-                                        bool valid, const Best& best) {
+                                        bool valid, const Best& best, f3 D) {
     if (sink.exit_mode) {
         if (valid) {
             const float4 d4 = wf.load_ray_d(p);
@@ -195,7 +195,7 @@ __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, 
     }
     const bool hit = valid && best.h.prim >= 0;
     if (hit || (valid && !sink.hitq.items)) {
-        wf.store_hit(p, make_float4(best.h.pl.x, best.h.pl.y, best.h.pl.z, best.h.dist), make_int2(best.h.prim, best.h.sub));
+        wf.store_hit(p, best.h.pl, best.h.prim, best.h.sub, D);
     }
     if (sink.hitq.items) warp_append(s_count, sink.hitq, hit, p);
 }
@@ -254,7 +254,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
         const int kind = has_ray ? walk_kind(w) : -1;  // WALK_POP: a dead entry was dropped, pop again next time
         // finished rays: deliver and free the lane
         if (__any_sync(0xffffffffu, kind == WALK_DONE)) {
-            deliver(S, wf, sink, s_hits, p, kind == WALK_DONE, w.best);
+            deliver(S, wf, sink, s_hits, p, kind == WALK_DONE, w.best, w.D);
             if (kind == WALK_DONE) has_ray = false;
         }
 #ifndef MCPT_NODE_STEPS
@@ -296,15 +296,13 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
         uint32_t p;
         const bool valid = queue_item(qin, base + threadIdx.x, len, p);
         Best best;
-        {
-            float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
-            if (valid) wf.load_ray(p, o4, d4);
-            if (FLAT)
-                scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
-            else if (valid)
-                scene_walk<COUNT, MESHES>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
-        }
-        deliver(S, wf, sink, &s_hits, p, valid, best);
+        float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
+        if (valid) wf.load_ray(p, o4, d4);
+        if (FLAT)
+            scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
+        else if (valid)
+            scene_walk<COUNT, MESHES>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
+        deliver(S, wf, sink, &s_hits, p, valid, best, mk3(d4.x, d4.y, d4.z));
     }
     if (ray_counter && threadIdx.x == 0) {
         // rays this CTA traced: its region length, or its share of the identity queue (last tile cut at n)

@@ -35,23 +35,32 @@ __global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, D
     for (uint32_t base = 0; base < len; base += kBlock) {
         uint32_t kind = 0, p;  // kind: 0 ended, 1 goes on, 2 goes on after an interior traversal
         if (queue_item(qin, base + threadIdx.x, len, p)) {
-            float4 ha;
+            f3 pl, D;
             int2 hb;
-            wf.load_hit(p, ha, hb);
-            float4 o4 = make_float4(0.0f, 0.0f, 0.0f, 0.0f), d4;
-            if (FAST)
-                d4 = wf.load_ray_d(p);
-            else
+            wf.load_hit(p, pl, hb.x, hb.y, D);  // the direction of the ray that hit comes with the record
+            f3 O = mk3(0.0f, 0.0f, 0.0f);
+            if (!FAST) {
+                float4 o4, d4;
                 wf.load_ray(p, o4, d4);  // only E = normalize(O - P) needs the origin (see bounce())
-            const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
-            const uint32_t n_draws = first_bounce ? 0u : __float_as_uint(d4.w);
+                O = mk3(o4.x, o4.y, o4.z);
+            }
+            // a fresh path starts with total = 0 and attenuation 0.8 (tp/montecarlo.frag:105-107), no draws
+            f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
+            uint32_t n_draws = 0u;
+            if (!first_bounce) {
+                float4 a4, t4;
+                wf.load_rad(p, a4, t4);
+                total = mk3(t4.x, t4.y, t4.z);
+                attenu = mk3(a4.x, a4.y, a4.z);
+                n_draws = __float_as_uint(t4.w);
+            }
             if (prm.mode != 0) {
                 // debug shaders: a single traversal, no bounce
                 f3 res = mk3(0.0f, 0.0f, 0.2f);
                 if (hb.x >= 0) {
                     uint3 seed = path_seed(p, npix, prm.width, prm.height, first_pass, prm.date, n_draws);
                     f3 N = mk3(0, 0, 0), P = mk3(0, 0, 0);
-                    intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
+                    intersection_info(S, hb.x, hb.y, pl, prm.flat_face, N, P);
                     if (prm.mode == 1) {
                         float r0 = random_float(seed), r1 = random_float(seed), r2 = random_float(seed);
                         res = mk3(fabsf(N.x) * r0, fabsf(N.y) * r1, fabsf(N.z) * r2);
@@ -63,19 +72,11 @@ __global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, D
                 }
                 wf.store_rad(p, make_float4(0.0f, 0.0f, 0.0f, tag_ended), make_float4(res.x, res.y, res.z, 0.0f));
             } else {
-                // a fresh path starts with total = 0 and attenuation 0.8 (tp/montecarlo.frag:105-107)
-                f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
-                if (!first_bounce) {
-                    float4 a4, t4;
-                    wf.load_rad(p, a4, t4);
-                    total = mk3(t4.x, t4.y, t4.z);
-                    attenu = mk3(a4.x, a4.y, a4.z);
-                }
                 ++my_segments;
                 const uint3 seed0 = path_seed(p, npix, prm.width, prm.height, first_pass, prm.date, n_draws);
                 uint3 seed = seed0;
                 f3 N = mk3(0, 0, 0), P = mk3(0, 0, 0);
-                intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
+                intersection_info(S, hb.x, hb.y, pl, prm.flat_face, N, P);
                 const float4 mat = __ldg(S.mat + hb.x);
                 const float4 col = __ldg(S.color + hb.x);
                 BounceOut bo = bounce<FAST>(O, D, N, P, mat, col, attenu, total, seed, prm.refract_ind);
@@ -89,7 +90,7 @@ __global__ void __launch_bounds__(kBlock, MCPT_SHADE_MINB) k_shade(DevScene S, D
                     wf.store_ray(p, make_float4(bo.nO.x, bo.nO.y, bo.nO.z, 0.0f),
                                  make_float4(bo.nD.x, bo.nD.y, bo.nD.z, __uint_as_float(nd)));
                     wf.store_rad(p, make_float4(bo.new_att.x, bo.new_att.y, bo.new_att.z, tag_alive),
-                                 make_float4(total.x, total.y, total.z, 0.0f));
+                                 make_float4(total.x, total.y, total.z, __uint_as_float(nd)));
                     if (bo.kind == 2) wf.store_keep(p, make_float4(N.x, N.y, N.z, 0.0f), make_float4(P.x, P.y, P.z, 0.0f));
                     kind = uint32_t(bo.kind);
                 }
@@ -141,13 +142,14 @@ __global__ void __launch_bounds__(kBlock) k_shade_exit(DevScene S, DevParams prm
     for (uint32_t i = threadIdx.x; i < len; i += kBlock) {
         uint32_t p;
         if (!queue_item(qin, i, len, p)) continue;
-        float4 ha, n4, p4;
+        float4 n4, p4;
+        f3 pl, Dhit;
         int2 hb;
-        wf.load_hit(p, ha, hb);
+        wf.load_hit(p, pl, hb.x, hb.y, Dhit);
         const float4 d4 = wf.load_ray_d(p);
         wf.load_keep(p, n4, p4);
         f3 N = mk3(n4.x, n4.y, n4.z), P = mk3(p4.x, p4.y, p4.z);
-        intersection_info(S, hb.x, hb.y, mk3(ha.x, ha.y, ha.z), prm.flat_face, N, P);
+        intersection_info(S, hb.x, hb.y, pl, prm.flat_face, N, P);
         f3 nO = P + N * MCPT_BIAS;
         f3 nD = refract3(mk3(d4.x, d4.y, d4.z), -N, 1.0f / prm.refract_ind);
         wf.store_ray(p, make_float4(nO.x, nO.y, nO.z, 0.0f), make_float4(nD.x, nD.y, nD.z, d4.w));  // w: the path's RNG draw count

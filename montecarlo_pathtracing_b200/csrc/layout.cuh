@@ -150,8 +150,8 @@ struct DevParams {
 // load or store (LDG / STG.E.ENL2.256 on sm_100a) so that every access of a stage is a whole sector:
 //   sector 0  ray     origin.xyz | direction.xyz, w = number of RNG draws the path has consumed (uint bits)
 //                     read by k_traverse, written by k_raygen / k_shade / the exit of interior rays
-//   sector 1  hit     pl.xyz, dist | prim, sub        written by k_traverse, read by k_shade
-//   sector 2  rad     attenuation.xyz, w = path tag | radiance gathered so far (`total`)
+//   sector 1  hit     pl.xyz, prim | sub, D.xyz (direction of the ray that hit)   written by k_traverse, read by k_shade
+//   sector 2  rad     attenuation.xyz, w = path tag | radiance gathered so far (`total`), w = RNG draws consumed
 //                     tag (uint bits): 2*batch: alive, 2*batch + 1: ended, the value random_path returns is
 //                     `total`; anything else: never shaded in this batch. k_shade, k_accumulate
 //   sector 3  keep    N | P of the entry hit (interior rays): written by k_shade, read where they exit
@@ -187,15 +187,19 @@ struct Wavefront {
         v.b = d;
         *sec(p, 0) = v;
     }
-    __device__ __forceinline__ void load_hit(size_t p, float4& ha, int2& hb) const {
+    // hit sector: pl.xyz, prim | sub, D.xyz -- the direction of the ray that hit rides along, so that
+    // k_shade does not read the ray sector at all (the hit distance is not needed downstream)
+    __device__ __forceinline__ void load_hit(size_t p, f3& pl, int& prim, int& sub, f3& D) const {
         const PathSector v = *sec(p, 1);
-        ha = v.a;
-        hb = make_int2(__float_as_int(v.b.x), __float_as_int(v.b.y));
+        pl = mk3(v.a.x, v.a.y, v.a.z);
+        prim = __float_as_int(v.a.w);
+        sub = __float_as_int(v.b.x);
+        D = mk3(v.b.y, v.b.z, v.b.w);
     }
-    __device__ __forceinline__ void store_hit(size_t p, float4 ha, int2 hb) const {
+    __device__ __forceinline__ void store_hit(size_t p, f3 pl, int prim, int sub, f3 D) const {
         PathSector v;
-        v.a = ha;
-        v.b = make_float4(__int_as_float(hb.x), __int_as_float(hb.y), 0.0f, 0.0f);
+        v.a = make_float4(pl.x, pl.y, pl.z, __int_as_float(prim));
+        v.b = make_float4(__int_as_float(sub), D.x, D.y, D.z);
         *sec(p, 1) = v;
     }
     __device__ __forceinline__ void load_rad(size_t p, float4& attenu, float4& total) const {
