@@ -291,7 +291,7 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         }
     }
     if (!flat.empty()) {
-        S.smem_top_nodes = int(flat.size()) - 1;  // the flat list takes the tree's place (always staged) ...
+        S.smem_top_nodes = 8 * int(flat.size()) - 1;  // the flat list, once per ray octant (stage_scene), takes the tree's place ...
         S.smem_prims = d->n_prims;                // ... and so do all (<= 16) primitive records
     }
     S.smem_bytes = int(sizeof(DevNode)) * (S.smem_top_nodes + 1 + S.smem_mesh_nodes) + int(sizeof(DevPrim)) * S.smem_prims;

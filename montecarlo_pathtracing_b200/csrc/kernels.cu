@@ -36,9 +36,22 @@ __device__ __forceinline__ SmemScene stage_scene(const DevScene& S, unsigned cha
     DevNode* top = reinterpret_cast<DevNode*>(smem);
     DevNode* mesh = top + (S.smem_top_nodes + 1);
     DevPrim* prims = reinterpret_cast<DevPrim*>(mesh + S.smem_mesh_nodes);
-    {
-        // the flat leaf list (small scenes) or the top levels of the tree
-        const float4* src = reinterpret_cast<const float4*>(S.n_flat > 0 ? S.flat : S.top_nodes);
+    if (S.n_flat > 0) {
+        // the flat leaf list of a small scene, once per ray octant: copy `oct` holds each box as {planes the
+        // ray enters through, planes it leaves through} for directions with sign bits oct (bit 0: x < 0, bit 1:
+        // y < 0, bit 2: z < 0), so that the slab test needs no min / max per axis (scene_walk_flat)
+        const int n = S.n_flat;
+        for (int i = threadIdx.x; i < 8 * n; i += blockDim.x) {
+            const int oct = i / n;
+            const float4 lo = __ldg(&S.flat[i - oct * n].lo), hi = __ldg(&S.flat[i - oct * n].hi);
+            DevNode d;
+            d.lo = make_float4((oct & 1) ? hi.x : lo.x, (oct & 2) ? hi.y : lo.y, (oct & 4) ? hi.z : lo.z, lo.w);
+            d.hi = make_float4((oct & 1) ? lo.x : hi.x, (oct & 2) ? lo.y : hi.y, (oct & 4) ? lo.z : hi.z, hi.w);
+            top[i] = d;
+        }
+    } else {
+        // the top levels of the tree
+        const float4* src = reinterpret_cast<const float4*>(S.top_nodes);
         float4* dst = reinterpret_cast<float4*>(top);
         const int n4 = (S.smem_top_nodes + 1) * 2;
         for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);

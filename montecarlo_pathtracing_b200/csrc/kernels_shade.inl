@@ -9,7 +9,10 @@
 // others). Paths that go on are appended to `next` -- and to `interior` when the new ray starts
 // inside a transparent primitive -- by warp_append into this CTA's regions of the two queues
 // (kernels.cu): that is the whole compaction, there is no separate pass and no flag array.
-// (Measured and dropped: prefetch.global.L2 of the next path's state at the end of an iteration, +3 % time.)
+// (Measured and dropped: prefetch.global.L2 of the next path's state at the end of an iteration, +3 % time;
+// a software pipeline that requests the next path's queue entry and sectors before the current path is
+// shaded: +2..9 % time at 64 or 80 registers -- the gathers are limited by DRAM efficiency on scattered
+// 32-byte sectors (45-54 % of peak), not by exposed latency.)
 #ifndef MCPT_SHADE_MINB
 #define MCPT_SHADE_MINB 4  // 64 registers, 4 CTAs per SM: the kernel waits on its first loads (measured +2 %)
 // (Measured and dropped: compiling the FAST instantiation with FMA contraction. 48 % of its instructions

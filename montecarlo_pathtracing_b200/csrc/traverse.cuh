@@ -60,6 +60,14 @@ MCPT_DEV bool slab(const DevNode& n, f3 idir, f3 od, float tmax) {
     return tn <= tf;
 }
 
+// the same test on a box whose planes are already ordered for the ray's octant (lo: entry, hi: exit):
+// a product with a reciprocal of the matching sign is monotonic, so the per-axis min / max drop out
+MCPT_DEV bool slab_sorted(const DevNode& n, f3 idir, f3 od, float tmax) {
+    const float tn = fmaxf(fmaxf(__fmaf_rn(n.lo.x, idir.x, od.x), __fmaf_rn(n.lo.y, idir.y, od.y)), fmaxf(__fmaf_rn(n.lo.z, idir.z, od.z), 0.0f));
+    const float tf = fminf(fminf(__fmaf_rn(n.hi.x, idir.x, od.x), __fmaf_rn(n.hi.y, idir.y, od.y)), fminf(__fmaf_rn(n.hi.z, idir.z, od.z), tmax));
+    return tn <= tf;
+}
+
 // Reciprocals that feed only the culling frame (idir, od, tmax) are MUFU approximations: their
 // relative error (2^-23) is two orders of magnitude below the inflation of the boxes (1e-5) and the
 // slack on tmax (1e-4), and no hit record depends on them. The IEEE divide they replace was 8 % of
@@ -633,9 +641,12 @@ MCPT_DEV void scene_walk_flat(Work& wk, const DevScene& S, const SmemScene& sm, 
     const float slack = 1e-4f * (fabsf(O.x) + fabsf(O.y) + fabsf(O.z)) + 1e-3f;
     float tmax = FLT_MAX;
     const int n = S.n_flat;
+    // the staged copy of the list for this ray's octant: lo = entry planes, hi = exit planes (stage_scene)
+    const uint32_t oct = (__float_as_uint(idir.x) >> 31) | ((__float_as_uint(idir.y) >> 31) << 1) | ((__float_as_uint(idir.z) >> 31) << 2);
+    const DevNode* boxes = sm.top_nodes + oct * uint32_t(n);
     for (int i = 0; i < n; ++i) {
-        const DevNode nd = sm.top_nodes[i];  // flat list is staged where the tree would be
-        const bool pass = valid && slab(nd, idir, od, tmax);
+        const DevNode nd = boxes[i];
+        const bool pass = valid && slab_sorted(nd, idir, od, tmax);
         if (COUNT && valid) ++wk.boxes;
         if (__any_sync(0xffffffffu, pass)) {
             if (pass) {

@@ -1,0 +1,5 @@
+set -x
+timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest54.log 2>&1; echo "pytest exit $?" >> gpurun_out/pytest54.log
+for w in c2 c1 c5 mesh; do
+  timeout 300 python bench.py --steps 10 --no-cpu-baseline --workload $w > gpurun_out/r54_${w}.json 2>> gpurun_out/r54.err
+done
