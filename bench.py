@@ -117,7 +117,7 @@ def oracle_for(s, raw):
     return o
 
 
-def run_reference(args):
+def run_reference(args, result_out):
     """Reference arm: the reference's algorithm (CPU oracle, kind 'port') on all host cores."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -143,17 +143,28 @@ def run_reference(args):
     paths = rows * w * args.steps
     val = paths / dt / 1e6
     sample = f"{rows} rows x {w} px x 1 spp per step (centre band of the {w}x{h} frame), {args.steps} steps"
-    print(json.dumps({
+    result_out.write(json.dumps({
         "impl": "reference", "metric": "Msamples/s", "value": val, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "note": "reference shader text + host code compiled as C++ (oracle/_ref) on the host cores; GLSL via a graphics API is unavailable on this box"},
         "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": cores, "kind": o.cpu_kind, "sample": sample},
         "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    }) + "\n")
+    result_out.flush()
+
+
+def claim_stdout():
+    """Keep stdout for the ONE JSON line: everything else a library writes to fd 1 (NCCL prints its version
+    banner there) goes to stderr. Returns the file to print the result line to."""
+    sys.stdout.flush()
+    result = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
+    return result
 
 
 def main():
+    result_out = claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -169,7 +180,7 @@ def main():
     ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
-        return run_reference(args)
+        return run_reference(args, result_out)
 
     import torch
     import torch.distributed as dist
@@ -312,10 +323,11 @@ def main():
     total_kernel_ms = sum(kernel_ms.values())
     dominant = max(kernel_ms, key=kernel_ms.get)
     rays = st["rays"]
-    # algorithmic bytes per traversed ray: 32 B ray (origin+direction float4) read, 24 B hit
-    # record written, 4 B queue index read; scene data of the repo scenes is served from
-    # shared memory (0 B). Mesh scenes add 64 B per node pair + 48 B per triangle (L2-resident).
-    bytes_per_ray = 60.0
+    # algorithmic bytes per traversed ray: 4 B queue index read, 32 B ray sector (origin | direction) read,
+    # 32 B hit sector (local hit point, primitive | face, direction) written; scene data of the repo scenes is
+    # served from shared memory (0 B). Mesh scenes add 128 B per four-children node + 48 B per triangle
+    # (L2-resident).
+    bytes_per_ray = 68.0
     alg_bytes = rays * bytes_per_ray
     achieved = alg_bytes / (trav_ms * 1e-3) / 1e9 if trav_ms > 0 else 0.0
     # DRAM traffic per launch from the committed ncu --set full capture (bytes per ray of the
@@ -401,7 +413,8 @@ def main():
         "e2e": {"value": e2e_val, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h)},
         "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
     }
-    print(json.dumps(out))
+    result_out.write(json.dumps(out) + "\n")
+    result_out.flush()
     if world > 1:
         dist.destroy_process_group()
 

@@ -71,6 +71,10 @@ def main(argv=None):
     ap.add_argument("--ref", default=None, help="converged image (.npz with 'image', or .pfm) to compare with")
     ap.add_argument("--curve", default=None, help="comma-separated spp marks: RMSE / luminance after each (needs --ref)")
     args = ap.parse_args(argv)
+    sys.stdout.flush()
+    report_out = os.fdopen(os.dup(1), "w") if argv is None else sys.stdout   # CLI: keep fd 1 for the report line
+    if argv is None:
+        os.dup2(2, 1)                                                         # (NCCL prints its banner on stdout)
 
     world, rank, local = (int(os.environ.get(k, d)) for k, d in (("WORLD_SIZE", "1"), ("RANK", "0"), ("LOCAL_RANK", "0")))
     dist = None
@@ -129,7 +133,8 @@ def main(argv=None):
         if ref is not None and not args.curve:
             report["vs_ref"] = imageio.compare(img, ref)
         report["non_finite_pixels"] = int((~np.isfinite(img)).any(axis=-1).sum())
-        print(json.dumps(report))
+        report_out.write(json.dumps(report) + "\n")
+        report_out.flush()
     ctx.close()
     if dist is not None:
         dist.destroy_process_group()
