@@ -397,7 +397,7 @@ def main():
         dt = time.perf_counter() - t0
         cpu = {"value": rows * w * n_spp / dt / 1e6, "unit": "Msamples/s", "cores": cores, "kind": o.cpu_kind,
                "sample": f"{rows} rows x {w} px x {n_spp} spp (centre band of the {w}x{h} frame), {dt:.1f} s",
-               "counters": o.last_counters}
+               **({"counters": o.last_counters} if any((o.last_counters or {}).values()) else {})}
 
     out = {
         "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,

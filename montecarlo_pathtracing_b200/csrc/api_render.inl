@@ -60,8 +60,8 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
 int passes_per_batch(const mcpt_ctx* c, uint32_t npix) {
     if (c->opt_passes_per_batch > 0) return c->opt_passes_per_batch;
     // ~64M paths in flight (9 GB of wavefront state out of 180 GB): late bounces keep enough rays per launch
-    // to fill 148 SMs, and a step needs fewer launches (measured on config 2: 8M paths 4.8, 16M 5.33, 32M 5.58,
-    // 64M 5.73, 128M 5.76 Gsamples/s)
+    // to fill 148 SMs, and a step needs fewer launches (measured on config 2: 16M paths 5.33, 32M 5.58, 64M 5.73,
+    // 128M 5.76 Gsamples/s)
     uint64_t target = 64ull << 20;
     uint64_t ppb = target / std::max<uint32_t>(npix, 1);
     return int(std::min<uint64_t>(std::max<uint64_t>(ppb, 1), 64));
