@@ -11,8 +11,9 @@
 //    (flat list of small scenes, one-ray-per-lane tree walk, mcpt_trace_rays). DevNode2, 64 bytes =
 //    both child boxes + two child tokens: the mesh trees built on the GPU at upload (bvh_build.cu)
 //    and the top-level tree re-packed into the same form, walked with one explicit stack by the
-//    persistent warps. Boxes are inflated by a few ulps so the (FMA, non-exact) slab test stays
-//    conservative.
+//    persistent warps; DevNode4, 128 bytes = four child boxes + tokens: the same trees with every second
+//    level folded away, walked on scenes with meshes. Boxes are inflated by a few ulps so the (FMA,
+//    non-exact) slab test stays conservative.
 //  * primitive records: 128 bytes = inverse transform (3 rows), forward transform
 //    (3 rows), {type, mesh id, leaf slot}, instead of the 256-byte PrimData.
 //  * triangles: 48 bytes per LEAF SLOT (three float4: A,B,C with the triangle id
