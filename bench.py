@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """bench.py — Msamples/s of the path-tracing hot path on N B200s (BASELINE.json metric).
 
-  python bench.py [--gpus N --steps K --warmup W] [--impl reference] [--workload c2|c1|c5|mesh]
+  python bench.py [--gpus N --steps K --warmup W] [--impl reference] [--workload c2|c1|c5|mesh|c4|scene1..scene8]
 
 One step = mcpt_render of SPP passes of the workload on every rank (rank r traces its own
 seed range, passes [r*SPP, (r+1)*SPP)) followed, for N > 1, by ONE NCCL sum-reduce of the
@@ -35,6 +35,9 @@ WORKLOADS = {
     "c2": ("c2", {}, 1920, 1080, 64, 8, 1.5, "BASELINE config 2: repo scene 6, 1920x1080, 64 spp, IOR 1.5, roughness 0.5, light 0.4, 8 bounces"),
     "c5": ("c5", {}, 1920, 1080, 64, 16, 1.5, "BASELINE config 5 (divergence stress) at 64 spp per step: all transparent+reflective, roughness 0.1, 16 bounces, 1080p"),
     "mesh": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 1920, 1080, 16, 8, 1.5, "BASELINE config 3 at 16 spp per step: 16 meshes x 65536 triangles, 1080p, 8 bounces"),
+    # the repo's eight scenes (hot keys Q..I, MontecarloGPU/montecarlo.cpp:236-290) at the metric's settings
+    **{f"scene{k}": (k, {}, 1920, 1080, 32, 8, 1.0, f"repo scene {k}, 1920x1080, 32 spp per step, light 0.4, IOR 1.0, 8 bounces")
+       for k in range(1, 9)},
     "c4": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 3840, 2160, 4, 8, 1.5, "BASELINE config 4 at 4 spp per step: 16 meshes x 65536 triangles, 3840x2160, 8 bounces"),
 }
 
@@ -177,6 +180,7 @@ def main():
     ap.add_argument("--refill", type=int, default=0, help="persistent warps: idle lanes that trigger a refill (0 = auto)")
     ap.add_argument("--persistent", type=int, default=1, help="1 = persistent warps with lane refill on tree scenes")
     ap.add_argument("--mesh-bvh", type=int, default=1, help="1 = GPU-built LBVH per mesh, 0 = the uploaded median-split trees")
+    ap.add_argument("--top-sah", type=int, default=1, help="1 = SAH-built top-level tree for the persistent walk, 0 = the reference's median-split topology")
     ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -209,6 +213,7 @@ def main():
     ctx.set_option(capi.OPT_FAST_MATH, args.fast_math)
     if args.occ:
         ctx.set_option(capi.OPT_TRAVERSE_OCC, args.occ)
+    ctx.set_option(capi.OPT_TOP_SAH, args.top_sah)
     ctx.set_option(capi.OPT_MESH_BVH, args.mesh_bvh)
     ctx.set_option(capi.OPT_PERSISTENT, args.persistent)
     ctx.set_option(capi.OPT_REFILL_LANES, args.refill)

@@ -92,8 +92,11 @@ enum {
     MCPT_OPT_PERSISTENT = 8,       /* 1 = scenes walked through the tree (> 16 primitives, or meshes) are traced by
                                       persistent warps whose idle lanes fetch new rays (default), 0 = one ray per
                                       lane per tile. Set before mcpt_upload_scene. Same results. */
-    MCPT_OPT_REFILL_LANES = 9      /* persistent warps: idle lanes of a warp that trigger a refill from the queue,
+    MCPT_OPT_REFILL_LANES = 9,     /* persistent warps: idle lanes of a warp that trigger a refill from the queue,
                                       1..32; 0 = auto (8 with meshes, 32 without). Set before mcpt_upload_scene. */
+    MCPT_OPT_TOP_SAH = 10          /* 1 = the persistent warps walk a top-level tree built at upload by a full-sweep
+                                      SAH over the primitives' leaf boxes (default), 0 = the topology of the uploaded
+                                      median-split tree. Set before mcpt_upload_scene. Same results. */
 };
 
 /* wavefront stages, in launch order inside one bounce */

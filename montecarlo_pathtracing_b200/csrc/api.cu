@@ -70,6 +70,7 @@ struct mcpt_ctx {
     int opt_fast_math = 0;
     int opt_profile = 0;
     int opt_flat_walk = 1;
+    int opt_top_sah = 1;
     int opt_mesh_bvh = 1;
     int opt_persistent = 1;
     int opt_refill_lanes = 0;
@@ -310,6 +311,7 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
         case MCPT_OPT_PROFILE_STAGES: c->opt_profile = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_COUNT_WORK: c->opt_count_work = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_TOP_SAH: c->opt_top_sah = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TRAVERSE_OCC:
             if (value != 0 && (value < 2 || value > 4))
                 return fail(c, MCPT_E_INVALID, "traverse occupancy must be 0 (auto), 2, 3 or 4 CTAs per SM");

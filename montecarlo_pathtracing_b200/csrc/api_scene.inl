@@ -32,7 +32,159 @@ int validate_bvh(mcpt_ctx* c, const mcpt_bvh_desc& b, int n_items, const char* w
 
 }  // namespace
 
-extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
+extern "C" namespace {
+
+// ---- host-side builders of the persistent walk's top-level tree
+struct TopItem {
+    float lo[3], hi[3];
+    int prim;
+};
+
+inline void set_child2(DevNode2& N, int j, const DevNode& b, int tok) {
+    float4& lo = j ? N.lo1 : N.lo0;
+    float4& hi = j ? N.hi1 : N.hi0;
+    lo.x = b.lo.x; lo.y = b.lo.y; lo.z = b.lo.z;
+    hi.x = b.hi.x; hi.y = b.hi.y; hi.z = b.hi.z;
+    std::memcpy(j ? &N.hi0.w : &N.lo0.w, &tok, sizeof(int));  // tokens live in lo0.w / hi0.w
+    if (j) lo.w = hi.w = 0.0f;
+}
+
+inline DevNode box_of(const std::vector<TopItem>& it, int begin, int end) {
+    DevNode b = empty_node();
+    for (int i = begin; i < end; ++i) {
+        b.lo.x = std::min(b.lo.x, it[i].lo[0]); b.lo.y = std::min(b.lo.y, it[i].lo[1]); b.lo.z = std::min(b.lo.z, it[i].lo[2]);
+        b.hi.x = std::max(b.hi.x, it[i].hi[0]); b.hi.y = std::max(b.hi.y, it[i].hi[1]); b.hi.z = std::max(b.hi.z, it[i].hi[2]);
+    }
+    return b;
+}
+
+inline double half_area(const float lo[3], const float hi[3]) {
+    const double x = double(hi[0]) - lo[0], y = double(hi[1]) - lo[1], z = double(hi[2]) - lo[2];
+    return (x < 0 || y < 0 || z < 0) ? 0.0 : x * y + y * z + z * x;
+}
+
+// items[begin, end) -> token of the subtree (>= 0: node index, < 0: ~primitive). Full-sweep SAH on the three
+// axes (items sorted by box centre); below `depth_left` levels of head room the split is the median of the
+// longest axis, which bounds the depth (the walk's stack holds one entry per level).
+int build_top_sah_rec(std::vector<TopItem>& it, int begin, int end, int depth_left, std::vector<DevNode2>& nodes) {
+    const int n = end - begin;
+    if (n == 1) return ~it[begin].prim;
+    const int idx = int(nodes.size());
+    nodes.push_back(DevNode2{});
+    int best_axis = -1, best_split = begin + n / 2;
+    int balanced_levels = 0;
+    while ((1 << balanced_levels) < n) ++balanced_levels;
+    auto by_axis = [&](int ax) {
+        std::stable_sort(it.begin() + begin, it.begin() + end, [ax](const TopItem& a, const TopItem& b) {
+            return a.lo[ax] + a.hi[ax] < b.lo[ax] + b.hi[ax];
+        });
+    };
+    if (depth_left > balanced_levels) {
+        double best = 1e300;
+        std::vector<double> right(n + 1, 0.0);
+        for (int ax = 0; ax < 3; ++ax) {
+            by_axis(ax);
+            float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+            for (int i = n - 1; i >= 1; --i) {
+                for (int k = 0; k < 3; ++k) {
+                    lo[k] = std::min(lo[k], it[begin + i].lo[k]);
+                    hi[k] = std::max(hi[k], it[begin + i].hi[k]);
+                }
+                right[i] = half_area(lo, hi);
+            }
+            float llo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, lhi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+            for (int i = 1; i < n; ++i) {
+                for (int k = 0; k < 3; ++k) {
+                    llo[k] = std::min(llo[k], it[begin + i - 1].lo[k]);
+                    lhi[k] = std::max(lhi[k], it[begin + i - 1].hi[k]);
+                }
+                const double cost = half_area(llo, lhi) * i + right[i] * (n - i);
+                if (cost < best) {
+                    best = cost;
+                    best_axis = ax;
+                    best_split = begin + i;
+                }
+            }
+        }
+    }
+    if (best_axis < 0) {  // no head room left (or degenerate boxes): median of the longest axis
+        const DevNode b = box_of(it, begin, end);
+        const float ex = b.hi.x - b.lo.x, ey = b.hi.y - b.lo.y, ez = b.hi.z - b.lo.z;
+        best_axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
+        best_split = begin + n / 2;
+    }
+    by_axis(best_axis);
+    const int t0 = build_top_sah_rec(it, begin, best_split, depth_left - 1, nodes);
+    const int t1 = build_top_sah_rec(it, best_split, end, depth_left - 1, nodes);
+    DevNode2 N{};
+    set_child2(N, 0, box_of(it, begin, best_split), t0);
+    set_child2(N, 1, box_of(it, best_split, end), t1);
+    nodes[idx] = N;
+    return idx;
+}
+
+void build_top_sah(std::vector<TopItem>& items, std::vector<DevNode2>& nodes) {
+    nodes.clear();
+    if (items.size() == 1) {  // a single primitive: the root holds that leaf and an empty child
+        DevNode2 N{};
+        set_child2(N, 0, box_of(items, 0, 1), ~items[0].prim);
+        set_child2(N, 1, empty_node(), INT_MIN);
+        nodes.push_back(N);
+        return;
+    }
+    nodes.reserve(items.size());
+    build_top_sah_rec(items, 0, int(items.size()), 30, nodes);  // <= 30 levels: one stack entry per level (kWalkStack)
+}
+
+// fold every second level of a two-children tree (root = node 0) into four-children nodes
+void fold_top4(const std::vector<DevNode2>& n2, std::vector<DevNode4>& n4) {
+    for (DevNode4& N : n4) {
+        std::memset(&N, 0, sizeof N);
+        N.tok = make_int4(INT_MIN, INT_MIN, INT_MIN, INT_MIN);
+    }
+    if (n2.empty()) return;
+    auto child = [&](const DevNode2& N, int j, DevNode& b, int& tok) {
+        const float4& lo = j ? N.lo1 : N.lo0;
+        const float4& hi = j ? N.hi1 : N.hi0;
+        b.lo = lo;
+        b.hi = hi;
+        std::memcpy(&tok, j ? &N.hi0.w : &N.lo0.w, sizeof(int));
+    };
+    std::vector<int> todo{0};
+    while (!todo.empty()) {
+        const int k = todo.back();
+        todo.pop_back();
+        DevNode4& W = n4[k];
+        int m = 0;
+        auto put = [&](const DevNode& b, int tok) {
+            (&W.lox.x)[m] = b.lo.x; (&W.loy.x)[m] = b.lo.y; (&W.loz.x)[m] = b.lo.z;
+            (&W.hix.x)[m] = b.hi.x; (&W.hiy.x)[m] = b.hi.y; (&W.hiz.x)[m] = b.hi.z;
+            (&W.tok.x)[m] = tok;
+            ++m;
+            if (tok >= 0) todo.push_back(tok);
+        };
+        for (int j = 0; j < 2; ++j) {
+            DevNode b;
+            int tok;
+            child(n2[k], j, b, tok);
+            if (tok == INT_MIN) continue;
+            if (tok >= 0) {
+                for (int jj = 0; jj < 2; ++jj) {
+                    DevNode bb;
+                    int t2;
+                    child(n2[tok], jj, bb, t2);
+                    if (t2 != INT_MIN) put(bb, t2);
+                }
+            } else {
+                put(b, tok);
+            }
+        }
+    }
+}
+
+}  // namespace
+
+int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     if (!c || !d) return MCPT_E_INVALID;
     CK(c, cudaSetDevice(c->device));
     if (d->n_prims < 0 || (d->n_prims > 0 && !d->prim_data)) return fail(c, MCPT_E_INVALID, "bad primitive table");
@@ -97,68 +249,51 @@ extern "C" int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         if (!empty) top[k] = pack_node(d->root.bb[k - 1], aux);
     }
 
-    // ---- the same tree in the two-children node format of the mesh trees (persistent warps walk both
-    // levels with one node step): node k-1 holds the boxes of heap children 2k and 2k+1
-    std::vector<DevNode2> top2(t_first_leaf - 1);
-    for (uint32_t k = 1; k < t_first_leaf; ++k) {
-        int tok[2];
-        for (int j = 0; j < 2; ++j) {
-            const uint32_t ch = 2 * k + uint32_t(j);
-            if (ch < t_first_leaf)
-                tok[j] = int(ch - 1);
-            else {
-                const int prim = d->root.ind[ch - t_first_leaf];
-                tok[j] = prim >= 0 ? ~prim : INT_MIN;  // kTokEmpty
-            }
-        }
-        const DevNode &a = top[2 * k], &b = top[2 * k + 1];
-        DevNode2& N = top2[k - 1];
-        N.lo0 = make_float4(a.lo.x, a.lo.y, a.lo.z, 0.0f);
-        N.hi0 = make_float4(a.hi.x, a.hi.y, a.hi.z, 0.0f);
-        N.lo1 = make_float4(b.lo.x, b.lo.y, b.lo.z, 0.0f);
-        N.hi1 = make_float4(b.hi.x, b.hi.y, b.hi.z, 0.0f);
-        std::memcpy(&N.lo0.w, &tok[0], sizeof(int));
-        std::memcpy(&N.hi0.w, &tok[1], sizeof(int));
-    }
-
-    // ---- and with every second level folded away (DevNode4, MCPT_WIDE): the node of heap index k at an
-    // even level holds its grandchildren 4k .. 4k+3 (its children 2k, 2k+1 where those are leaves); stored
-    // at k-1 like top2, the entries of odd levels stay unused
-    std::vector<DevNode4> top4(std::max<uint32_t>(t_first_leaf - 1, 1u));
+    // ---- the top-level tree of the persistent walk. Hit records do not depend on the tree (candidates are
+    // ranked by the reference's exact distance and visit order, intersect.cuh), so the persistent warps walk a
+    // tree of their own instead of the reference's median split with its cycling axis (bvh_gpu/bvh.cpp:34-93):
+    // a full-sweep SAH build over the primitives' (inflated) leaf boxes, one primitive per leaf, in the
+    // two-children node format of the mesh trees (top2, root = node 0) and folded into four-children nodes
+    // (top4). Measured on repo scene 8 (895 primitives): 69 -> see profiles/README.md box tests per ray.
+    // MCPT_OPT_TOP_SAH = 0 keeps the reference's topology.
+    std::vector<DevNode2> top2;
     {
-        auto slot = [&](DevNode4& N, int j, uint32_t ch) {
-            int tok = INT_MIN;  // kTokEmpty
-            DevNode b = empty_node();
-            if (ch < t_first_leaf) {
-                tok = int(ch - 1);
-                b = top[ch];
-            } else {
-                const int prim = d->root.ind[ch - t_first_leaf];
-                if (prim >= 0) {
-                    tok = ~prim;
-                    b = top[ch];
+        std::vector<TopItem> items;
+        for (uint32_t sl = 0; sl < t_first_leaf; ++sl) {
+            const int prim = d->root.ind[sl];
+            if (prim < 0 || prims[prim].slot != int(sl)) continue;  // each primitive once, at its first slot
+            const DevNode& nb = top[t_first_leaf + sl];
+            items.push_back(TopItem{{nb.lo.x, nb.lo.y, nb.lo.z}, {nb.hi.x, nb.hi.y, nb.hi.z}, prim});
+        }
+        if (c->opt_top_sah && !items.empty()) {
+            build_top_sah(items, top2);
+        } else {
+            // the reference's own topology: node k-1 holds the boxes of heap children 2k and 2k+1
+            top2.resize(std::max<uint32_t>(t_first_leaf - 1, 1u));
+            if (td == 0) {
+                const int prim = d->root.ind[0];
+                set_child2(top2[0], 0, top[1], prim >= 0 ? ~prim : INT_MIN);
+                set_child2(top2[0], 1, empty_node(), INT_MIN);
+            }
+            for (uint32_t k = 1; k < t_first_leaf; ++k)
+                for (int j = 0; j < 2; ++j) {
+                    const uint32_t ch = 2 * k + uint32_t(j);
+                    int tok;
+                    if (ch < t_first_leaf)
+                        tok = int(ch - 1);
+                    else {
+                        const int prim = d->root.ind[ch - t_first_leaf];
+                        tok = prim >= 0 ? ~prim : INT_MIN;  // kTokEmpty
+                    }
+                    set_child2(top2[k - 1], j, top[ch], tok);
                 }
-            }
-            (&N.lox.x)[j] = b.lo.x; (&N.loy.x)[j] = b.lo.y; (&N.loz.x)[j] = b.lo.z;
-            (&N.hix.x)[j] = b.hi.x; (&N.hiy.x)[j] = b.hi.y; (&N.hiz.x)[j] = b.hi.z;
-            (&N.tok.x)[j] = tok;
-        };
-        for (DevNode4& N : top4) {
-            std::memset(&N, 0, sizeof N);
-            N.tok = make_int4(INT_MIN, INT_MIN, INT_MIN, INT_MIN);
         }
-        if (td == 0) {
-            slot(top4[0], 0, 1u);  // a single leaf slot: the root is that leaf
-        }
-        for (int level = 0; level < td; level += 2)
-            for (uint32_t k = 1u << level; k < (2u << level); ++k) {
-                DevNode4& N = top4[k - 1];
-                if (level + 1 < td)
-                    for (int j = 0; j < 4; ++j) slot(N, j, 4 * k + uint32_t(j));
-                else
-                    for (int j = 0; j < 2; ++j) slot(N, j, 2 * k + uint32_t(j));
-            }
     }
+    // ---- and with every second level folded away (DevNode4, scenes with meshes): a node at even depth
+    // holds its grandchildren (or a child, where that child is a leaf); stored at the index of the
+    // two-children node it replaces, the entries of odd depths stay unused
+    std::vector<DevNode4> top4(top2.size());
+    fold_top4(top2, top4);
 
     // ---- small scenes: flat list of leaf boxes for the warp-coherent walk
     std::vector<DevNode> flat;
