@@ -271,7 +271,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
             if (kind == WALK_DONE) has_ray = false;
         }
 #ifndef MCPT_NODE_STEPS
-#define MCPT_NODE_STEPS (WIDE ? 2 : 4)  // (four-children nodes: 1 -> 930, 2 -> 1003, 3 -> 996 Msamples/s.) Two-children node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 946, 6 -> 930, 8 -> 900 Msamples/s
+#define MCPT_NODE_STEPS (WIDE ? 2 : (MESHES ? 4 : 6))  // (four-children nodes: 1 -> 930, 2 -> 1003, 3 -> 996 Msamples/s; SAH-built trees of analytic primitives, divergence-stress scene: 2 -> 3222, 4 -> 3398, 6 -> 3504 Msamples/s.) Two-children node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 946, 6 -> 930, 8 -> 900 Msamples/s
 #endif
         if (kind == WALK_NODE) {
             // a run of node steps: the lanes at a triangle or a primitive wait, but the dispatch, the
