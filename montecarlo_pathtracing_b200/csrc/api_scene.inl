@@ -63,6 +63,56 @@ inline double half_area(const float lo[3], const float hi[3]) {
     return (x < 0 || y < 0 || z < 0) ? 0.0 : x * y + y * z + z * x;
 }
 
+// world box of the local box [lo, hi] under the primitive's forward transform, inflated like every other box
+inline DevNode world_box(const Aff& fwd, const float lo[3], const float hi[3]) {
+    mcpt_bb b{{FLT_MAX, FLT_MAX, FLT_MAX}, {-FLT_MAX, -FLT_MAX, -FLT_MAX}};
+    for (int k = 0; k < 8; ++k) {
+        const float x = (k & 1) ? hi[0] : lo[0], y = (k & 2) ? hi[1] : lo[1], z = (k & 4) ? hi[2] : lo[2];
+        const float w[3] = {fwd.r0.x * x + fwd.r0.y * y + fwd.r0.z * z + fwd.r0.w, fwd.r1.x * x + fwd.r1.y * y + fwd.r1.z * z + fwd.r1.w,
+                            fwd.r2.x * x + fwd.r2.y * y + fwd.r2.z * z + fwd.r2.w};
+        for (int a = 0; a < 3; ++a) {
+            b.min[a] = std::min(b.min[a], w[a]);
+            b.max[a] = std::max(b.max[a], w[a]);
+        }
+    }
+    return pack_node(b, -1);
+}
+
+// A rotated, elongated primitive has a loose axis-aligned box (a 80 x 10 beam at 45 degrees: 6x the area of
+// the beam). Such a primitive enters the tree as kTopSlices boxes instead, the world boxes of slabs of its
+// bounding cube (the reference's own bound, unit cube +-1.005, bvh_gpu/scene.cpp:18-42) cut along its longest
+// axis: their union still contains the primitive, every slab is a leaf of its own with the same primitive
+// token (a ray through two slabs offers the same candidate twice, which changes nothing). Only for
+// primitives whose intersector demands a > EPSILON (sphere, cube, cylinder): the quad and the cone accept
+// hits behind the origin when the origin is inside the reference's leaf box, which a sliced bound could miss.
+constexpr int kTopSlices = 8;
+bool slice_loose_primitive(const DevPrim& P, const DevNode& full, int prim, std::vector<TopItem>& items) {
+    if (P.type != MCPT_PRIM_SPHERE && P.type != MCPT_PRIM_CUBE && P.type != MCPT_PRIM_CYLINDER) return false;
+    const float e = 1.005f;
+    const float col[3] = {P.fwd.r0.x * P.fwd.r0.x + P.fwd.r1.x * P.fwd.r1.x + P.fwd.r2.x * P.fwd.r2.x,
+                          P.fwd.r0.y * P.fwd.r0.y + P.fwd.r1.y * P.fwd.r1.y + P.fwd.r2.y * P.fwd.r2.y,
+                          P.fwd.r0.z * P.fwd.r0.z + P.fwd.r1.z * P.fwd.r1.z + P.fwd.r2.z * P.fwd.r2.z};
+    const int ax = (col[0] >= col[1] && col[0] >= col[2]) ? 0 : (col[1] >= col[2] ? 1 : 2);
+    DevNode part[kTopSlices];
+    double sum = 0.0;
+    for (int k = 0; k < kTopSlices; ++k) {
+        float lo[3] = {-e, -e, -e}, hi[3] = {e, e, e};
+        lo[ax] = -e + 2.0f * e * float(k) / float(kTopSlices);
+        hi[ax] = -e + 2.0f * e * float(k + 1) / float(kTopSlices);
+        part[k] = world_box(P.fwd, lo, hi);
+        // never larger than the reference's own leaf box
+        part[k].lo.x = std::max(part[k].lo.x, full.lo.x); part[k].lo.y = std::max(part[k].lo.y, full.lo.y); part[k].lo.z = std::max(part[k].lo.z, full.lo.z);
+        part[k].hi.x = std::min(part[k].hi.x, full.hi.x); part[k].hi.y = std::min(part[k].hi.y, full.hi.y); part[k].hi.z = std::min(part[k].hi.z, full.hi.z);
+        const float l3[3] = {part[k].lo.x, part[k].lo.y, part[k].lo.z}, h3[3] = {part[k].hi.x, part[k].hi.y, part[k].hi.z};
+        sum += half_area(l3, h3);
+    }
+    const float fl[3] = {full.lo.x, full.lo.y, full.lo.z}, fh[3] = {full.hi.x, full.hi.y, full.hi.z};
+    if (!(sum < 0.7 * half_area(fl, fh))) return false;  // not loose: one box
+    for (int k = 0; k < kTopSlices; ++k)
+        items.push_back(TopItem{{part[k].lo.x, part[k].lo.y, part[k].lo.z}, {part[k].hi.x, part[k].hi.y, part[k].hi.z}, prim});
+    return true;
+}
+
 // items[begin, end) -> token of the subtree (>= 0: node index, < 0: ~primitive). Full-sweep SAH on the three
 // axes (items sorted by box centre); below `depth_left` levels of head room the split is the median of the
 // longest axis, which bounds the depth (the walk's stack holds one entry per level).
@@ -263,6 +313,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
             const int prim = d->root.ind[sl];
             if (prim < 0 || prims[prim].slot != int(sl)) continue;  // each primitive once, at its first slot
             const DevNode& nb = top[t_first_leaf + sl];
+            if (c->opt_top_sah && slice_loose_primitive(prims[prim], nb, prim, items)) continue;
             items.push_back(TopItem{{nb.lo.x, nb.lo.y, nb.lo.z}, {nb.hi.x, nb.hi.y, nb.hi.z}, prim});
         }
         if (c->opt_top_sah && !items.empty()) {
