@@ -181,6 +181,7 @@ def main():
     ap.add_argument("--persistent", type=int, default=1, help="1 = persistent warps with lane refill on tree scenes")
     ap.add_argument("--mesh-bvh", type=int, default=1, help="1 = GPU-built LBVH per mesh, 0 = the uploaded median-split trees")
     ap.add_argument("--top-sah", type=int, default=1, help="1 = SAH-built top-level tree for the persistent walk, 0 = the reference's median-split topology")
+    ap.add_argument("--flat-walk", type=int, default=1, help="1 = warp-coherent flat walk for scenes of <= 16 primitives, 0 = tree walk (persistent warps)")
     ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -214,6 +215,7 @@ def main():
     if args.occ:
         ctx.set_option(capi.OPT_TRAVERSE_OCC, args.occ)
     ctx.set_option(capi.OPT_TOP_SAH, args.top_sah)
+    ctx.set_option(capi.OPT_FLAT_WALK, args.flat_walk)
     ctx.set_option(capi.OPT_MESH_BVH, args.mesh_bvh)
     ctx.set_option(capi.OPT_PERSISTENT, args.persistent)
     ctx.set_option(capi.OPT_REFILL_LANES, args.refill)
