@@ -278,3 +278,32 @@ def test_headless_render_tool_writes_the_back_buffer_and_reports_convergence(tmp
     curve = json.loads(buf.getvalue().strip().splitlines()[-1])["curve"]
     assert [c["spp"] for c in curve] == [4, 64, 1024]
     assert curve[0]["rmse"] > curve[1]["rmse"] > curve[2]["rmse"]
+
+
+@pytest.mark.parametrize("kind,kw", [(1, {}), (2, {}), (6, {}), (3, {}), (8, {}), ("c5", {}), ("mesh", {"n_meshes": 3, "tris_log2": 9})])
+def test_top_level_tree_choices_do_not_change_the_image(kind, kw):
+    """The persistent warps walk a tree of the library's own (full-sweep SAH, rotated elongated primitives
+    entered as slab boxes; MCPT_OPT_TOP_SAH) or the reference's median-split topology, small scenes the flat
+    list (MCPT_OPT_FLAT_WALK): candidates are ranked by the reference's distance and visit order, so sums,
+    ray and segment counts are the same bit for bit whichever structure found them."""
+    s, o = both(kind, **kw)
+    iv, ipv = capi.default_camera(160, 90)
+    out = {}
+    for flat_walk, top_sah in ((1, 1), (0, 1), (0, 0)):
+        c = Context(0)
+        try:
+            c.set_option(capi.OPT_FLAT_WALK, flat_walk)
+            c.set_option(capi.OPT_TOP_SAH, top_sah)
+            c.upload_scene(s)
+            c.resize(160, 90)
+            c.set_camera(iv, ipv)
+            c.set_params(nb_bounces=8, refract_ind=1.5, date=float(DATE))
+            c.render(0, 4)
+            out[(flat_walk, top_sah)] = (c.read_accum(), c.stats())
+        finally:
+            c.close()
+    base, st = out[(1, 1)]
+    assert base[..., :3].mean() > 0.01
+    for key in ((0, 1), (0, 0)):
+        assert np.array_equal(base, out[key][0]), key
+        assert out[key][1]["rays"] == st["rays"] and out[key][1]["segments"] == st["segments"], key
