@@ -38,8 +38,17 @@ WORKLOADS = {
     # the repo's eight scenes (hot keys Q..I, MontecarloGPU/montecarlo.cpp:236-290) at the metric's settings
     **{f"scene{k}": (k, {}, 1920, 1080, 32, 8, 1.0, f"repo scene {k}, 1920x1080, 32 spp per step, light 0.4, IOR 1.0, 8 bounces")
        for k in range(1, 9)},
+    # the reference's own screenshots: window 1280x1000, Bounces 9, Paths 1 per frame --
+    # one step = one frame of the locked viewer; FPS = 1000 / ms_per_step
+    **{f"fps{k}": (k, {"light": 0.443}, 1280, 1000, 1, 9, 1.0, f"viewer frame of the reference's screenshots: repo scene {k}, 1280x1000, 1 path per frame, 9 bounces, IOR 1.0")
+       for k in range(1, 9)},
     "c4": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 3840, 2160, 4, 8, 1.5, "BASELINE config 4 at 4 spp per step: 16 meshes x 65536 triangles, 3840x2160, 8 bounces"),
 }
+
+
+# Msamples/s derived from the FPS read-outs of the reference's screenshots (FPS x 1.28 Mpixel
+# x 1 path per frame; unknown desktop GPU through OpenGL): the published numbers of the fpsK workloads
+REFERENCE_SCREENSHOT_MSAMPLES = {"fps1": 34.5, "fps2": 20.0, "fps3": 24.0, "fps4": 27.6, "fps5": 83.6, "fps7": 13.0, "fps8": 6.6}
 
 
 def peaks():
@@ -94,7 +103,8 @@ class ClockSampler:
 def build_scene(name):
     from common import host_scene
     kind, kw, w, h, spp, bounces, ior, desc = WORKLOADS[name]
-    s = host_scene(kind, 0.4, **kw)
+    kw = dict(kw)
+    s = host_scene(kind, kw.pop("light", 0.4), **kw)
     raw = s.prim_data()
     s.finalize()
     return s, raw, (w, h, spp, bounces, ior, desc)
@@ -409,7 +419,8 @@ def main():
     out = {
         "metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "vs_baseline": (value / REFERENCE_SCREENSHOT_MSAMPLES[args.workload]) if args.workload in REFERENCE_SCREENSHOT_MSAMPLES else None,
+        "dtype": "f32", "data": "synthetic",
         "config": {"workload": desc, "name": args.workload, "width": w, "height": h, "spp_per_step_per_gpu": spp,
                    "bounces": bounces, "ior": ior, "parallelism": f"spp-split x{world}, one ncclReduce(sum) per step" if world > 1 else "single GPU",
                    "l2": "wavefront state of a batch (>1 GB) exceeds the 126 MB L2; no flush needed",
