@@ -1,7 +1,7 @@
 // api.cu — context management and the C ABI of include/mcpt.h.
 //
 // Owns all device memory of a context: the re-packed scene (layout.cuh), the
-// accumulation buffer, and the SoA wavefront state sized for a batch of passes.
+// accumulation buffer, and the wavefront state (32-byte sector planes, layout.cuh) sized for a batch of passes.
 // mcpt_render() drives the wavefront: for each batch of passes
 //   raygen -> { traverse -> shade -> [traverse of the interior rays] } x bounces -> accumulate
 // with queue lengths kept on the device.

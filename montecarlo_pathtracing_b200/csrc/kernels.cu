@@ -174,7 +174,7 @@ __device__ __forceinline__ void warp_append(uint32_t* s_count, const QueueOut& q
 
 // Where the closest-hit search of one bounce delivers its result.
 //  * Main traversal of the Monte Carlo mode (hit queue): the rays that hit something get their record
-//    in hit_a / hit_b and are appended to the queue, so the shading kernel only ever sees hits; a ray
+//    in the hit sector and are appended to the queue, so the shading kernel only ever sees hits; a ray
 //    that leaves the scene needs nothing at all: its path simply stays as it is, and k_accumulate
 //    evaluates the fake sky (tp/montecarlo.frag:118-119) from the path's last total / attenuation /
 //    direction. No dependent load sits between two walks of a warp.
@@ -183,7 +183,7 @@ __device__ __forceinline__ void warp_append(uint32_t* s_count, const QueueOut& q
 //    was hit: intersection_info writes nothing for shape -1) and leave through
 //    refract(D, -N, 1 / refract_ind). This used to be a kernel of its own (k_shade_exit: 2.1 ms per C2
 //    step at 14 % issue utilisation, waiting on its loads); here the loads overlap other warps' walks.
-//  * Debug shaders (no queue, no exit): every ray's record goes to hit_a / hit_b.
+//  * Debug shaders (no queue, no exit): every ray's record goes to the hit sector.
 struct HitSink {
     QueueOut hitq;
     int exit_mode;

@@ -11,9 +11,11 @@
 //   * scene_walk_flat -- <= 16 analytic primitives: the leaf boxes as one list in
 //     shared memory, stepped through by all lanes of a warp together;
 //   * the resumable walk (walk_begin / walk_node / walk_tri / walk_prim) -- every
-//     other scene, under persistent warps (k_traverse, PERSIST): both levels in the
-//     64-byte two-children node format, nearer child first, the farther one pushed
-//     with its entry parameter on one explicit stack;
+//     other scene, under persistent warps (k_traverse, PERSIST): a top-level tree
+//     of the library's own (full-sweep SAH at upload, api_scene.inl) and the GPU-built
+//     mesh trees, both in the 64-byte two-children node format -- or, on scenes with
+//     meshes, folded into 128-byte four-children nodes -- nearest child first, the
+//     others pushed with their entry parameters on one explicit stack;
 //   * scene_walk + mesh_walk / mesh_walk_lbvh -- one ray per lane over the
 //     reference's implicit heap order, which needs no stack at all: the node's heap
 //     index plus a 32-bit trail ("a sibling is still pending at this level") live in
@@ -336,13 +338,14 @@ MCPT_DEV void scene_walk(Work& wk, const DevScene& S, const SmemScene& sm, f3 O,
 // The closest-hit search cut into single steps, for persistent warps (k_traverse, PERSIST): a lane
 // whose ray is finished takes the next ray of its warp's queue region while its neighbours go on
 // walking. To keep the lanes of a warp in the same instruction stream as often as possible, BOTH
-// levels of the scene are walked by the same node step: the top-level tree is re-packed at upload
-// into the 64-byte two-children node format of the mesh trees (DevScene::top2), and one explicit
+// levels of the scene are walked by the same node step: the top-level tree is built at upload
+// (SAH) in the 64-byte two-children node format of the mesh trees (DevScene::top2), and one explicit
 // stack serves both levels. Entering a mesh pushes a marker, switches the culling frame (idir, od,
 // tmax) to mesh-local space and parks the world frame in `wsave`; popping the marker restores it.
 // Three kinds of step remain:
-//   WALK_NODE  one node of either level: both child boxes, nearer first, farther pushed with its
-//              entry parameter (dropped when popped if a closer hit is known by then)
+//   WALK_NODE  one node of either level: both (or all four, DevNode4) child boxes, nearest first,
+//              the others pushed with their entry parameters (dropped when popped if a closer hit
+//              is known by then)
 //   WALK_TRI   one triangle of a mesh leaf
 //   WALK_PRIM  a top-level leaf: the analytic intersector, or the entry into a mesh
 // Candidates go through the same arithmetic and the same total order (distance, then the
