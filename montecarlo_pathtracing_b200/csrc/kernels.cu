@@ -191,9 +191,10 @@ struct HitSink {
     float refract_ind;
 };
 
+template <bool EXIT>
 __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, const HitSink& sink, uint32_t* s_count, uint32_t p,
                                         bool valid, const Best& best, f3 D) {
-    if (sink.exit_mode) {
+    if (EXIT) {
         if (valid) {
             const float4 d4 = wf.load_ray_d(p);
             float4 n4, p4;
@@ -226,7 +227,7 @@ __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, 
 // want it -- no gain; one queue region per warp instead of per CTA -- no atomics at all and ordered
 // survivors, but warps of a CTA finish at different times, -4 % at C2.)
 
-template <bool COUNT, bool MESHES>
+template <bool COUNT, bool MESHES, bool EXIT>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
                                                     uint32_t len, const HitSink& sink, uint32_t* s_next, uint32_t* s_hits,
                                                     Work& wk) {
@@ -267,7 +268,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
         const int kind = has_ray ? walk_kind(w) : -1;  // WALK_POP: a dead entry was dropped, pop again next time
         // finished rays: deliver and free the lane
         if (__any_sync(0xffffffffu, kind == WALK_DONE)) {
-            deliver(S, wf, sink, s_hits, p, kind == WALK_DONE, w.best, w.D);
+            deliver<EXIT>(S, wf, sink, s_hits, p, kind == WALK_DONE, w.best, w.D);
             if (kind == WALK_DONE) has_ray = false;
         }
 #ifndef MCPT_NODE_STEPS
@@ -291,7 +292,9 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
 // FLAT: warp-coherent flat walk (S.n_flat > 0); MESHES: the scene has triangle meshes; PERSIST:
 // persistent warps with per-lane refill (tree scenes; mesh trees must be the GPU-built ones).
 // Every lane of a warp stays in the loop together (warp-uniform trip count).
-template <bool COUNT, int MINB, bool FLAT, bool MESHES, bool PERSIST>
+// EXIT: interior rays, the kernel builds their exit rays itself (HitSink; scenes without meshes only) -- a
+// template parameter so that the main traversal does not carry that code (registers, instruction cache).
+template <bool COUNT, int MINB, bool FLAT, bool MESHES, bool PERSIST, bool EXIT>
 __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront wf, QueueIn qin, HitSink sink,
                                                             unsigned long long* ray_counter, unsigned long long* work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -304,7 +307,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
     if (threadIdx.x == 0) s_hits = s_next = 0u;
     SmemScene sm = stage_scene(S, smem_raw);  // ends with a barrier
     Work wk;
-    if (PERSIST) traverse_persistent<COUNT, MESHES>(S, sm, wf, qin, len, sink, &s_next, &s_hits, wk);
+    if (PERSIST) traverse_persistent<COUNT, MESHES, EXIT>(S, sm, wf, qin, len, sink, &s_next, &s_hits, wk);
     for (uint32_t base = 0; !PERSIST && base < len; base += kBlock) {
         uint32_t p;
         const bool valid = queue_item(qin, base + threadIdx.x, len, p);
@@ -315,7 +318,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
             scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
         else if (valid)
             scene_walk<COUNT, MESHES>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, best);
-        deliver(S, wf, sink, &s_hits, p, valid, best, mk3(d4.x, d4.y, d4.z));
+        deliver<EXIT>(S, wf, sink, &s_hits, p, valid, best, mk3(d4.x, d4.y, d4.z));
     }
     if (ray_counter && threadIdx.x == 0) {
         // rays this CTA traced: its region length, or its share of the identity queue (last tile cut at n)
@@ -337,8 +340,15 @@ template <bool COUNT, int MINB>
 static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const HitSink& sink,
                                  unsigned long long* ray_counter, unsigned long long* work) {
     const int grid = lc.grid;
-#define MCPT_TRAVERSE(FLAT, MESHES, PERSIST) \
-    k_traverse<COUNT, MINB, FLAT, MESHES, PERSIST><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink, ray_counter, work)
+#define MCPT_TRAVERSE(FLAT, MESHES, PERSIST)                                                                                        \
+    do {                                                                                                                            \
+        if (!MESHES && sink.exit_mode)                                                                                              \
+            k_traverse<COUNT, MINB, FLAT, MESHES, PERSIST, !MESHES><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink,    \
+                                                                                                              ray_counter, work);  \
+        else                                                                                                                        \
+            k_traverse<COUNT, MINB, FLAT, MESHES, PERSIST, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink,      \
+                                                                                                            ray_counter, work);    \
+    } while (0)
     if (S.n_flat > 0)
         MCPT_TRAVERSE(true, false, false);
     else if (S.n_meshes == 0) {
