@@ -195,6 +195,23 @@ int mcpt_trace_rays(mcpt_ctx* ctx, int64_t n, const float* o, const float* d,
 int mcpt_trace_rays_device(mcpt_ctx* ctx, int64_t n, const float* o4, const float* d4,
                            mcpt_hit* out_dev, int any_hit);
 
+/* Host-only inspection of the top-level tree the persistent warps would walk for `desc` (built exactly as
+ * mcpt_upload_scene builds it; no context and no CUDA device needed): sizes, depths, and the invariants the
+ * traversal relies on. top_sah as MCPT_OPT_TOP_SAH. Used by the CPU tests. */
+typedef struct mcpt_tree_stats {
+    int32_t nodes;          /* two-children nodes                                                        */
+    int32_t leaves;         /* leaf references (a sliced primitive counts once per slab box)             */
+    int32_t prims_reached;  /* distinct primitives that own at least one leaf                            */
+    int32_t prims_expected; /* primitives that own a leaf slot of the uploaded tree                      */
+    int32_t depth;          /* longest root-to-leaf path in two-children levels (the walk's stack bound) */
+    int32_t depth4;         /* ... in four-children levels                                               */
+    int32_t leaves4;        /* leaf references reachable through the four-children nodes                 */
+    int32_t violations;     /* child boxes that do not contain what is below them + sample points of a
+                               primitive's bounding cube that none of its leaf boxes contains            */
+    double sah_cost;        /* sum over nodes of child-box half-areas x leaves below / root half-area    */
+} mcpt_tree_stats;
+int mcpt_inspect_walk_tree(const mcpt_scene_desc* desc, int top_sah, mcpt_tree_stats* out);
+
 int mcpt_get_stats(mcpt_ctx* ctx, mcpt_stats* out);
 int mcpt_reset_stats(mcpt_ctx* ctx);
 /* synchronises the stream */

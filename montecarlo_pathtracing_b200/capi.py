@@ -53,6 +53,12 @@ class Stats(C.Structure):
                 ("boxes", C.c_uint64), ("prim_tests", C.c_uint64), ("tri_tests", C.c_uint64)]
 
 
+class TreeStats(C.Structure):  # mcpt_tree_stats
+    _fields_ = [("nodes", C.c_int32), ("leaves", C.c_int32), ("prims_reached", C.c_int32), ("prims_expected", C.c_int32),
+                ("depth", C.c_int32), ("depth4", C.c_int32), ("leaves4", C.c_int32), ("violations", C.c_int32),
+                ("sah_cost", C.c_double)]
+
+
 class StageTimes(C.Structure):
     _fields_ = [("ms", C.c_double * 8), ("launches", C.c_uint64 * 8)]
 
@@ -67,7 +73,7 @@ MCPT_SYMBOLS = [
     "mcpt_synchronize", "mcpt_set_option", "mcpt_upload_scene", "mcpt_resize", "mcpt_set_camera", "mcpt_set_params",
     "mcpt_clear", "mcpt_render", "mcpt_resolve", "mcpt_get_accum", "mcpt_bind_accum", "mcpt_read_accum",
     "mcpt_write_accum", "mcpt_reduce_nccl", "mcpt_trace_rays", "mcpt_trace_rays_device", "mcpt_get_stats",
-    "mcpt_reset_stats", "mcpt_get_stage_times",
+    "mcpt_reset_stats", "mcpt_get_stage_times", "mcpt_inspect_walk_tree",
 ]
 # every symbol include/mcpt_host.h declares
 MCPTH_SYMBOLS = [
@@ -121,6 +127,7 @@ def lib():
         L.mcpt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.mcpt_reset_stats.argtypes = [C.c_void_p]
         L.mcpt_get_stage_times.argtypes = [C.c_void_p, C.POINTER(StageTimes)]
+        L.mcpt_inspect_walk_tree.argtypes = [C.POINTER(SceneDesc), C.c_int, C.POINTER(TreeStats)]
         _lib = L
     return _lib
 

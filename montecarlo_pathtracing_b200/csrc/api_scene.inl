@@ -232,6 +232,60 @@ void fold_top4(const std::vector<DevNode2>& n2, std::vector<DevNode4>& n4) {
     }
 }
 
+// The two trees of the persistent walk from the uploaded tables: `prims` with type, fwd and slot filled in, `top`
+// the reference's heap-order tree with inflated boxes (index 1-based, leaf level = primitive ids).
+void build_walk_trees(const mcpt_scene_desc* d, const std::vector<DevPrim>& prims, const std::vector<DevNode>& top, bool top_sah,
+                      std::vector<DevNode2>& top2, std::vector<DevNode4>& top4) {
+    const int td = d->root.depth;
+    const uint32_t t_first_leaf = 1u << td;
+    // ---- the top-level tree of the persistent walk. Hit records do not depend on the tree (candidates are
+    // ranked by the reference's exact distance and visit order, intersect.cuh), so the persistent warps walk a
+    // tree of their own instead of the reference's median split with its cycling axis (bvh_gpu/bvh.cpp:34-93):
+    // a full-sweep SAH build over the primitives' (inflated) leaf boxes, one primitive per leaf, in the
+    // two-children node format of the mesh trees (top2, root = node 0) and folded into four-children nodes
+    // (top4). Measured on repo scene 8 (895 primitives): 69 -> see profiles/README.md box tests per ray.
+    // MCPT_OPT_TOP_SAH = 0 keeps the reference's topology.
+    top2.clear();
+    {
+        std::vector<TopItem> items;
+        for (uint32_t sl = 0; sl < t_first_leaf; ++sl) {
+            const int prim = d->root.ind[sl];
+            if (prim < 0 || prims[prim].slot != int(sl)) continue;  // each primitive once, at its first slot
+            const DevNode& nb = top[t_first_leaf + sl];
+            if (top_sah && slice_loose_primitive(prims[prim], nb, prim, items)) continue;
+            items.push_back(TopItem{{nb.lo.x, nb.lo.y, nb.lo.z}, {nb.hi.x, nb.hi.y, nb.hi.z}, prim});
+        }
+        if (top_sah && !items.empty()) {
+            build_top_sah(items, top2);
+        } else {
+            // the reference's own topology: node k-1 holds the boxes of heap children 2k and 2k+1
+            top2.resize(std::max<uint32_t>(t_first_leaf - 1, 1u));
+            if (td == 0) {
+                const int prim = d->root.ind[0];
+                set_child2(top2[0], 0, top[1], prim >= 0 ? ~prim : INT_MIN);
+                set_child2(top2[0], 1, empty_node(), INT_MIN);
+            }
+            for (uint32_t k = 1; k < t_first_leaf; ++k)
+                for (int j = 0; j < 2; ++j) {
+                    const uint32_t ch = 2 * k + uint32_t(j);
+                    int tok;
+                    if (ch < t_first_leaf)
+                        tok = int(ch - 1);
+                    else {
+                        const int prim = d->root.ind[ch - t_first_leaf];
+                        tok = prim >= 0 ? ~prim : INT_MIN;  // kTokEmpty
+                    }
+                    set_child2(top2[k - 1], j, top[ch], tok);
+                }
+        }
+    }
+    // ---- and with every second level folded away (DevNode4, scenes with meshes): a node at even depth
+    // holds its grandchildren (or a child, where that child is a leaf); stored at the index of the
+    // two-children node it replaces, the entries of odd depths stay unused
+    top4.assign(top2.size(), DevNode4{});
+    fold_top4(top2, top4);
+}
+
 }  // namespace
 
 int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
@@ -299,52 +353,10 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         if (!empty) top[k] = pack_node(d->root.bb[k - 1], aux);
     }
 
-    // ---- the top-level tree of the persistent walk. Hit records do not depend on the tree (candidates are
-    // ranked by the reference's exact distance and visit order, intersect.cuh), so the persistent warps walk a
-    // tree of their own instead of the reference's median split with its cycling axis (bvh_gpu/bvh.cpp:34-93):
-    // a full-sweep SAH build over the primitives' (inflated) leaf boxes, one primitive per leaf, in the
-    // two-children node format of the mesh trees (top2, root = node 0) and folded into four-children nodes
-    // (top4). Measured on repo scene 8 (895 primitives): 69 -> see profiles/README.md box tests per ray.
-    // MCPT_OPT_TOP_SAH = 0 keeps the reference's topology.
+    // ---- the trees of the persistent walk (build_walk_trees above)
     std::vector<DevNode2> top2;
-    {
-        std::vector<TopItem> items;
-        for (uint32_t sl = 0; sl < t_first_leaf; ++sl) {
-            const int prim = d->root.ind[sl];
-            if (prim < 0 || prims[prim].slot != int(sl)) continue;  // each primitive once, at its first slot
-            const DevNode& nb = top[t_first_leaf + sl];
-            if (c->opt_top_sah && slice_loose_primitive(prims[prim], nb, prim, items)) continue;
-            items.push_back(TopItem{{nb.lo.x, nb.lo.y, nb.lo.z}, {nb.hi.x, nb.hi.y, nb.hi.z}, prim});
-        }
-        if (c->opt_top_sah && !items.empty()) {
-            build_top_sah(items, top2);
-        } else {
-            // the reference's own topology: node k-1 holds the boxes of heap children 2k and 2k+1
-            top2.resize(std::max<uint32_t>(t_first_leaf - 1, 1u));
-            if (td == 0) {
-                const int prim = d->root.ind[0];
-                set_child2(top2[0], 0, top[1], prim >= 0 ? ~prim : INT_MIN);
-                set_child2(top2[0], 1, empty_node(), INT_MIN);
-            }
-            for (uint32_t k = 1; k < t_first_leaf; ++k)
-                for (int j = 0; j < 2; ++j) {
-                    const uint32_t ch = 2 * k + uint32_t(j);
-                    int tok;
-                    if (ch < t_first_leaf)
-                        tok = int(ch - 1);
-                    else {
-                        const int prim = d->root.ind[ch - t_first_leaf];
-                        tok = prim >= 0 ? ~prim : INT_MIN;  // kTokEmpty
-                    }
-                    set_child2(top2[k - 1], j, top[ch], tok);
-                }
-        }
-    }
-    // ---- and with every second level folded away (DevNode4, scenes with meshes): a node at even depth
-    // holds its grandchildren (or a child, where that child is a leaf); stored at the index of the
-    // two-children node it replaces, the entries of odd depths stay unused
-    std::vector<DevNode4> top4(top2.size());
-    fold_top4(top2, top4);
+    std::vector<DevNode4> top4;
+    build_walk_trees(d, prims, top, c->opt_top_sah != 0, top2, top4);
 
     // ---- small scenes: flat list of leaf boxes for the warp-coherent walk
     std::vector<DevNode> flat;
@@ -519,5 +531,125 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     trim_cache(c);
     c->scene = S;
     c->have_scene = true;
+    return MCPT_OK;
+}
+
+// ---- host-only inspection of the walk trees (CPU tests)
+int mcpt_inspect_walk_tree(const mcpt_scene_desc* d, int top_sah, mcpt_tree_stats* out) {
+    if (!d || !out || d->n_prims < 0 || (d->n_prims > 0 && !d->prim_data) || !d->root.bb || !d->root.ind || d->root.depth < 0 ||
+        d->root.depth > 30)
+        return MCPT_E_INVALID;
+    std::memset(out, 0, sizeof *out);
+    const int td = d->root.depth;
+    const uint32_t t_first_leaf = 1u << td, t_nodes = 2u << td;
+    std::vector<DevPrim> prims(d->n_prims);
+    for (int i = 0; i < d->n_prims; ++i) {
+        const mcpt_prim_data& pd = d->prim_data[i];
+        DevPrim& p = prims[i];
+        std::memset(&p, 0, sizeof p);
+        p.type = int(pd.type[0]);
+        p.slot = -1;
+        p.fwd = rows_of(p.type == MCPT_PRIM_MESH ? pd.mesh_transfo : pd.transfo);
+        if (p.type > MCPT_PRIM_ORIENTED_QUAD) p.type = -1;
+    }
+    std::vector<DevNode> top(t_nodes, empty_node());
+    for (uint32_t k = 1; k < t_nodes; ++k) {
+        int aux = -1;
+        if (k >= t_first_leaf) {
+            aux = d->root.ind[k - t_first_leaf];
+            if (aux >= d->n_prims) return MCPT_E_INVALID;
+            if (aux < 0) continue;
+            if (prims[aux].slot < 0) prims[aux].slot = int(k - t_first_leaf);
+        }
+        top[k] = pack_node(d->root.bb[k - 1], aux);
+    }
+    std::vector<DevNode2> top2;
+    std::vector<DevNode4> top4;
+    build_walk_trees(d, prims, top, top_sah != 0, top2, top4);
+    out->nodes = int(top2.size());
+    for (int i = 0; i < d->n_prims; ++i) out->prims_expected += prims[i].slot >= 0 ? 1 : 0;
+
+    auto child = [&](int node, int j, float lo[3], float hi[3]) {
+        const DevNode2& N = top2[node];
+        const float4& l = j ? N.lo1 : N.lo0;
+        const float4& h = j ? N.hi1 : N.hi0;
+        lo[0] = l.x; lo[1] = l.y; lo[2] = l.z;
+        hi[0] = h.x; hi[1] = h.y; hi[2] = h.z;
+        int tok;
+        std::memcpy(&tok, j ? &N.hi0.w : &N.lo0.w, sizeof tok);
+        return tok;
+    };
+    std::vector<std::vector<std::array<float, 6>>> boxes_of(d->n_prims);
+    double root_area = 0.0;
+    // iterative post-order: (node, depth); returns the box of each subtree and the leaves below it
+    struct Ret { float lo[3], hi[3]; int leaves; };
+    std::function<Ret(int, int)> visit = [&](int node, int depth) -> Ret {
+        Ret r{{FLT_MAX, FLT_MAX, FLT_MAX}, {-FLT_MAX, -FLT_MAX, -FLT_MAX}, 0};
+        out->depth = std::max(out->depth, depth + 1);
+        for (int j = 0; j < 2; ++j) {
+            float lo[3], hi[3];
+            const int tok = child(node, j, lo, hi);
+            if (tok == INT_MIN) continue;
+            int below = 1;
+            if (tok >= 0) {
+                if (tok >= int(top2.size()) || depth > 64) { ++out->violations; continue; }
+                const Ret sub = visit(tok, depth + 1);
+                below = sub.leaves;
+                for (int k = 0; k < 3; ++k)
+                    if (sub.lo[k] < lo[k] || sub.hi[k] > hi[k]) { ++out->violations; break; }
+            } else {
+                const int prim = ~tok;
+                if (prim < 0 || prim >= d->n_prims) { ++out->violations; continue; }
+                ++out->leaves;
+                boxes_of[prim].push_back({lo[0], lo[1], lo[2], hi[0], hi[1], hi[2]});
+            }
+            out->sah_cost += half_area(lo, hi) * below;
+            r.leaves += below;
+            for (int k = 0; k < 3; ++k) {
+                r.lo[k] = std::min(r.lo[k], lo[k]);
+                r.hi[k] = std::max(r.hi[k], hi[k]);
+            }
+        }
+        return r;
+    };
+    if (!top2.empty()) {
+        const Ret r = visit(0, 0);
+        root_area = half_area(r.lo, r.hi);
+    }
+    if (root_area > 0.0) out->sah_cost /= root_area;
+    // every primitive: points of its bounding cube (the reference's bound of the unit shape) lie in one of its leaf boxes
+    for (int i = 0; i < d->n_prims; ++i) {
+        if (boxes_of[i].empty()) continue;
+        ++out->prims_reached;
+        if (prims[i].type <= MCPT_PRIM_MESH) continue;
+        const Aff& f = prims[i].fwd;
+        for (int a = -2; a <= 2; ++a)
+            for (int b = -2; b <= 2; ++b)
+                for (int c2 = -2; c2 <= 2; ++c2) {
+                    const float x = 0.5f * a, y = 0.5f * b, z = (prims[i].type == MCPT_PRIM_ORIENTED_QUAD) ? 0.0f : 0.5f * c2;
+                    const float w[3] = {f.r0.x * x + f.r0.y * y + f.r0.z * z + f.r0.w, f.r1.x * x + f.r1.y * y + f.r1.z * z + f.r1.w,
+                                        f.r2.x * x + f.r2.y * y + f.r2.z * z + f.r2.w};
+                    bool inside = false;
+                    for (const auto& bx : boxes_of[i])
+                        inside = inside || (w[0] >= bx[0] && w[1] >= bx[1] && w[2] >= bx[2] && w[0] <= bx[3] && w[1] <= bx[4] && w[2] <= bx[5]);
+                    if (!inside) ++out->violations;
+                }
+    }
+    // the four-children fold reaches the same leaves
+    std::function<void(int, int)> visit4 = [&](int node, int depth) {
+        out->depth4 = std::max(out->depth4, depth + 1);
+        const DevNode4& W = top4[node];
+        for (int j = 0; j < 4; ++j) {
+            const int tok = (&W.tok.x)[j];
+            if (tok == INT_MIN) continue;
+            if (tok >= 0) {
+                if (tok >= int(top4.size()) || depth > 64) { ++out->violations; continue; }
+                visit4(tok, depth + 1);
+            } else {
+                ++out->leaves4;
+            }
+        }
+    };
+    if (!top4.empty()) visit4(0, 0);
     return MCPT_OK;
 }

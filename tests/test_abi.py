@@ -114,3 +114,33 @@ def test_python_constants_mirror_the_header_enums():
         assert getattr(capi, "OPT_" + name) == int(value), name
     stages = {int(v): n.lower() for n, v in re.findall(r"MCPT_STAGE_(\w+)\s*=\s*(\d+)", txt) if n != "COUNT"}
     assert tuple(stages[i] for i in range(len(stages))) == tuple(capi.STAGE_NAMES)
+
+
+@pytest.mark.parametrize("kind,kw", [(1, {}), (3, {}), (5, {}), (7, {}), (8, {}), ("c5", {}), ("mesh", {"n_meshes": 5, "tris_log2": 6})])
+def test_walk_tree_invariants_on_the_host(kind, kw):
+    """The top-level tree the persistent warps walk (full-sweep SAH, loose primitives as slab boxes, the
+    four-children fold) is host code: mcpt_inspect_walk_tree builds it as mcpt_upload_scene does -- no CUDA
+    device -- and reports the invariants the traversal relies on."""
+    import ctypes as C
+    from common import host_scene
+    s = host_scene(kind, 0.4, **kw)
+    s.finalize()
+    d = s.desc()
+    L = capi.lib()
+    st = {}
+    for top_sah in (1, 0):
+        t = capi.TreeStats()
+        assert L.mcpt_inspect_walk_tree(C.byref(d), top_sah, C.byref(t)) == 0
+        st[top_sah] = t
+        assert t.violations == 0                                   # boxes contain what is below them; slabs cover their primitive
+        assert t.prims_reached == t.prims_expected == s.nb_prim    # every primitive owns a leaf
+        assert t.leaves4 == t.leaves >= t.prims_reached            # the fold reaches the same leaves
+        assert t.depth <= 30                                       # one stack entry per level (kWalkStack)
+        assert t.depth4 <= (t.depth + 1) // 2 + 1
+    sah, ref = st[1], st[0]
+    assert sah.nodes == sah.leaves - 1                             # one primitive (or slab) per leaf, two children per node
+    assert sah.sah_cost <= ref.sah_cost * 1.001                    # never worse than the reference's median split
+    if kind == 8:
+        assert sah.leaves > sah.prims_reached                      # the rotated beams entered as slab boxes
+        assert sah.sah_cost < 0.7 * ref.sah_cost
+    assert L.mcpt_inspect_walk_tree(None, 1, C.byref(capi.TreeStats())) == capi.MCPT_E_INVALID
