@@ -94,9 +94,13 @@ enum {
                                       lane per tile. Set before mcpt_upload_scene. Same results. */
     MCPT_OPT_REFILL_LANES = 9,     /* persistent warps: idle lanes of a warp that trigger a refill from the queue,
                                       1..32; 0 = auto (8 with meshes, 32 without). Set before mcpt_upload_scene. */
-    MCPT_OPT_TOP_SAH = 10          /* 1 = the persistent warps walk a top-level tree built at upload by a full-sweep
+    MCPT_OPT_TOP_SAH = 10,         /* 1 = the persistent warps walk a top-level tree built at upload by a full-sweep
                                       SAH over the primitives' leaf boxes (default), 0 = the topology of the uploaded
                                       median-split tree. Set before mcpt_upload_scene. Same results. */
+    MCPT_OPT_TRACE_WALKER = 11     /* mcpt_trace_rays (closest hit): 0 = through the production traversal kernel of
+                                      mcpt_render with whatever walker the scene selected (default), 1 = the
+                                      one-ray-per-lane walk over the uploaded trees in the reference's visit order.
+                                      any_hit always takes the latter. Same records. */
 };
 
 /* wavefront stages, in launch order inside one bounce */

@@ -15,6 +15,7 @@
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 #include <functional>
 #include <new>
@@ -53,6 +54,8 @@ struct mcpt_ctx {
     size_t accum_bytes = 0;
     void* resolve_tmp = nullptr;  // device staging for host-destination resolves
     size_t resolve_tmp_bytes = 0;
+    char* trace_wf = nullptr;     // ray + hit sectors of mcpt_trace_rays through the production kernel (grow-only)
+    uint64_t trace_wf_slots = 0;
 
     // wavefront
     Wavefront wf{};
@@ -78,6 +81,7 @@ struct mcpt_ctx {
     int opt_refill_lanes = 0;
     int opt_traverse_occ = 0;  // 0 = auto
     int opt_count_work = 0;
+    int opt_trace_walker = 0;  // mcpt_trace_rays: 0 = the production kernel (k_traverse), 1 = the reference-order walk (k_trace)
 
     // stage profiling: (stage, start, stop) triples waiting to be read, plus a free list
     struct Span {
@@ -88,7 +92,7 @@ struct mcpt_ctx {
     std::vector<cudaEvent_t> free_events;
 
     uint64_t paths_started = 0;
-    unsigned long long launches_base = 0;
+    unsigned long long launches = 0;  // kernels launched by this context since the last mcpt_reset_stats
 };
 
 namespace {
@@ -162,7 +166,9 @@ LaunchCfg lcfg(const mcpt_ctx* c) {
     // measured: flat walk and persistent warps are best at 4 (latency hiding beats the spills of the
     // 64-register cap: +7..10 % over 3); the one-ray-per-lane tree walk at 3
     if (occ == 0) occ = (c->have_scene && (c->scene.n_flat > 0 || c->scene.persistent)) ? 4 : 3;
-    return LaunchCfg{c->sm_count, c->stream, occ};
+    LaunchCfg lc{c->sm_count, c->stream, occ};
+    lc.launches = const_cast<unsigned long long*>(&c->launches);
+    return lc;
 }
 
 // rows of the affine part of a column-major mat4
@@ -252,12 +258,11 @@ int mcpt_create(int device, mcpt_ctx** out) {
         return MCPT_E_NOMEM;
     }
     c->dev_stats = static_cast<unsigned long long*>(p);
-    cudaMemset(c->dev_stats, 0, kStatWords * sizeof(unsigned long long));
+    cudaMemsetAsync(c->dev_stats, 0, kStatWords * sizeof(unsigned long long), c->stream);
     c->prm.nb_bounces = 3;       // RTViewer defaults, montecarlo.cpp:126-141
     c->prm.refract_ind = 1.0f;
     c->user_params.nb_bounces = 3;
     c->user_params.refract_ind = 1.0f;
-    c->launches_base = launches_issued();
     *out = c;
     return MCPT_OK;
 }
@@ -272,6 +277,7 @@ int mcpt_destroy(mcpt_ctx* c) {
     if (c->accum_owned && c->accum) cudaFree(c->accum);
     if (c->dev_stats) cudaFree(c->dev_stats);
     if (c->resolve_tmp) cudaFree(c->resolve_tmp);
+    if (c->trace_wf) cudaFree(c->trace_wf);
     for (auto& sp : c->spans) {
         cudaEventDestroy(sp.a);
         cudaEventDestroy(sp.b);
@@ -314,6 +320,7 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
         case MCPT_OPT_COUNT_WORK: c->opt_count_work = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TOP_SAH: c->opt_top_sah = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_TRACE_WALKER: c->opt_trace_walker = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TRAVERSE_OCC:
             if (value != 0 && (value < 2 || value > 4))
                 return fail(c, MCPT_E_INVALID, "traverse occupancy must be 0 (auto), 2, 3 or 4 CTAs per SM");

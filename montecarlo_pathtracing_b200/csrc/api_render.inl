@@ -343,8 +343,31 @@ int mcpt_trace_rays_device(mcpt_ctx* c, int64_t n, const float* o4, const float*
     if (!c->have_scene) return fail(c, MCPT_E_INVALID, "mcpt_trace_rays before mcpt_upload_scene");
     if (n == 0) return MCPT_OK;
     CK(c, cudaSetDevice(c->device));
-    launch_trace(lcfg(c), c->scene, n, reinterpret_cast<const float4*>(o4), reinterpret_cast<const float4*>(d4), out_dev,
-                 any_hit != 0);
+    const float4 *o = reinterpret_cast<const float4*>(o4), *d = reinterpret_cast<const float4*>(d4);
+    if (any_hit || c->opt_trace_walker != 0) {
+        launch_trace(lcfg(c), c->scene, n, o, d, out_dev, any_hit != 0);
+        CK(c, cudaGetLastError());
+        return MCPT_OK;
+    }
+    // the production kernel over a private pair of sector planes (ray, hit)
+    if (n > 0x7fffff00ll) return fail(c, MCPT_E_INVALID, "batch of %lld rays is too large", (long long)n);
+    if (uint64_t(n) > c->trace_wf_slots) {
+        CK(c, cudaStreamSynchronize(c->stream));
+        if (c->trace_wf) cudaFree(c->trace_wf);
+        c->trace_wf = nullptr;
+        c->trace_wf_slots = 0;
+        void* p = nullptr;
+        cudaError_t e = cudaMalloc(&p, size_t(n) * 64);
+        if (e != cudaSuccess) return fail(c, MCPT_E_NOMEM, "trace sectors: %s", cudaGetErrorString(e));
+        c->trace_wf = static_cast<char*>(p);
+        c->trace_wf_slots = uint64_t(n);
+    }
+    Wavefront wf{};
+    wf.rec = c->trace_wf;
+    wf.plane = size_t(c->trace_wf_slots) * 32;
+    LaunchCfg lq = lcfg(c);
+    lq.grid = wavefront_grid(c, uint64_t(n));
+    launch_trace_wavefront(lq, c->scene, n, o, d, wf, queue_cap(c, uint64_t(n)), out_dev);
     CK(c, cudaGetLastError());
     return MCPT_OK;
 }
@@ -354,27 +377,33 @@ int mcpt_trace_rays(mcpt_ctx* c, int64_t n, const float* o, const float* d, mcpt
     if (!c->have_scene) return fail(c, MCPT_E_INVALID, "mcpt_trace_rays before mcpt_upload_scene");
     if (n == 0) return MCPT_OK;
     CK(c, cudaSetDevice(c->device));
-    std::vector<float4> ho(n), hd(n);
+    std::vector<float4> ho, hd;
+    try {
+        ho.resize(size_t(n));
+        hd.resize(size_t(n));
+    } catch (const std::exception&) {
+        return fail(c, MCPT_E_NOMEM, "host staging of %lld rays", (long long)n);
+    }
     for (int64_t i = 0; i < n; ++i) {
         ho[i] = make_float4(o[3 * i], o[3 * i + 1], o[3 * i + 2], 0.0f);
         hd[i] = make_float4(d[3 * i], d[3 * i + 1], d[3 * i + 2], 0.0f);
     }
     float4 *dev_o = nullptr, *dev_d = nullptr;
     mcpt_hit* dev_h = nullptr;
+    int rc = MCPT_OK;
     cudaError_t e = cudaMalloc(&dev_o, n * sizeof(float4));
     if (e == cudaSuccess) e = cudaMalloc(&dev_d, n * sizeof(float4));
     if (e == cudaSuccess) e = cudaMalloc(&dev_h, n * sizeof(mcpt_hit));
     if (e == cudaSuccess) e = cudaMemcpyAsync(dev_o, ho.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
     if (e == cudaSuccess) e = cudaMemcpyAsync(dev_d, hd.data(), n * sizeof(float4), cudaMemcpyHostToDevice, c->stream);
-    if (e == cudaSuccess) {
-        launch_trace(lcfg(c), c->scene, n, dev_o, dev_d, dev_h, any_hit != 0);
-        e = cudaGetLastError();
-    }
-    if (e == cudaSuccess) e = cudaMemcpyAsync(out, dev_h, n * sizeof(mcpt_hit), cudaMemcpyDeviceToHost, c->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) rc = mcpt_trace_rays_device(c, n, &dev_o->x, &dev_d->x, dev_h, any_hit);
+    if (e == cudaSuccess && rc == MCPT_OK) e = cudaMemcpyAsync(out, dev_h, n * sizeof(mcpt_hit), cudaMemcpyDeviceToHost, c->stream);
+    cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    if (e == cudaSuccess) e = e2;
     cudaFree(dev_o);
     cudaFree(dev_d);
     cudaFree(dev_h);
+    if (rc != MCPT_OK) return rc;
     if (e != cudaSuccess) return fail(c, MCPT_E_CUDA, "trace_rays: %s", cudaGetErrorString(e));
     return MCPT_OK;
 }
@@ -388,7 +417,7 @@ int mcpt_get_stats(mcpt_ctx* c, mcpt_stats* out) {
     out->paths = c->paths_started;
     out->rays = h[0];
     out->segments = h[1];
-    out->launches = launches_issued() - c->launches_base;
+    out->launches = c->launches;
     out->boxes = h[2];
     out->prim_tests = h[3];
     out->tri_tests = h[4];
@@ -400,9 +429,11 @@ int mcpt_get_stage_times(mcpt_ctx* c, mcpt_stage_times* out) {
     CK(c, cudaSetDevice(c->device));
     CK(c, cudaStreamSynchronize(c->stream));
     std::memset(out, 0, sizeof *out);
+    const bool dump = std::getenv("MCPT_DUMP_SPANS") != nullptr;  // diagnostic: every launch's stage and time on stderr
     for (auto& sp : c->spans) {
         float ms = 0.0f;
         if (cudaEventElapsedTime(&ms, sp.a, sp.b) == cudaSuccess) out->ms[sp.stage] += ms;
+        if (dump) std::fprintf(stderr, "span %d %.4f\n", sp.stage, ms);
         out->launches[sp.stage] += 1;
         c->free_events.push_back(sp.a);
         c->free_events.push_back(sp.b);
@@ -416,7 +447,7 @@ int mcpt_reset_stats(mcpt_ctx* c) {
     CK(c, cudaSetDevice(c->device));
     CK(c, cudaMemsetAsync(c->dev_stats, 0, kStatWords * sizeof(unsigned long long), c->stream));
     c->paths_started = 0;
-    c->launches_base = launches_issued();
+    c->launches = 0;
     return MCPT_OK;
 }
 

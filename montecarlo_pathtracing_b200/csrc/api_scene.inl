@@ -7,7 +7,7 @@ template <class T>
 int upload_vec(mcpt_ctx* c, const std::vector<T>& h, T** out) {
     int rc = dev_alloc(c, c->scene_allocs, out, h.size());
     if (rc) return rc;
-    if (!h.empty()) CK(c, cudaMemcpy(*out, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+    if (!h.empty()) CK(c, cudaMemcpyAsync(*out, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice, c->stream));
     return MCPT_OK;
 }
 
@@ -15,7 +15,7 @@ template <class T>
 int upload_raw(mcpt_ctx* c, const T* h, size_t count, T** out) {
     int rc = dev_alloc(c, c->scene_allocs, out, count);
     if (rc) return rc;
-    if (count) CK(c, cudaMemcpy(*out, h, count * sizeof(T), cudaMemcpyHostToDevice));
+    if (count) CK(c, cudaMemcpyAsync(*out, h, count * sizeof(T), cudaMemcpyHostToDevice, c->stream));
     return MCPT_OK;
 }
 
@@ -288,8 +288,23 @@ void build_walk_trees(const mcpt_scene_desc* d, const std::vector<DevPrim>& prim
 
 }  // namespace
 
+static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d);
+
+// the C ABI never throws: host allocation failures of the re-pack become MCPT_E_NOMEM
 int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     if (!c || !d) return MCPT_E_INVALID;
+    try {
+        return upload_scene_impl(c, d);
+    } catch (const std::bad_alloc&) {
+        c->have_scene = false;
+        return fail(c, MCPT_E_NOMEM, "host allocation failed while re-packing the scene");
+    } catch (const std::exception& e) {
+        c->have_scene = false;
+        return fail(c, MCPT_E_INVALID, "scene upload: %s", e.what());
+    }
+}
+
+static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     CK(c, cudaSetDevice(c->device));
     if (d->n_prims < 0 || (d->n_prims > 0 && !d->prim_data)) return fail(c, MCPT_E_INVALID, "bad primitive table");
     if (d->n_meshes < 0 || (d->n_meshes > 0 && !d->meshes)) return fail(c, MCPT_E_INVALID, "bad mesh table");
@@ -329,6 +344,13 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
         } else {
             p.fwd = rows_of(pd.transfo);
             if (p.type > MCPT_PRIM_ORIENTED_QUAD) p.type = -1;  // the shader's switch has no such case
+        }
+        {
+            const float cx = std::sqrt(p.fwd.r0.x * p.fwd.r0.x + p.fwd.r1.x * p.fwd.r1.x + p.fwd.r2.x * p.fwd.r2.x);
+            const float cy = std::sqrt(p.fwd.r0.y * p.fwd.r0.y + p.fwd.r1.y * p.fwd.r1.y + p.fwd.r2.y * p.fwd.r2.y);
+            const float cz = std::sqrt(p.fwd.r0.z * p.fwd.r0.z + p.fwd.r1.z * p.fwd.r1.z + p.fwd.r2.z * p.fwd.r2.z);
+            const float smin = std::min(cx, std::min(cy, cz));
+            p.inv_smin = (smin > 1e-20f && std::isfinite(smin)) ? 1.0f / smin : 1e30f;  // degenerate: always both roots
         }
         color[i] = make_float4(pd.color[0], pd.color[1], pd.color[2], pd.color[3]);
         mat[i] = make_float4(pd.mat_info[0], pd.mat_info[1], pd.mat_info[2], pd.mat_info[3]);
@@ -424,7 +446,8 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
                 (rc = dev_alloc(c, c->scene_allocs, &dn4, size_t(std::max(n_leaves - 1, 1)))) ||
                 (rc = dev_alloc(c, c->scene_allocs, &dt2, size_t(n_leaves) * kMeshLeafTris)))
                 return rc;
-            CK(c, cudaMemcpy(d_slot, slot_of_tri.data(), slot_of_tri.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+            CK(c, cudaMemcpyAsync(d_slot, slot_of_tri.data(), slot_of_tri.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
+            CK(c, cudaStreamSynchronize(c->stream));  // slot_of_tri is a temporary of this iteration
             unsigned long long launched = 0;
             cudaError_t e;
             {
@@ -433,7 +456,7 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
                 e = build_mesh_lbvh(c->stream, dp, di, int(md.n_tris), d_slot, lo, hi, dn2, dn4, dt2, n_leaves, build_ws, build_ws_bytes,
                                     &launched);
             }
-            add_launches(launched);
+            c->launches += launched;
             CK(c, e);
             M.nodes2 = dn2;
             M.nodes4 = dn4;
@@ -524,10 +547,10 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
     // (measured: 1.8x on the 1 M-triangle workload, +20 % on a tree of 122 analytic primitives)
     S.persistent = (c->opt_persistent && flat.empty() && (d->n_meshes == 0 || c->opt_mesh_bvh)) ? 1 : 0;
     S.refill_lanes = c->opt_refill_lanes > 0 ? c->opt_refill_lanes : (d->n_meshes > 0 ? 8 : 32);
-    if (!build_allocs.empty()) {
-        CK(c, cudaStreamSynchronize(c->stream));  // the tree builds are done: their scratch can go
-        free_all(c, build_allocs);
-    }
+    // every copy above was enqueued on the context's stream from host temporaries of this call (pageable memory:
+    // the runtime stages them, but the order against later work on c->stream is only defined in-stream)
+    CK(c, cudaStreamSynchronize(c->stream));
+    if (!build_allocs.empty()) free_all(c, build_allocs);  // the tree builds are done: their scratch can go
     trim_cache(c);
     c->scene = S;
     c->have_scene = true;
@@ -535,7 +558,15 @@ int mcpt_upload_scene(mcpt_ctx* c, const mcpt_scene_desc* d) {
 }
 
 // ---- host-only inspection of the walk trees (CPU tests)
+static int inspect_walk_tree_impl(const mcpt_scene_desc* d, int top_sah, mcpt_tree_stats* out);
 int mcpt_inspect_walk_tree(const mcpt_scene_desc* d, int top_sah, mcpt_tree_stats* out) {
+    try {
+        return inspect_walk_tree_impl(d, top_sah, out);
+    } catch (const std::exception&) {
+        return MCPT_E_NOMEM;
+    }
+}
+static int inspect_walk_tree_impl(const mcpt_scene_desc* d, int top_sah, mcpt_tree_stats* out) {
     if (!d || !out || d->n_prims < 0 || (d->n_prims > 0 && !d->prim_data) || !d->root.bb || !d->root.ind || d->root.depth < 0 ||
         d->root.depth > 30)
         return MCPT_E_INVALID;

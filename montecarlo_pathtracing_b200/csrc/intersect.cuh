@@ -91,7 +91,9 @@ struct Cand {
     bool c1, c2;
 };
 
-MCPT_DEV void sphere_test(Cand& k, f3 O, f3 D) {
+// tol: the rounding noise of a world-space distance from this ray's origin, in local units (prim_test: the
+// culling slack, ~1e-4 |Ow|, over the smallest scale of the primitive's transform)
+MCPT_DEV void sphere_test(Cand& k, f3 O, f3 D, float tol) {
     float OO = dot3(O, O);
     float OD = dot3(O, D);
     float D2 = dot3(D, D);
@@ -102,9 +104,10 @@ MCPT_DEV void sphere_test(Cand& k, f3 O, f3 D) {
         if (a > MCPT_EPSILON) {
             k.a1 = a;
             k.c1 = true;
-            // The far root loses against the near one under the shader's strict '<' whenever the
-            // two are separated by more than rounding noise; it is evaluated only when they are not.
-            if (a > 1e-3f && 2.0f * sq > 1e-3f * (a * D2)) return;
+            // The far root loses against the near one under the shader's strict '<' whenever the two are
+            // separated by more than the rounding noise of dist = |Ow - Pg| (which grows with |Ow|, not with
+            // the hit distance: hence tol); it is evaluated only when they are not.
+            if (a > 1e-3f && 2.0f * sq > (1e-3f * a + tol) * D2) return;
         }
         a = -(OD - sq) / D2;
         if (a > MCPT_EPSILON) {

@@ -13,10 +13,6 @@
 
 namespace mcpt {
 
-static unsigned long long g_launches = 0;
-unsigned long long launches_issued() { return g_launches; }
-void add_launches(unsigned long long n) { g_launches += n; }
-
 constexpr int kBlock = 256;
 
 static inline int grid_for(const LaunchCfg& lc, uint64_t n, int blocks_per_sm) {
@@ -114,7 +110,7 @@ void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& 
                    int n_passes, uint32_t npix) {
     uint64_t total = uint64_t(npix) * uint64_t(n_passes);
     k_raygen<<<grid_for(lc, total, 16), kBlock, 0, lc.stream>>>(prm, cam, wf, first_pass, n_passes, npix);
-    ++g_launches;
+    lc.count();
 }
 
 // ----------------------------------------------------------------- traverse
@@ -377,7 +373,7 @@ void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const
         launch_traverse_kind<false, 3>(lc, S, wf, qin, sink, ray_counter, nullptr);
     else
         launch_traverse_kind<false, 2>(lc, S, wf, qin, sink, ray_counter, nullptr);
-    ++g_launches;
+    lc.count();
 }
 
 // traverse_all_bvh as a callable on caller-provided rays (mcpt_trace_rays)
@@ -436,7 +432,70 @@ void launch_trace(const LaunchCfg& lc, const DevScene& S, int64_t n, const float
                   bool any_hit) {
     k_trace<<<grid_for(lc, uint64_t(n), 8), kBlock, S.smem_bytes, lc.stream>>>(S, n, o, d, static_cast<mcpt_hit*>(hits_out),
                                                                                any_hit ? 1 : 0);
-    ++g_launches;
+    lc.count();
+}
+
+// ---- the same callable through the PRODUCTION traversal kernel
+// The ray batches of the parity tests go through k_traverse itself -- flat list, heap walk, persistent warps over
+// the SAH top2 / top4 trees and the GPU-built mesh trees, whichever mcpt_upload_scene selected -- exactly as a
+// render launches it for the debug shaders: identity queue, no hit queue, every record to the hit sector
+// (deliver()). Two thin kernels move the caller's rays into ray sectors and the hit sectors into mcpt_hit
+// records. The hit sector carries {pl, prim, sub}; dist and pg are functions of those and of the ray origin
+// (offer_at: Pg = fwd * Pl, dist = |O - Pg|) and are re-evaluated here with the same unfused arithmetic.
+__global__ void __launch_bounds__(kBlock) k_trace_pack(int64_t n, const float4* __restrict__ o, const float4* __restrict__ d,
+                                                        Wavefront wf) {
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        const float4 o4 = o[i], d4 = d[i];
+        wf.store_ray(size_t(i), make_float4(o4.x, o4.y, o4.z, 0.0f), make_float4(d4.x, d4.y, d4.z, 0.0f));
+    }
+}
+
+__global__ void __launch_bounds__(kBlock) k_trace_unpack(DevScene S, int64_t n, const float4* __restrict__ o, Wavefront wf,
+                                                          mcpt_hit* __restrict__ out) {
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        f3 pl, D;
+        int prim, sub;
+        wf.load_hit(size_t(i), pl, prim, sub, D);
+        const float4 o4 = o[i];
+        mcpt_hit h;
+        h.index = prim;
+        h.pl[0] = pl.x;
+        h.pl[1] = pl.y;
+        h.pl[2] = pl.z;
+        if (prim >= 0) {
+            const DevPrim* pp = S.prims + prim;
+            Aff fwd;
+            fwd.r0 = pp->fwd.r0;
+            fwd.r1 = pp->fwd.r1;
+            fwd.r2 = pp->fwd.r2;
+            const f3 pg = xform_point(fwd, pl);
+            h.dist = distance3(mk3(o4.x, o4.y, o4.z), pg);
+            h.pg[0] = pg.x;
+            h.pg[1] = pg.y;
+            h.pg[2] = pg.z;
+            h.shape = pp->type;
+            h.tri_index = (pp->type == MCPT_PRIM_MESH) ? sub : -1;
+            h.dir = (pp->type == MCPT_PRIM_MESH) ? 0 : sub;
+        } else {
+            h.dist = MCPT_FLT_MAX;
+            h.pg[0] = h.pg[1] = h.pg[2] = 0.0f;
+            h.shape = -1;
+            h.tri_index = -1;
+            h.dir = -1;
+        }
+        out[i] = h;
+    }
+}
+
+void launch_trace_wavefront(const LaunchCfg& lq, const DevScene& S, int64_t n, const float4* o, const float4* d, Wavefront wf,
+                            uint32_t cap, void* hits_out) {
+    k_trace_pack<<<grid_for(lq, uint64_t(n), 16), kBlock, 0, lq.stream>>>(n, o, d, wf);
+    lq.count();
+    const QueueIn identity{nullptr, nullptr, uint32_t(n), cap};
+    const QueueOut none{nullptr, nullptr, 0};
+    launch_traverse(lq, S, wf, identity, none, nullptr, nullptr, nullptr);
+    k_trace_unpack<<<grid_for(lq, uint64_t(n), 16), kBlock, 0, lq.stream>>>(S, n, o, wf, static_cast<mcpt_hit*>(hits_out));
+    lq.count();
 }
 
 // (shade / compact / accumulate / resolve follow in kernels_shade.inl)

@@ -34,6 +34,10 @@ struct LaunchCfg {
     cudaStream_t stream;
     int traverse_occ = 2;  // resident CTAs per SM the traversal kernel is compiled for (register cap)
     int grid = 1;          // CTAs of every queue-driven kernel of the current batch (fixed: regions are per CTA)
+    unsigned long long* launches = nullptr;  // the owning context's launch counter (host side, one caller thread per context)
+    void count(unsigned long long n = 1) const {
+        if (launches) *launches += n;
+    }
 };
 
 void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,
@@ -51,8 +55,10 @@ void launch_resolve(const LaunchCfg& lc, const float4* accum, int w, int h, floa
                     bool rgba8);
 void launch_trace(const LaunchCfg& lc, const DevScene& S, int64_t n, const float4* o, const float4* d, void* hits_out,
                   bool any_hit);
-// counts launches issued through the functions above (host side)
-unsigned long long launches_issued();
-void add_launches(unsigned long long n);
+// closest-hit search of caller-provided rays through the PRODUCTION traversal kernel (k_traverse with whatever walker
+// the scene selected): rays are packed into ray sectors of `wf`, traced over the identity queue with every record
+// delivered to the hit sector, and unpacked into mcpt_hit records (mcpt_trace_rays, MCPT_OPT_TRACE_WALKER = 0)
+void launch_trace_wavefront(const LaunchCfg& lq, const DevScene& S, int64_t n, const float4* o, const float4* d, Wavefront wf,
+                            uint32_t cap, void* hits_out);
 
 }  // namespace mcpt

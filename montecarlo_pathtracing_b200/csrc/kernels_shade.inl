@@ -5,8 +5,8 @@
 // One iteration of random_path's loop after traverse_all_bvh
 // (tp/montecarlo.frag:117-175), or one of the two debug shaders
 // (tp/montecarlo_mat.frag:5-20, tp/montecarlo_mat_tr.frag:5-20) when mode != 0.
-// In the Monte Carlo mode the queue holds only rays that hit something (k_traverse ends the
-// others). Paths that go on are appended to `next` -- and to `interior` when the new ray starts
+// In the Monte Carlo mode the queue holds only rays that hit something (a ray that leaves the scene keeps its
+// path state and k_accumulate evaluates the fake sky). Paths that go on are appended to `next` -- and to `interior` when the new ray starts
 // inside a transparent primitive -- by warp_append into this CTA's regions of the two queues
 // (kernels.cu): that is the whole compaction, there is no separate pass and no flag array.
 // (Measured and dropped: prefetch.global.L2 of the next path's state at the end of an iteration, +3 % time;
@@ -133,7 +133,7 @@ void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, 
     else
         k_shade<false><<<lc.grid, kBlock, 0, lc.stream>>>(S, prm, wf, qin, nx, in, first_bounce ? 1 : 0, last_bounce ? 1 : 0,
                                                           first_pass, npix, seg_counter);
-    ++g_launches;
+    lc.count();
 }
 
 // --------------------------------------------------------------- shade_exit
@@ -164,7 +164,7 @@ __global__ void __launch_bounds__(kBlock) k_shade_exit(DevScene S, DevParams prm
 
 void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin) {
     k_shade_exit<<<lc.grid, kBlock, 0, lc.stream>>>(S, prm, wf, qin);
-    ++g_launches;
+    lc.count();
 }
 
 // --------------------------------------------------------------- accumulate
@@ -205,7 +205,7 @@ __global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __r
 
 void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes, uint32_t batch) {
     k_accumulate<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(wf, accum, npix, n_passes, batch);
-    ++g_launches;
+    lc.count();
 }
 
 // ------------------------------------------------------------------ resolve
@@ -241,5 +241,5 @@ void launch_resolve(const LaunchCfg& lc, const float4* accum, int w, int h, floa
     k_resolve<<<grid_for(lc, total, 16), kBlock, 0, lc.stream>>>(accum, w, h, divisor, subsampling,
                                                                  rgba8 ? nullptr : static_cast<float*>(dst),
                                                                  rgba8 ? static_cast<uchar4*>(dst) : nullptr);
-    ++g_launches;
+    lc.count();
 }

@@ -41,7 +41,7 @@ struct DevPrim {
     int32_t type; // MCPT_PRIM_*
     int32_t mesh; // mesh id for type 0, else -1
     int32_t slot; // leaf slot of this primitive in the top-level tree (visit rank)
-    int32_t pad;
+    float inv_smin; // 1 / the smallest column norm of fwd: world noise -> local units (sphere_test)
     float4 pad2;
 };
 static_assert(sizeof(DevPrim) == 128, "DevPrim must be 128 bytes");

@@ -265,7 +265,7 @@ MCPT_DEV void prim_test(Work& wk, const DevScene& S, const SmemScene& sm, int p,
                     mesh_walk<COUNT>(wk, M, sm.mesh_nodes, Oi, Di, O, fwd, p, tslot, slack, best);
             }
             break;
-        case MCPT_PRIM_SPHERE: sphere_test(k, Oi, Di); break;
+        case MCPT_PRIM_SPHERE: sphere_test(k, Oi, Di, slack * pp->inv_smin); break;
         case MCPT_PRIM_CUBE: cube_test(k, Oi, Di); break;
         case MCPT_PRIM_CYLINDER: cylinder_test(k, Oi, Di); break;
         case MCPT_PRIM_CONE: cone_test(k, Oi, Di, O, S.leaf_bb + 6 * p); break;

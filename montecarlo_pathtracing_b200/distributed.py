@@ -33,13 +33,18 @@ class SplitRenderer:
     def __init__(self, ctx, width, height, rank=0, world=1, group=None):
         import torch
         self.ctx, self.rank, self.world, self.group = ctx, rank, world, group
+        # zero_(), k_accumulate and the reduce must be ordered on ONE stream: the context launches on torch's
+        # current stream from here on (its own stream is non-blocking and would not be ordered against torch's)
+        # (handle 0 is torch's legacy default stream; mcpt_set_stream reads NULL as "own stream", so it is passed
+        # as cudaStreamLegacy = 1)
+        ctx.set_stream(torch.cuda.current_stream().cuda_stream or 1)
         ctx.resize(width, height)
         self.accum = torch.zeros(height * width * 4, dtype=torch.float32, device="cuda")
         ctx.bind_accum(self.accum.data_ptr(), self.accum.numel() * 4)
 
     def render(self, n_passes, first_pass=0, root=0):
-        """Clear, trace this rank's share of the passes, reduce to root. Asynchronous on the current
-        torch stream (make it the context's stream with Context.set_stream)."""
+        """Clear, trace this rank's share of the passes, reduce to root. Asynchronous on the torch
+        stream that was current when the renderer was made (the context launches on it)."""
         first, count = pass_range(self.rank, self.world, n_passes, first_pass)
         self.accum.zero_()
         self.ctx.render(first, count)

@@ -60,6 +60,8 @@ def lib(kind="port"):
         L.oracle_tex_data.restype = vp
         L.oracle_set_uniforms.argtypes = [vp, C.c_int, C.c_float, C.c_float, C.c_int, fp, fp]
         L.oracle_set_threads.argtypes = [C.c_int]
+        if hasattr(L, "oracle_set_ulp_perturb"):
+            L.oracle_set_ulp_perturb.argtypes = [C.c_int]
         L.oracle_trace.argtypes = [vp, C.c_int64, fp, fp, vp, C.c_int, vp]
         L.oracle_render.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, fp, C.c_int, C.c_int, vp]
         L.oracle_rng_stream.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, C.c_int, fp, vp]
@@ -243,6 +245,10 @@ class Oracle:
 
     def set_threads(self, n=0):
         return self.L.oracle_set_threads(n)
+
+    def set_ulp_perturb(self, n=0):
+        """Port oracle only: shift every sin / cos / log / pow result of the bounce sampler by n ulps."""
+        self.L.oracle_set_ulp_perturb(int(n))
 
     def trace(self, o, d, any_hit=False):
         o, d = _f32(o).reshape(-1, 3), _f32(d).reshape(-1, 3)

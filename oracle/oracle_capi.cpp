@@ -128,6 +128,9 @@ void oracle_set_uniforms(OracleCtx* c, int nb_bounces, float refract_ind, float 
     if (invPV) std::memcpy(c->U.invPV, invPV, sizeof c->U.invPV);
 }
 
+// sensitivity probe: shift every sin / cos / log / pow result of the bounce sampler by n ulps (process-wide; 0 = off)
+void oracle_set_ulp_perturb(int n) { oracle::g_ulp_perturb = n; }
+
 int oracle_set_threads(int n) {
     if (n > 0) omp_set_num_threads(n);
     return omp_get_max_threads();

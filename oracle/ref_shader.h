@@ -120,4 +120,6 @@ private:
 // (v1,v2,v3)); sets Ori_in, Dir_in, screen_tc of `s`.
 void setup_fragment(Shader& s, int x, int y, int w, int h);
 
+extern int g_ulp_perturb;  // sensitivity probe, ref_shader_path.cpp
+
 }  // namespace oracle

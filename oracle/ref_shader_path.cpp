@@ -10,6 +10,17 @@ namespace oracle {
 static const float FLT_MAX_ = 3.402823e38f;
 static const float PI = 2.0f * acosf(0.0f);
 static const float BIAS = 1e-2f;
+
+// Sensitivity probe (tests only): move the result of every transcendental call of the bounce sampler by
+// g_ulp_perturb ulps. GLSL leaves sin / cos / log / pow to the driver with errors of several ulps, so two
+// conforming implementations of the reference differ by this much; the tests use it to measure how far fixed-seed
+// images of a scene may drift apart for that reason alone (chaotic scenes: tests/test_oracle_golden.py).
+int g_ulp_perturb = 0;
+static inline float ulps(float v) {
+    for (int k = 0; k < g_ulp_perturb; ++k) v = nextafterf(v, INFINITY);
+    for (int k = 0; k > g_ulp_perturb; --k) v = nextafterf(v, -INFINITY);
+    return v;
+}
 enum { CODE_MESH = 0, CODE_SPHERE = 1, CODE_CUBE = 2, CODE_CYLINDER = 3, CODE_CONE = 4, CODE_ORIENTED_QUAD = 5 };
 
 // raytracer_func.frag:642-678
@@ -184,10 +195,10 @@ vec4 Shader::intersection_mat_info() { return read_material(closest_intersection
 vec3 Shader::sample_hemisphere(float roughness) {
     float alpha = roughness * roughness;
     float beta = 2.0f * PI * random_float();
-    float tanTheta2 = -alpha * alpha * logf(1.0f - random_float());
+    float tanTheta2 = -alpha * alpha * ulps(logf(1.0f - random_float()));
     float cosTheta = 1.0f / sqrtf(1.0f + tanTheta2);
     float sinTheta = sqrtf(glsl::max(0.0f, 1.0f - cosTheta * cosTheta));
-    vec3 localDir = V3(cosf(beta) * sinTheta, sinf(beta) * sinTheta, cosTheta);
+    vec3 localDir = V3(ulps(cosf(beta)) * sinTheta, ulps(sinf(beta)) * sinTheta, cosTheta);
     return normalize(localDir);
 }
 
@@ -249,7 +260,7 @@ vec3 Shader::random_path(vec3 Dir, vec3 Orig) {
         vec3 R = reflect(-ray, N);
         vec3 E = normalize(O - P);
         float se = mix(100.0f, 2.0f, mat.y);
-        float spec = powf(glsl::max(0.0f, dot(E, R)), se);
+        float spec = ulps(powf(glsl::max(0.0f, dot(E, R)), se));
         total = total + (colrgb * 0.1f + attenu * mat.z * (1.0f - mat.x) * col.w);
         if (mat.z <= 0.5f && !(stHead == 9 - 1)) {
             if (mat.x > 0 && col.w == 1) {  // reflection

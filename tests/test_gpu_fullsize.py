@@ -104,26 +104,47 @@ def million():
 
 
 def test_config3_million_triangles_traversal(million):
-    """Hit records on the 2^20-triangle scene: the GPU-built trees (mcpt_trace_rays walks the two-children
-    form) and the uploaded median-split trees return the same records bit for bit on 2^20 random rays, and
-    both equal the oracle on a subset."""
+    """Hit records on the 2^20-triangle scene, 2^20 random rays through the PRODUCTION kernel (mcpt_trace_rays
+    runs k_traverse itself): the four-children persistent walk over the GPU-built trees (what bench.py times),
+    the one-ray-per-lane walk over the two-children trees, the walk over the uploaded median-split trees and
+    k_trace return the same records bit for bit, and equal the oracle on a subset."""
     s, o = million
     ro, rd = random_rays(s.prim_data(), 1 << 20, seed=7, clip=150.0)
-    hits = []
-    for mesh_bvh in (1, 0):
+    hits = {}
+    for name, (persistent, mesh_bvh, trace_walker) in {"wide persistent": (1, 1, 0), "one ray per lane": (0, 1, 0),
+                                                       "reference trees": (0, 0, 0), "k_trace": (1, 1, 1)}.items():
         c = Context(0)
         try:
+            c.set_option(capi.OPT_PERSISTENT, persistent)
             c.set_option(capi.OPT_MESH_BVH, mesh_bvh)
+            c.set_option(capi.OPT_TRACE_WALKER, trace_walker)
             c.upload_scene(s)
-            hits.append(c.trace_rays(ro, rd))
+            hits[name] = c.trace_rays(ro, rd)
         finally:
             c.close()
-    assert hits[0].tobytes() == hits[1].tobytes()
-    assert (hits[0]["tri_index"] >= 0).sum() > 10000
+    base = hits["wide persistent"]
+    for name, h in hits.items():
+        assert h.tobytes() == base.tobytes(), name
+    assert (base["tri_index"] >= 0).sum() > 10000
     n = 20000
     ref = o.trace(ro[:n], rd[:n])
-    assert len(compare_hits(hits[0][:n], ref)) == 0
-    assert np.array_equal(hits[0]["dist"][:n], ref["dist"])            # distances bit-exact, not just 1e-5
+    assert len(compare_hits(base[:n], ref)) == 0
+    assert np.array_equal(base["dist"][:n], ref["dist"])               # distances bit-exact, not just 1e-5
+    assert np.array_equal(base["pl"][:n].view(np.uint32), ref["pl"].view(np.uint32))
+
+
+def test_config3_full_size_band_parity(million):
+    """BASELINE config 3 at its full resolution: a 4-row band of the 1920x1080 frame of the 16 x 65 536-triangle
+    scene against the oracle (as for configs 2 and 5): pixel / seed / camera-ray indexing and the default
+    (four-children persistent) walker on the real workload."""
+    s, o = million
+    c = Context(0)
+    try:
+        c.set_option(capi.OPT_FAST_MATH, 1)                             # what bench.py measures
+        iv, ipv = _setup(c, s, W, H, 8, 1.5)
+        _band_parity(c, o, W, H, iv, ipv, 8, 1.5, rows=4, spp=2, frac=0.975)
+    finally:
+        c.close()
 
 
 def test_config3_config4_full_size_render_walkers_agree(million):

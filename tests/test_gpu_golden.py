@@ -41,26 +41,53 @@ def _image_ok(img, ref_sum, spp, frac=0.985):
 
 # Scene 8 (colonnes) is a hall of 891 columns on a near-mirror floor (roughness 0.9999): a last-ulp
 # difference in sin/cos is amplified over 9 bounces, so more 16-spp pixels contain one diverged path.
+# Measured, not assumed: the CPU oracle against itself with the sampler's transcendentals moved by ONE ulp loses
+# 3-5 % of scene 8's pixels at 9 bounces and none on the other scenes (tests/test_oracle_golden.py::
+# test_scene8_waiver_is_the_noise_floor_of_the_transcendentals); test_scene8_disagreement_grows_with_the_bounce_count
+# below shows the GPU agreeing on >= 99.9 % of the pixels at 1-2 bounces with the same hit records everywhere.
 PIXEL_FRACTION = {8: 0.90}
 
 
-@pytest.mark.parametrize("sid", range(1, 9))
-@pytest.mark.parametrize("flat", [1, 0])
-def test_traversal_vs_reference_fixture(ctx, sid, flat):
-    g = np.load(GOLD / f"scene{sid}.npz")
+# Every walker the library can select goes through the SAME kernel a render launches (k_traverse; the ray batch
+# rides through ray / hit sectors, mcpt_trace_rays with MCPT_OPT_TRACE_WALKER = 0): the warp-coherent flat list
+# (scenes of <= 16 primitives), persistent warps over the SAH-built top2 tree (the default of scenes 3, 5, 7, 8 --
+# the kernel bench.py times there), persistent warps over the reference's topology, the stack-free heap walk, and
+# the reference-order walk of k_trace. Options in the order (flat, persistent, top_sah, trace_walker).
+WALKERS = {
+    "default": (1, 1, 1, 0),
+    "persistent-sah": (0, 1, 1, 0),
+    "persistent-ref-topology": (0, 1, 0, 0),
+    "heap-walk": (0, 0, 1, 0),
+    "k_trace": (1, 1, 1, 1),
+}
+
+
+def _set_walker(ctx, walker):
+    flat, persistent, top_sah, trace_walker = WALKERS[walker]
     ctx.set_option(capi.OPT_FLAT_WALK, flat)
+    ctx.set_option(capi.OPT_PERSISTENT, persistent)
+    ctx.set_option(capi.OPT_TOP_SAH, top_sah)
+    ctx.set_option(capi.OPT_TRACE_WALKER, trace_walker)
+
+
+@pytest.mark.parametrize("sid", range(1, 9))
+@pytest.mark.parametrize("walker", list(WALKERS))
+def test_traversal_vs_reference_fixture(ctx, sid, walker):
+    g = np.load(GOLD / f"scene{sid}.npz")
+    _set_walker(ctx, walker)
     try:
         _upload(ctx, g)
+        got = ctx.trace_rays(g["ray_o"], g["ray_d"])
+        any_hit = ctx.trace_rays(g["ray_o"], g["ray_d"], any_hit=True)
     finally:
-        ctx.set_option(capi.OPT_FLAT_WALK, 1)
-    got = ctx.trace_rays(g["ray_o"], g["ray_d"])
+        _set_walker(ctx, "default")
     ref = g["hits"]
     for f in ("index", "tri_index", "shape", "dir"):
         assert np.array_equal(got[f], ref[f]), f
     hit = ref["index"] >= 0
     assert np.all(np.abs(got["dist"][hit] - ref["dist"][hit]) <= 1e-5 * ref["dist"][hit])   # the stated bar
     assert got.tobytes() == ref.tobytes()                                                    # what the library delivers
-    assert np.array_equal(ctx.trace_rays(g["ray_o"], g["ray_d"], any_hit=True)["index"] >= 0, g["any_hit"])
+    assert np.array_equal(any_hit["index"] >= 0, g["any_hit"])
 
 
 @pytest.mark.parametrize("sid", range(1, 9))
@@ -90,10 +117,71 @@ def test_image_vs_reference_fixture(ctx, sid):
         _image_ok(ctx.resolve(8), g["image_ior2"], 8)
 
 
-def test_mesh_scene_vs_reference_fixture(ctx):
+def test_scene8_disagreement_grows_with_the_bounce_count(ctx):
+    """The scene-8 waiver (PIXEL_FRACTION) backed by a measurement: against the oracle at the fixture's size and
+    seeds, the first bounces agree on (nearly) every pixel -- same hit records (the traversal tests), same shading --
+    and the share of 16-spp pixels holding a diverged path grows with the bounce count, as chaotic amplification of
+    last-ulp differences in the sampler's sin / cos / log / pow does."""
+    from common import both
+    s, o = both(8)                                   # light 0.4, as the fixture (tests/golden/make_golden.py)
+    g = np.load(GOLD / "scene8.npz")
+    w, h, spp, _ = (int(v) for v in g["size"])
+    ctx.upload_scene(o.scene_desc())
+    ctx.resize(w, h)
+    ctx.set_camera(g["inv_v"], g["inv_pv"])
+    frac = {}
+    for nb in (1, 2, 4, 9):
+        o.set_uniforms(nb, float(g["ior"]), DATE, 0, g["inv_v"], g["inv_pv"])
+        ref = o.render(w, h, 0, spp) / np.float32(spp)
+        ctx.set_params(nb_bounces=nb, refract_ind=float(g["ior"]), date=float(DATE))
+        ctx.clear()
+        ctx.render(0, spp)
+        frac[nb] = float(np.isclose(ctx.resolve(spp), ref, rtol=2e-3, atol=2e-3).all(axis=2).mean())
+    print("scene 8, share of pixels within 2e-3 of the oracle by bounce count:", frac)
+    assert frac[1] >= 0.999 and frac[2] >= 0.995
+    assert frac[9] >= PIXEL_FRACTION[8]
+    assert frac[9] <= frac[2]
+
+
+def _mesh_fixture():
     g = np.load(GOLD / "mesh.npz")
     meshes = [{"bvh": {"depth": g[f"m{m}_depth"], "bb": g[f"m{m}_bb"], "ind": g[f"m{m}_ind"]}, "tri": g[f"m{m}_tri"],
                "pos": g[f"m{m}_pos"], "nrm": g[f"m{m}_nrm"], "mesh_line": g[f"m{m}_line"]} for m in range(2)]
+    return g, meshes
+
+
+# (persistent, mesh_bvh, top_sah, trace_walker): four-children persistent walk over the GPU-built trees (default,
+# what bench.py times on configs 3 / 4), the same over the reference's top-level topology, one ray per lane over
+# the GPU-built two-children trees, the same over the uploaded median-split trees, and k_trace.
+MESH_WALKERS = {
+    "default-wide-persistent": (1, 1, 1, 0),
+    "wide-persistent-ref-topology": (1, 1, 0, 0),
+    "one-ray-per-lane-lbvh": (0, 1, 1, 0),
+    "one-ray-per-lane-reference-trees": (0, 0, 1, 0),
+    "k_trace": (1, 1, 1, 1),
+    "k_trace-reference-trees": (1, 0, 1, 1),
+}
+
+
+@pytest.mark.parametrize("walker", list(MESH_WALKERS))
+def test_mesh_traversal_vs_reference_fixture(ctx, walker):
+    g, meshes = _mesh_fixture()
+    persistent, mesh_bvh, top_sah, trace_walker = MESH_WALKERS[walker]
+    opts = ((capi.OPT_PERSISTENT, persistent, 1), (capi.OPT_MESH_BVH, mesh_bvh, 1), (capi.OPT_TOP_SAH, top_sah, 1),
+            (capi.OPT_TRACE_WALKER, trace_walker, 0))
+    for o, v, _ in opts:
+        ctx.set_option(o, v)
+    try:
+        _upload(ctx, g, meshes)
+        got = ctx.trace_rays(g["ray_o"], g["ray_d"])
+    finally:
+        for o, _, dflt in opts:
+            ctx.set_option(o, dflt)
+    assert got.tobytes() == g["hits"].tobytes()
+
+
+def test_mesh_scene_vs_reference_fixture(ctx):
+    g, meshes = _mesh_fixture()
     _upload(ctx, g, meshes)
     got = ctx.trace_rays(g["ray_o"], g["ray_d"])
     assert got.tobytes() == g["hits"].tobytes()

@@ -151,3 +151,32 @@ def test_live_reference_build_agrees_with_the_restatement(sid, bounces, ior):
     for x in (r, o):
         x.set_uniforms(bounces, ior, np.float32(0.031), 0, iv, ipv)
     assert np.array_equal(r.render(80, 50, 3, 5), o.render(80, 50, 3, 5), equal_nan=True)
+
+
+def test_scene8_waiver_is_the_noise_floor_of_the_transcendentals():
+    """tests/test_gpu_golden.py lets 10 % of scene 8's 16-spp pixels differ from the reference fixture and 1.5 % on
+    the other scenes. Evidence that this is amplification of last-ulp differences in sin / cos / log / pow (which
+    GLSL, glibc and CUDA are all free to round differently), not a defect: the oracle against ITSELF with every
+    transcendental result of the bounce sampler moved by ONE ulp. Scenes 1 and 6: no 16-spp pixel moves by more than
+    the 2e-3 tolerance. Scene 8 (hall of columns on a near-mirror floor): identical up to 2 bounces, and at the
+    fixture's 9 bounces 3-5 % of the pixels move -- from one ulp; CUDA's libm differs from glibc by up to 2 ulps
+    and the MUFU sampler by more."""
+    from common import both
+    w, h, spp = 64, 48, 16
+    drift = {}
+    for sid in (1, 6, 8):
+        s, o = both(sid)
+        iv, ipv = capi.default_camera(w, h)
+        for nb in (2, 9):
+            o.set_uniforms(nb, 1.0, DATE, 0, iv, ipv)
+            a = o.render(w, h, 0, spp) / spp
+            try:
+                o.set_ulp_perturb(1)
+                b = o.render(w, h, 0, spp) / spp
+            finally:
+                o.set_ulp_perturb(0)
+            drift[sid, nb] = 1.0 - np.isclose(a, b, rtol=2e-3, atol=2e-3).all(axis=2).mean()
+    print({k: round(float(v), 4) for k, v in drift.items()})
+    assert drift[1, 9] <= 0.002 and drift[6, 9] <= 0.002
+    assert drift[8, 2] <= 0.002
+    assert 0.01 <= drift[8, 9] <= 0.10
