@@ -223,6 +223,25 @@ __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, 
 // want it -- no gain; one queue region per warp instead of per CTA -- no atomics at all and ordered
 // survivors, but warps of a CTA finish at different times, -4 % at C2.)
 
+#ifndef MCPT_POPS_PER_ITER
+#define MCPT_POPS_PER_ITER 2  // measured on the mesh workload: 1 -> 704, 2 -> 752, 3 -> 744, unbounded -> 731 Msamples/s
+#endif
+// MCPT_FLOW (default 1): one iteration of a persistent warp is a pipeline of the step kinds in the order a ray
+// usually needs them -- take an entry off the stack, enter a primitive, a run of node steps, a triangle -- and a
+// lane FLOWS through it: the kind of step it needs is re-read before every stage, so "pop, node, node, triangle"
+// of one ray costs one iteration, not three. Every stage is executed once per iteration anyway (some lane of the
+// warp needs it); chaining halves the iterations per ray and fills each stage with more lanes. Measured on the
+// 1 M-triangle workload: 1106 -> 1261 Msamples/s (traverse 22.6 -> 19.7 ms, interior 5.2 -> 4.6 ms per step).
+// 0: one kind of step per lane per iteration (round 1).
+#ifndef MCPT_FLOW
+#define MCPT_FLOW 1
+#endif
+// MCPT_BATCH_DELIVER (with MCPT_FLOW): a finished ray keeps its lane until the refill threshold is reached and
+// all finished records are delivered together right before the refill.
+#ifndef MCPT_BATCH_DELIVER
+#define MCPT_BATCH_DELIVER 0
+#endif
+
 template <bool COUNT, bool MESHES, bool EXIT>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
                                                     uint32_t len, const HitSink& sink, uint32_t* s_next, uint32_t* s_hits,
@@ -237,7 +256,38 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
     const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
     bool has_ray = false, exhausted = false;
     uint32_t p = 0;
+#ifndef MCPT_NODE_STEPS
+#define MCPT_NODE_STEPS (WIDE ? 2 : (MESHES ? 4 : 6))  // (four-children nodes: 1 -> 930, 2 -> 1003, 3 -> 996 Msamples/s; SAH-built trees of analytic primitives, divergence-stress scene: 2 -> 3222, 4 -> 3398, 6 -> 3504 Msamples/s.) Two-children node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 946, 6 -> 930, 8 -> 900 Msamples/s
+#endif
     while (true) {
+#if MCPT_FLOW && MCPT_BATCH_DELIVER
+        const uint32_t fin = __ballot_sync(0xffffffffu, has_ray && w.done);
+        const uint32_t freeable = fin | __ballot_sync(0xffffffffu, !has_ray);
+        if (freeable) {
+            const bool all = freeable == 0xffffffffu;
+            if (all || __popc(freeable) >= S.refill_lanes) {
+                if (fin) {
+                    const bool mine = has_ray && w.done;
+                    deliver<EXIT>(S, wf, sink, s_hits, p, mine, w.best, w.D);
+                    if (mine) has_ray = false;
+                }
+                if (!exhausted) {
+                    uint32_t first = 0;
+                    if (lane == 0) first = atomicAdd(s_next, uint32_t(__popc(freeable)));
+                    first = __shfl_sync(0xffffffffu, first, 0);
+                    if (!has_ray && queue_item(qin, first + __popc(freeable & below), len, p)) {
+                        float4 o4, d4;
+                        wf.load_ray(p, o4, d4);
+                        walk_begin<WIDE>(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+                        has_ray = true;
+                    }
+                    exhausted = first + __popc(freeable) >= len;
+                } else if (all) {
+                    break;
+                }
+            }
+        }
+#else
         const uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
         if (idle) {
             if (!exhausted && (idle == 0xffffffffu || __popc(idle) >= S.refill_lanes)) {
@@ -255,21 +305,35 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
                 break;
             }
         }
-#ifndef MCPT_POPS_PER_ITER
-#define MCPT_POPS_PER_ITER 2  // measured on the mesh workload: 1 -> 704, 2 -> 752, 3 -> 744, unbounded -> 731 Msamples/s
 #endif
 #pragma unroll 1
         for (int r = 0; r < MCPT_POPS_PER_ITER && has_ray && w.cur == kTokPop && !w.done; ++r)
             walk_pop_one<WIDE>(w, S, st, wsave);
+#if MCPT_FLOW
+        if (has_ray && walk_kind(w) == WALK_PRIM) walk_prim<COUNT, MESHES, WIDE>(w, wk, S, sm, st, wsave);
+        if (has_ray && walk_kind(w) == WALK_NODE) {
+            walk_node<COUNT, WIDE>(w, wk, S, st, wsave);
+#pragma unroll
+            for (int r = 1; r < MCPT_NODE_STEPS; ++r)
+                if (w.cur >= 0) walk_node<COUNT, WIDE>(w, wk, S, st, wsave);
+        }
+        if (MESHES && has_ray && walk_kind(w) == WALK_TRI) walk_tri<COUNT>(w, wk, S, sm, st, wsave);
+#if !MCPT_BATCH_DELIVER
+        {  // finished rays: deliver and free the lane
+            const bool fin = has_ray && w.done;
+            if (__any_sync(0xffffffffu, fin)) {
+                deliver<EXIT>(S, wf, sink, s_hits, p, fin, w.best, w.D);
+                if (fin) has_ray = false;
+            }
+        }
+#endif
+#else
         const int kind = has_ray ? walk_kind(w) : -1;  // WALK_POP: a dead entry was dropped, pop again next time
         // finished rays: deliver and free the lane
         if (__any_sync(0xffffffffu, kind == WALK_DONE)) {
             deliver<EXIT>(S, wf, sink, s_hits, p, kind == WALK_DONE, w.best, w.D);
             if (kind == WALK_DONE) has_ray = false;
         }
-#ifndef MCPT_NODE_STEPS
-#define MCPT_NODE_STEPS (WIDE ? 2 : (MESHES ? 4 : 6))  // (four-children nodes: 1 -> 930, 2 -> 1003, 3 -> 996 Msamples/s; SAH-built trees of analytic primitives, divergence-stress scene: 2 -> 3222, 4 -> 3398, 6 -> 3504 Msamples/s.) Two-children node steps per iteration of a persistent warp; measured on the mesh workload: 1 -> 762, 2 -> 901, 3 -> 934, 4 -> 946, 6 -> 930, 8 -> 900 Msamples/s
-#endif
         if (kind == WALK_NODE) {
             // a run of node steps: the lanes at a triangle or a primitive wait, but the dispatch, the
             // ballots and the rarer step kinds are paid once per run (popping inside the run as well
@@ -282,6 +346,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
             walk_tri<COUNT>(w, wk, S, sm, st, wsave);
         else if (kind == WALK_PRIM)
             walk_prim<COUNT, MESHES, WIDE>(w, wk, S, sm, st, wsave);
+#endif
     }
 }
 
