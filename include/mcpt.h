@@ -199,6 +199,20 @@ int mcpt_trace_rays(mcpt_ctx* ctx, int64_t n, const float* o, const float* d,
 int mcpt_trace_rays_device(mcpt_ctx* ctx, int64_t n, const float* o4, const float* d4,
                            mcpt_hit* out_dev, int any_hit);
 
+/* The same closest-hit search as mcpt_trace_rays_device for callers that cannot allocate device memory (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
+ * The ray / hit sectors the traversal kernel works in live in a fixed block
+ * inside the library image (a file-scope __device__ array of MCPT_TRACE_STATIC_MAX_RAYS x 64 bytes = 4 MiB, held by
+ * every GPU that loads the library until the process exits); the call performs no cudaMalloc / cudaFree and calls no
+ * allocating library routine. Inputs and outputs are the caller's device buffers (float4 o[n], float4 d[n],
+ * mcpt_hit out[n]); asynchronous on the context's stream; records are bit-identical to mcpt_trace_rays_device.
+ * n > MCPT_TRACE_STATIC_MAX_RAYS is rejected with MCPT_E_INVALID (split the batch). All calls on one device share
+ * the block, which keeps the previous call's contents (nothing in it needs clearing: every slot a call reads, it
+ * has written first); calls that OVERLAP on the GPU -- other streams, other contexts of the same device -- race on
+ * it and must be serialised by the caller. */
+#define MCPT_TRACE_STATIC_MAX_RAYS 65536
+int mcpt_trace_rays_static(mcpt_ctx* ctx, int64_t n, const float* o4, const float* d4, mcpt_hit* out_dev);
+
 /* Host-only inspection of the top-level tree the persistent warps would walk for `desc` (built exactly as
  * mcpt_upload_scene builds it; no context and no CUDA device needed): sizes, depths, and the invariants the
  * traversal relies on. top_sah as MCPT_OPT_TOP_SAH. Used by the CPU tests. */

@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <functional>
+#include <mutex>
 #include <new>
 #include <string>
 #include <unordered_map>
@@ -334,3 +335,4 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
 
 #include "api_render.inl"
 #include "api_scene.inl"
+#include "api_static.inl"

@@ -246,6 +246,10 @@ class Context:
     def trace_rays_device(self, n, o4_ptr, d4_ptr, out_ptr, any_hit=False):
         self._ck(self._L.mcpt_trace_rays_device(self._c, n, C.c_void_p(o4_ptr), C.c_void_p(d4_ptr), C.c_void_p(out_ptr), int(any_hit)))
 
+    def trace_rays_static(self, n, o4_ptr, d4_ptr, out_ptr):
+        """mcpt_trace_rays_static: device buffers in and out, fixed scratch inside the library, no allocation."""
+        self._ck(self._L.mcpt_trace_rays_static(self._c, n, C.c_void_p(o4_ptr), C.c_void_p(d4_ptr), C.c_void_p(out_ptr)))
+
     def stats(self) -> dict:
         s = Stats()
         self._ck(self._L.mcpt_get_stats(self._c, C.byref(s)))
