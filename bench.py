@@ -192,6 +192,7 @@ def main():
     ap.add_argument("--mesh-bvh", type=int, default=1, help="1 = GPU-built LBVH per mesh, 0 = the uploaded median-split trees")
     ap.add_argument("--top-sah", type=int, default=1, help="1 = SAH-built top-level tree for the persistent walk, 0 = the reference's median-split topology")
     ap.add_argument("--flat-walk", type=int, default=1, help="1 = warp-coherent flat walk for scenes of <= 16 primitives, 0 = tree walk (persistent warps)")
+    ap.add_argument("--unified", type=int, default=1, help="scenes with meshes: 1 = one world-space tree over the top level and every mesh instance, 0 = two-level walk")
     ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -227,6 +228,7 @@ def main():
     ctx.set_option(capi.OPT_TOP_SAH, args.top_sah)
     ctx.set_option(capi.OPT_FLAT_WALK, args.flat_walk)
     ctx.set_option(capi.OPT_MESH_BVH, args.mesh_bvh)
+    ctx.set_option(capi.OPT_UNIFIED, args.unified)
     ctx.set_option(capi.OPT_PERSISTENT, args.persistent)
     ctx.set_option(capi.OPT_REFILL_LANES, args.refill)
     ctx.upload_scene(s)

@@ -88,7 +88,8 @@ enum {
     MCPT_OPT_FLAT_WALK = 6,        /* 1 = warp-coherent flat walk for scenes of <= 16 primitives (default 1);
                                       set before mcpt_upload_scene */
     MCPT_OPT_TRAVERSE_OCC = 7,     /* resident 256-thread CTAs per SM the traversal kernel is register-capped
-                                      for: 2 (<=128 regs), 3 (<=80), 4 (<=64); 0 = auto (default) */
+                                      for: 2 (<=128 regs), 3 (<=80), 4 (<=64), unified walk also 5 (<=48), 6 (<=40);
+                                      0 = auto (default) */
     MCPT_OPT_PERSISTENT = 8,       /* 1 = scenes walked through the tree (> 16 primitives, or meshes) are traced by
                                       persistent warps whose idle lanes fetch new rays (default), 0 = one ray per
                                       lane per tile. Set before mcpt_upload_scene. Same results. */
@@ -97,10 +98,16 @@ enum {
     MCPT_OPT_TOP_SAH = 10,         /* 1 = the persistent warps walk a top-level tree built at upload by a full-sweep
                                       SAH over the primitives' leaf boxes (default), 0 = the topology of the uploaded
                                       median-split tree. Set before mcpt_upload_scene. Same results. */
-    MCPT_OPT_TRACE_WALKER = 11     /* mcpt_trace_rays (closest hit): 0 = through the production traversal kernel of
+    MCPT_OPT_TRACE_WALKER = 11,    /* mcpt_trace_rays (closest hit): 0 = through the production traversal kernel of
                                       mcpt_render with whatever walker the scene selected (default), 1 = the
                                       one-ray-per-lane walk over the uploaded trees in the reference's visit order.
                                       any_hit always takes the latter. Same records. */
+    MCPT_OPT_UNIFIED = 12          /* scenes with meshes: 1 = one world-space tree over the top level and every mesh
+                                      instance, built on the GPU at upload, walked in a single frame (default; needs
+                                      MCPT_OPT_MESH_BVH and MCPT_OPT_PERSISTENT), 0 = two-level walk (top-level tree,
+                                      then the mesh's own tree in mesh space). Set before mcpt_upload_scene. Same
+                                      records. With 1, mcpt_mesh_desc.bvh may be empty (bb == ind == NULL): no host
+                                      tree is needed, triangles of equal distance are then ranked by index. */
 };
 
 /* wavefront stages, in launch order inside one bounce */

@@ -83,6 +83,7 @@ struct mcpt_ctx {
     int opt_traverse_occ = 0;  // 0 = auto
     int opt_count_work = 0;
     int opt_trace_walker = 0;  // mcpt_trace_rays: 0 = the production kernel (k_traverse), 1 = the reference-order walk (k_trace)
+    int opt_unified = 1;       // scenes with meshes: one world-space tree (traverse.cuh, UWalk) instead of the two-level walk
 
     // stage profiling: (stage, start, stop) triples waiting to be read, plus a free list
     struct Span {
@@ -322,9 +323,10 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
         case MCPT_OPT_FLAT_WALK: c->opt_flat_walk = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TOP_SAH: c->opt_top_sah = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TRACE_WALKER: c->opt_trace_walker = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_UNIFIED: c->opt_unified = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TRAVERSE_OCC:
-            if (value != 0 && (value < 2 || value > 4))
-                return fail(c, MCPT_E_INVALID, "traverse occupancy must be 0 (auto), 2, 3 or 4 CTAs per SM");
+            if (value != 0 && (value < 2 || value > 6))
+                return fail(c, MCPT_E_INVALID, "traverse occupancy must be 0 (auto) or 2..6 CTAs per SM");
             c->opt_traverse_occ = value;
             return MCPT_OK;
     }

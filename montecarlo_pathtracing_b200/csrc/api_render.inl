@@ -344,7 +344,11 @@ int mcpt_trace_rays_device(mcpt_ctx* c, int64_t n, const float* o4, const float*
     if (n == 0) return MCPT_OK;
     CK(c, cudaSetDevice(c->device));
     const float4 *o = reinterpret_cast<const float4*>(o4), *d = reinterpret_cast<const float4*>(d4);
-    if (any_hit || c->opt_trace_walker != 0) {
+    // The one-ray-per-lane walk in the reference's visit order needs the per-mesh trees; a scene uploaded as ONE
+    // world-space tree (MCPT_OPT_UNIFIED) has none, and every batch goes through the production kernel: any_hit then
+    // reports the closest hit, which exists exactly when just_hit_bvh would find one.
+    const bool unified = c->scene.u_nodes != nullptr;
+    if ((any_hit || c->opt_trace_walker != 0) && !unified) {
         launch_trace(lcfg(c), c->scene, n, o, d, out_dev, any_hit != 0);
         CK(c, cudaGetLastError());
         return MCPT_OK;

@@ -313,10 +313,15 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     for (int m = 0; m < d->n_meshes; ++m) {
         const mcpt_mesh_desc& md = d->meshes[m];
         if (!md.tri_idx || !md.pos || !md.nrm) return fail(c, MCPT_E_INVALID, "mesh %d: null arrays", m);
-        rc = validate_bvh(c, md.bvh, int(md.n_tris), "mesh");
-        if (rc) return rc;
-        for (uint64_t i = 0; i < 3ull * md.n_tris; ++i)
-            if (md.tri_idx[i] >= md.n_verts) return fail(c, MCPT_E_INVALID, "mesh %d: vertex index out of range", m);
+        const bool no_tree = !md.bvh.bb && !md.bvh.ind;
+        if (no_tree && !c->opt_mesh_bvh) return fail(c, MCPT_E_INVALID, "mesh %d: no BVH uploaded; that needs MCPT_OPT_MESH_BVH = 1", m);
+        if (!no_tree) {
+            // depth and pointers here; the leaf slots and the vertex indices are range-checked on the device below
+            if (!md.bvh.bb || !md.bvh.ind) return fail(c, MCPT_E_INVALID, "mesh %d: null BVH arrays", m);
+            if (md.bvh.depth < 1 || md.bvh.depth > 29) return fail(c, MCPT_E_INVALID, "mesh %d: BVH depth %d out of range [1,29]", m, md.bvh.depth);
+            if (!c->opt_mesh_bvh && (rc = validate_bvh(c, md.bvh, int(md.n_tris), "mesh"))) return rc;
+        }
+        if (md.n_tris > 0x7fffff00u / 3u) return fail(c, MCPT_E_INVALID, "mesh %d: too many triangles", m);
     }
 
     CK(c, cudaStreamSynchronize(c->stream));
@@ -386,7 +391,9 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
         for (uint32_t k = t_nodes - 1; k >= t_first_leaf; --k)  // the reference's visit order: high slots first
             if (d->root.ind[k - t_first_leaf] >= 0) flat.push_back(top[k]);
 
-    // ---- meshes
+    // ---- meshes. Nothing here loops over a mesh on the host: the arrays go to the device as they are, the vertex
+    // indices and the reference tree's leaf slots are range-checked there (flag read back once at the end), the
+    // tie-break ranks are scattered from the leaf slots there, and the tree builds reduce their own vertex boxes.
     std::vector<DevMesh> meshes(d->n_meshes);
     std::vector<void*> build_allocs;  // scratch of the GPU tree builds, parked again at the end
     struct ParkOnExit {               // ... also on the error returns below
@@ -400,16 +407,27 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     } park_build_allocs{c, build_allocs};
     char* build_ws = nullptr;
     size_t build_ws_bytes = 0;
+    int* d_flag = nullptr;
+    if (d->n_meshes > 0) {
+        if ((rc = dev_alloc(c, build_allocs, &d_flag, 1))) return rc;
+        CK(c, cudaMemsetAsync(d_flag, 0, sizeof(int), c->stream));
+    }
     if (c->opt_mesh_bvh) {
         for (int m = 0; m < d->n_meshes; ++m) {
             const int nt = int(d->meshes[m].n_tris);
-            if (nt > 0) build_ws_bytes = std::max(build_ws_bytes, lbvh_workspace_bytes(nt, (nt + kMeshLeafTris - 1) / kMeshLeafTris));
+            if (nt > 0)
+                build_ws_bytes = std::max(build_ws_bytes, lbvh_workspace_bytes(nt, (nt + kMeshLeafTris - 1) / kMeshLeafTris, int(d->meshes[m].n_verts)));
         }
         if (build_ws_bytes && (rc = dev_alloc(c, build_allocs, &build_ws, build_ws_bytes))) return rc;
     }
+    // one world-space tree over the top level and every mesh instance (traverse.cuh, UWalk)?
+    const bool unified = c->opt_unified && c->opt_mesh_bvh && c->opt_persistent && !c->opt_trace_walker && d->n_meshes > 0 &&
+                         kMeshLeafTris == 1 && flat.empty();
+    std::vector<int32_t*> d_slots(d->n_meshes, nullptr);  // per mesh: the reference's leaf slot of every triangle (or null)
     for (int m = 0; m < d->n_meshes; ++m) {
         const mcpt_mesh_desc& md = d->meshes[m];
-        const int depth = md.bvh.depth;
+        const bool no_tree = !md.bvh.bb && !md.bvh.ind;
+        const int depth = no_tree ? 0 : md.bvh.depth;
         const uint32_t first_leaf = 1u << depth;
         DevMesh& M = meshes[m];
         std::memset(&M, 0, sizeof M);
@@ -419,42 +437,50 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
         if ((rc = upload_raw(c, md.tri_idx, 3 * size_t(md.n_tris), &di)) || (rc = upload_raw(c, md.pos, 3 * size_t(md.n_verts), &dp)) ||
             (rc = upload_raw(c, md.nrm, 3 * size_t(md.n_verts), &dnr)))
             return rc;
+        check_indices(c->stream, di, 3 * size_t(md.n_tris), md.n_verts, d_flag);
+        c->launches += md.n_tris ? 1 : 0;
         M.idx = di;
         M.pos = dp;
         M.nrm = dnr;
         M.depth = depth;
         M.n_tris = int(md.n_tris);
         if (c->opt_mesh_bvh && md.n_tris > 0) {
-            // rebuild the tree on the GPU (bvh_build.cu); the reference tree only supplies each
-            // triangle's leaf slot, which ranks equal-distance candidates like its own visit order
-            std::vector<int32_t> slot_of_tri(md.n_tris, -1);
-            for (uint32_t s = 0; s < first_leaf; ++s)
-                if (md.bvh.ind[s] >= 0) slot_of_tri[md.bvh.ind[s]] = int32_t(s);
-            float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-            for (size_t v = 0; v < size_t(md.n_verts); ++v)
-                for (int k = 0; k < 3; ++k) {
-                    lo[k] = std::min(lo[k], md.pos[3 * v + k]);
-                    hi[k] = std::max(hi[k], md.pos[3 * v + k]);
-                }
+            // the tree is rebuilt on the GPU (bvh_build.cu); an uploaded reference tree only supplies each triangle's
+            // leaf slot, which ranks equal-distance candidates like the reference's own visit order
+            if (!no_tree) {
+                int32_t* d_ind = nullptr;
+                if ((rc = upload_raw(c, md.bvh.ind, size_t(first_leaf), &d_ind)) || (rc = dev_alloc(c, build_allocs, &d_slots[m], size_t(md.n_tris))))
+                    return rc;
+                c->scene_allocs.pop_back();  // d_ind is scratch of this upload, not part of the scene
+                build_allocs.push_back(d_ind);
+                CK(c, slots_from_leaves(c->stream, d_ind, int(first_leaf), int(md.n_tris), d_slots[m], d_flag));
+                c->launches += 1;
+            }
+            if (unified) continue;  // the instances' subtrees are built below
             const int n_leaves = int((md.n_tris + kMeshLeafTris - 1) / kMeshLeafTris);
-            int32_t* d_slot = nullptr;
             DevNode2* dn2 = nullptr;
             DevNode4* dn4 = nullptr;
             DevTri* dt2 = nullptr;
-            if ((rc = dev_alloc(c, build_allocs, &d_slot, slot_of_tri.size())) ||
-                (rc = dev_alloc(c, c->scene_allocs, &dn2, size_t(std::max(n_leaves - 1, 1)))) ||
+            if ((rc = dev_alloc(c, c->scene_allocs, &dn2, size_t(std::max(n_leaves - 1, 1)))) ||
                 (rc = dev_alloc(c, c->scene_allocs, &dn4, size_t(std::max(n_leaves - 1, 1)))) ||
                 (rc = dev_alloc(c, c->scene_allocs, &dt2, size_t(n_leaves) * kMeshLeafTris)))
                 return rc;
-            CK(c, cudaMemcpyAsync(d_slot, slot_of_tri.data(), slot_of_tri.size() * sizeof(int32_t), cudaMemcpyHostToDevice, c->stream));
-            CK(c, cudaStreamSynchronize(c->stream));  // slot_of_tri is a temporary of this iteration
             unsigned long long launched = 0;
             cudaError_t e;
             {
                 // enqueued only: the builds of all meshes share one workspace in stream order
                 StageSpan sp(c, MCPT_STAGE_BVH_BUILD);
-                e = build_mesh_lbvh(c->stream, dp, di, int(md.n_tris), d_slot, lo, hi, dn2, dn4, dt2, n_leaves, build_ws, build_ws_bytes,
-                                    &launched);
+                LbvhBuild b;
+                b.d_pos = dp;
+                b.d_idx = di;
+                b.n_tris = int(md.n_tris);
+                b.n_verts = int(md.n_verts);
+                b.d_slot_of_tri = d_slots[m];
+                b.d_nodes = dn2;
+                b.d_nodes4 = dn4;
+                b.d_tris = dt2;
+                b.n_leaves = n_leaves;
+                e = build_mesh_lbvh(c->stream, b, build_ws, build_ws_bytes, &launched);
             }
             c->launches += launched;
             CK(c, e);
@@ -464,6 +490,7 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
             M.n_leaves2 = n_leaves;
             continue;
         }
+        if (md.n_tris == 0 && no_tree) continue;
         std::vector<DevNode> nodes(first_leaf, empty_node());  // interior nodes 1 .. first_leaf-1
         for (uint32_t k = 1; k < first_leaf; ++k) nodes[k] = pack_node(md.bvh.bb[k - 1], -1);
         std::vector<DevTri> tris(first_leaf);
@@ -473,6 +500,8 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
             T.a = T.b = T.c = make_float4(0, 0, 0, 0);
             if (t >= 0) {
                 const uint32_t* ix = md.tri_idx + 3 * size_t(t);
+                for (int q = 0; q < 3; ++q)
+                    if (ix[q] >= md.n_verts) return fail(c, MCPT_E_INVALID, "mesh %d: vertex index out of range", m);
                 const float *A = md.pos + 3 * size_t(ix[0]), *B = md.pos + 3 * size_t(ix[1]), *C = md.pos + 3 * size_t(ix[2]);
                 T.a = make_float4(A[0], A[1], A[2], 0);
                 T.b = make_float4(B[0], B[1], B[2], 0);
@@ -487,21 +516,119 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
         M.tris = dt;
     }
 
+    // ---- the unified world-space tree: [top-level four-children nodes | subtree of instance 0 | instance 1 | ...]
+    DevNode4* d_unodes = nullptr;
+    DevTri* d_utris = nullptr;
+    int u_n_tris = 0;
+    float u_pad_rel = 0.0f, u_pad_abs = 0.0f, u_radius = 0.0f;
+    if (unified) {
+        struct Inst {
+            int prim, mesh, node_base, leaf_base;
+        };
+        std::vector<Inst> inst;
+        std::vector<int> inst_of_prim(d->n_prims, -1);
+        size_t n_nodes = top4.size(), n_tris_total = 0;
+        for (int i = 0; i < d->n_prims; ++i) {
+            if (prims[i].type != MCPT_PRIM_MESH || prims[i].slot < 0) continue;
+            const int nt = meshes[prims[i].mesh].n_tris;
+            if (nt <= 0) continue;
+            inst_of_prim[i] = int(inst.size());
+            inst.push_back(Inst{i, prims[i].mesh, int(n_nodes), int(n_tris_total)});
+            n_nodes += size_t(std::max(nt - 1, 1));
+            n_tris_total += size_t(nt);
+        }
+        if (n_nodes > 0x3fffffffu || n_tris_total + size_t(d->n_prims) > 0x3fffffffu)
+            return fail(c, MCPT_E_UNSUPPORTED, "unified tree too large (%zu nodes, %zu triangle slots): set MCPT_OPT_UNIFIED = 0", n_nodes, n_tris_total);
+        u_n_tris = int(n_tris_total);
+        // leaf tokens of the top-level tree: a mesh instance becomes a link to the root of its subtree, an analytic
+        // primitive moves behind the triangle slots
+        std::vector<DevNode4> utop = top4;
+        for (DevNode4& N : utop)
+            for (int j = 0; j < 4; ++j) {
+                int& tok = (&N.tok.x)[j];
+                if (tok >= 0 || tok == INT_MIN) continue;
+                const int prim = ~tok;
+                if (prims[prim].type == MCPT_PRIM_MESH)
+                    tok = inst_of_prim[prim] >= 0 ? inst[inst_of_prim[prim]].node_base : INT_MIN;
+                else
+                    tok = ~(u_n_tris + prim);
+            }
+        if ((rc = dev_alloc(c, c->scene_allocs, &d_unodes, n_nodes)) || (rc = dev_alloc(c, c->scene_allocs, &d_utris, std::max<size_t>(n_tris_total, 1))))
+            return rc;
+        if (!utop.empty()) CK(c, cudaMemcpyAsync(d_unodes, utop.data(), utop.size() * sizeof(DevNode4), cudaMemcpyHostToDevice, c->stream));
+        CK(c, cudaStreamSynchronize(c->stream));  // utop is a temporary
+        double pad_rel = 0.0, pad_abs = 0.0, radius = 0.0;
+        for (const Inst& in : inst) {
+            const DevMesh& M = meshes[in.mesh];
+            const DevPrim& P = prims[in.prim];
+            unsigned long long launched = 0;
+            cudaError_t e;
+            {
+                StageSpan sp(c, MCPT_STAGE_BVH_BUILD);
+                LbvhBuild b;
+                b.d_pos = M.pos;
+                b.d_idx = M.idx;
+                b.n_tris = M.n_tris;
+                b.n_verts = int(d->meshes[in.mesh].n_verts);
+                b.d_slot_of_tri = d_slots[in.mesh];
+                b.fwd = &P.fwd;
+                b.d_nodes4 = d_unodes + in.node_base;
+                b.d_tris = d_utris + in.leaf_base;
+                b.n_leaves = M.n_tris;
+                b.node_base = in.node_base;
+                b.leaf_base = in.leaf_base;
+                b.prim = in.prim;
+                e = build_mesh_lbvh(c->stream, b, build_ws, build_ws_bytes, &launched);
+            }
+            c->launches += launched;
+            CK(c, e);
+            // how far fwd * inv is from the identity (the uploaded inverse is a rounded one): linear part as the largest
+            // absolute row sum, translation part as the largest component
+            const float4 f[3] = {P.fwd.r0, P.fwd.r1, P.fwd.r2}, v[3] = {P.inv.r0, P.inv.r1, P.inv.r2};
+            for (int r = 0; r < 3; ++r) {
+                double row = 0.0;
+                const double fr[3] = {f[r].x, f[r].y, f[r].z};
+                for (int cc = 0; cc < 4; ++cc) {
+                    const double vc[3] = {cc == 0 ? v[0].x : cc == 1 ? v[0].y : cc == 2 ? v[0].z : v[0].w,
+                                          cc == 0 ? v[1].x : cc == 1 ? v[1].y : cc == 2 ? v[1].z : v[1].w,
+                                          cc == 0 ? v[2].x : cc == 1 ? v[2].y : cc == 2 ? v[2].z : v[2].w};
+                    double e_rc = fr[0] * vc[0] + fr[1] * vc[1] + fr[2] * vc[2] + (cc == 3 ? double(f[r].w) : 0.0) - (cc == r ? 1.0 : 0.0);
+                    if (cc < 3) row += std::fabs(e_rc);
+                    else pad_abs = std::max(pad_abs, std::fabs(e_rc));
+                }
+                pad_rel = std::max(pad_rel, row);
+            }
+            const DevNode& nb = top[t_first_leaf + uint32_t(P.slot)];  // the instance's world box (reference leaf box)
+            radius = std::max({radius, std::fabs(double(nb.lo.x)), std::fabs(double(nb.lo.y)), std::fabs(double(nb.lo.z)),
+                               std::fabs(double(nb.hi.x)), std::fabs(double(nb.hi.y)), std::fabs(double(nb.hi.z))});
+        }
+        if (!std::isfinite(pad_rel) || !std::isfinite(pad_abs)) pad_rel = pad_abs = 1.0;
+        // twice the bound, plus a few ulps of the quantities involved
+        u_pad_rel = float(4.0 * pad_rel + 1e-6);
+        u_pad_abs = float(2.0 * pad_abs + 1e-6 * radius);
+        u_radius = float(3.0 * radius);
+    }
+
     // ---- shared-memory staging plan (<= 40 KB so no opt-in is needed and
     // several CTAs stay resident per SM)
     S.smem_top_nodes = 0;
     S.smem_prims = 0;
     S.smem_mesh_nodes = 0;
+    // persistent warps need every mesh tree in the GPU-built form
+    // (measured: 1.8x on the 1 M-triangle workload, +20 % on a tree of 122 analytic primitives)
+    const bool persistent = c->opt_persistent && flat.empty() && (d->n_meshes == 0 || c->opt_mesh_bvh);
     if (c->opt_smem_staging) {
         uint32_t keep = t_nodes - 1;            // all top-level nodes ...
         while (keep > 511) keep >>= 1;          // ... or the top levels that fit 16 KB
-        S.smem_top_nodes = int(keep);
+        // the heap-order tree is what the one-ray-per-lane walk reads; persistent warps walk top2 / top4 / u_nodes
+        // (read through L1) and stage the primitive records only
+        S.smem_top_nodes = persistent ? 0 : int(keep);
         S.smem_prims = std::min(d->n_prims, 64);
-        if (d->n_meshes > 0) {
+        if (d->n_meshes > 0 && !persistent) {
             int share = 512 / d->n_meshes;  // nodes per mesh out of a 16 KB budget
             int off = 0;
             for (DevMesh& M : meshes) {
-                if (M.nodes2) continue;  // GPU-built trees are read through L1/L2 only
+                if (M.nodes2 || !M.nodes) continue;  // GPU-built trees are read through L1/L2 only
                 int cnt = (1 << M.depth) - 1;
                 while (cnt > share) cnt >>= 1;  // 2^L - 1 stays of that form
                 M.smem_off = off;
@@ -528,6 +655,12 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     if ((rc = upload_vec(c, top2, &d_top2)) || (rc = upload_vec(c, top4, &d_top4))) return rc;
     S.top2 = d_top2;
     S.top4 = d_top4;
+    S.u_nodes = d_unodes;
+    S.u_tris = d_utris;
+    S.u_n_tris = u_n_tris;
+    S.u_pad_rel = u_pad_rel;
+    S.u_pad_abs = u_pad_abs;
+    S.u_radius = u_radius;
     if ((rc = upload_vec(c, top, &d_top)) || (rc = upload_vec(c, prims, &d_prims)) || (rc = upload_vec(c, color, &d_color)) ||
         (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)) || (rc = upload_vec(c, leaf_bb, &d_leaf_bb)) ||
         (rc = upload_vec(c, flat, &d_flat)))
@@ -543,13 +676,15 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.top_depth = td;
     S.n_prims = d->n_prims;
     S.n_meshes = d->n_meshes;
-    // persistent warps need every mesh tree in the GPU-built form
-    // (measured: 1.8x on the 1 M-triangle workload, +20 % on a tree of 122 analytic primitives)
-    S.persistent = (c->opt_persistent && flat.empty() && (d->n_meshes == 0 || c->opt_mesh_bvh)) ? 1 : 0;
+    S.persistent = persistent ? 1 : 0;
     S.refill_lanes = c->opt_refill_lanes > 0 ? c->opt_refill_lanes : (d->n_meshes > 0 ? 8 : 32);
     // every copy above was enqueued on the context's stream from host temporaries of this call (pageable memory:
     // the runtime stages them, but the order against later work on c->stream is only defined in-stream)
+    int h_flag = 0;
+    if (d_flag) CK(c, cudaMemcpyAsync(&h_flag, d_flag, sizeof(int), cudaMemcpyDeviceToHost, c->stream));
     CK(c, cudaStreamSynchronize(c->stream));
+    if (h_flag & 1) return fail(c, MCPT_E_INVALID, "mesh: vertex index out of range");
+    if (h_flag & 2) return fail(c, MCPT_E_INVALID, "mesh: leaf slot of the uploaded BVH holds an index out of range");
     if (!build_allocs.empty()) free_all(c, build_allocs);  // the tree builds are done: their scratch can go
     trim_cache(c);
     c->scene = S;

@@ -18,6 +18,7 @@
 #include <cub/device/device_radix_sort.cuh>
 #include <cuda_runtime.h>
 
+#include <algorithm>
 #include <cfloat>
 #include <climits>
 #include <cstdint>
@@ -39,13 +40,62 @@ __device__ __forceinline__ uint32_t expand10(uint32_t v) {
     return v;
 }
 
-__global__ void k_morton(const float* __restrict__ pos, const uint32_t* __restrict__ idx, int n_tris, float3 lo, float3 inv_ext,
+// order-preserving map float -> uint32 (atomicMin / atomicMax on floats of either sign)
+__device__ __forceinline__ uint32_t f2ord(float f) {
+    const uint32_t u = __float_as_uint(f);
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float ord2f(uint32_t u) { return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u); }
+
+__global__ void k_bounds_init(uint32_t* __restrict__ bounds) {
+    if (threadIdx.x < 3) bounds[threadIdx.x] = 0xffffffffu;
+    else if (threadIdx.x < 6) bounds[threadIdx.x] = 0u;
+}
+
+// Box of the vertices the tree is built over (bounds[0..2] = min, [3..5] = max, order-encoded), and -- for a tree in
+// world space (the unified tree of a mesh instance) -- those vertices themselves: wpos = fwd * pos. No host pass
+// over the vertex array is needed at upload.
+__global__ void k_xform_bounds(const float* __restrict__ pos, int n_verts, Aff fwd, int transform, float* __restrict__ wpos,
+                               uint32_t* __restrict__ bounds) {
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    for (int v = blockIdx.x * blockDim.x + threadIdx.x; v < n_verts; v += gridDim.x * blockDim.x) {
+        float x = pos[3 * v], y = pos[3 * v + 1], z = pos[3 * v + 2];
+        if (transform) {
+            const float wx = fwd.r0.x * x + fwd.r0.y * y + fwd.r0.z * z + fwd.r0.w;
+            const float wy = fwd.r1.x * x + fwd.r1.y * y + fwd.r1.z * z + fwd.r1.w;
+            const float wz = fwd.r2.x * x + fwd.r2.y * y + fwd.r2.z * z + fwd.r2.w;
+            x = wx; y = wy; z = wz;
+            wpos[3 * v] = x; wpos[3 * v + 1] = y; wpos[3 * v + 2] = z;
+        }
+        lo[0] = fminf(lo[0], x); lo[1] = fminf(lo[1], y); lo[2] = fminf(lo[2], z);
+        hi[0] = fmaxf(hi[0], x); hi[1] = fmaxf(hi[1], y); hi[2] = fmaxf(hi[2], z);
+    }
+    for (int k = 0; k < 3; ++k)
+        for (int off = 16; off > 0; off >>= 1) {
+            lo[k] = fminf(lo[k], __shfl_xor_sync(0xffffffffu, lo[k], off));
+            hi[k] = fmaxf(hi[k], __shfl_xor_sync(0xffffffffu, hi[k], off));
+        }
+    if ((threadIdx.x & 31) == 0)
+        for (int k = 0; k < 3; ++k) {
+            if (lo[k] <= hi[k]) {
+                atomicMin(bounds + k, f2ord(lo[k]));
+                atomicMax(bounds + 3 + k, f2ord(hi[k]));
+            }
+        }
+}
+
+// (vertex indices are clamped wherever a build kernel follows them: an out-of-range index is reported by
+// check_indices, it must not fault first)
+__global__ void k_morton(const float* __restrict__ pos, const uint32_t* __restrict__ idx, int n_tris, uint32_t vmax, const uint32_t* __restrict__ bounds,
                          uint32_t* __restrict__ keys, uint32_t* __restrict__ vals) {
     int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= n_tris) return;
+    const float3 lo = make_float3(ord2f(bounds[0]), ord2f(bounds[1]), ord2f(bounds[2]));
+    const float3 inv_ext = make_float3(1.0f / fmaxf(ord2f(bounds[3]) - lo.x, 1e-30f), 1.0f / fmaxf(ord2f(bounds[4]) - lo.y, 1e-30f),
+                                       1.0f / fmaxf(ord2f(bounds[5]) - lo.z, 1e-30f));
     float c[3];
     for (int k = 0; k < 3; ++k) {
-        float a = pos[3 * idx[3 * t] + k], b = pos[3 * idx[3 * t + 1] + k], d = pos[3 * idx[3 * t + 2] + k];
+        float a = pos[3 * min(idx[3 * t], vmax) + k], b = pos[3 * min(idx[3 * t + 1], vmax) + k], d = pos[3 * min(idx[3 * t + 2], vmax) + k];
         c[k] = (a + b + d) * (1.0f / 3.0f);
     }
     float fx = fminf(fmaxf((c[0] - lo.x) * inv_ext.x * 1024.0f, 0.0f), 1023.0f);
@@ -56,10 +106,13 @@ __global__ void k_morton(const float* __restrict__ pos, const uint32_t* __restri
 }
 
 // leaf c holds sorted triangles [L*c, L*c + L), L = kMeshLeafTris; writes the DevTri slots, the leaf box and the leaf key
-__global__ void k_leaves(const float* __restrict__ pos, const uint32_t* __restrict__ idx, const int32_t* __restrict__ slot_of_tri,
-                         const uint32_t* __restrict__ sorted_keys, const uint32_t* __restrict__ sorted_tris, int n_tris,
-                         int n_leaves, DevTri* __restrict__ tris, float* __restrict__ box_lo, float* __restrict__ box_hi,
-                         uint32_t* __restrict__ leaf_keys) {
+// pos: the vertices stored in the DevTri slots (mesh-local: the exact test runs there); bpos: the vertices the boxes are
+// fitted to (= pos, or the world positions of a mesh instance). slot_of_tri == null: no reference tree was uploaded,
+// the tie-break rank of a triangle is its index. prim: stored in c.w (the unified tree finds the instance there).
+__global__ void k_leaves(const float* __restrict__ pos, const float* __restrict__ bpos, const uint32_t* __restrict__ idx,
+                         const int32_t* __restrict__ slot_of_tri, const uint32_t* __restrict__ sorted_keys,
+                         const uint32_t* __restrict__ sorted_tris, int n_tris, uint32_t vmax, int n_leaves, int prim, DevTri* __restrict__ tris,
+                         float* __restrict__ box_lo, float* __restrict__ box_hi, uint32_t* __restrict__ leaf_keys) {
     int c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= n_leaves) return;
     float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
@@ -70,16 +123,18 @@ __global__ void k_leaves(const float* __restrict__ pos, const uint32_t* __restri
         int tri = -1, rank = -1;
         if (s < n_tris) {
             tri = int(sorted_tris[s]);
-            rank = slot_of_tri[tri];
+            rank = slot_of_tri ? slot_of_tri[tri] : tri;
         }
         if (rank < 0) tri = -1;  // not in the reference tree: never tested there either
         if (tri >= 0) {
             float v[3][3];
             for (int q = 0; q < 3; ++q)
                 for (int k = 0; k < 3; ++k) {
-                    v[q][k] = pos[3 * idx[3 * tri + q] + k];
-                    lo[k] = fminf(lo[k], v[q][k]);
-                    hi[k] = fmaxf(hi[k], v[q][k]);
+                    const uint32_t vi = 3 * min(idx[3 * tri + q], vmax) + k;
+                    v[q][k] = pos[vi];
+                    const float b = bpos[vi];
+                    lo[k] = fminf(lo[k], b);
+                    hi[k] = fmaxf(hi[k], b);
                 }
             T.a = make_float4(v[0][0], v[0][1], v[0][2], 0.0f);
             T.b = make_float4(v[1][0], v[1][1], v[1][2], 0.0f);
@@ -87,6 +142,7 @@ __global__ void k_leaves(const float* __restrict__ pos, const uint32_t* __restri
         }
         T.a.w = __int_as_float(tri);
         T.b.w = __int_as_float(rank);
+        T.c.w = __int_as_float(prim);
         tris[s] = T;
     }
     for (int k = 0; k < 3; ++k) {
@@ -211,7 +267,9 @@ struct Slot4 {
     int tok;
 };
 
-__device__ __forceinline__ void write_node4(DevNode4* __restrict__ out, const Slot4* s, int n_slots) {
+// node_base / leaf_base: where this tree's nodes and triangle slots sit in the arrays the walk indexes (0 for a mesh
+// tree of its own; the unified tree holds every instance's subtree in one node array and one slot array)
+__device__ __forceinline__ void write_node4(DevNode4* __restrict__ out, const Slot4* s, int n_slots, int node_base, int leaf_base) {
     float lo[3][4], hi[3][4];
     int tok[4];
     for (int j = 0; j < 4; ++j) {
@@ -220,7 +278,7 @@ __device__ __forceinline__ void write_node4(DevNode4* __restrict__ out, const Sl
             lo[k][j] = used ? s[j].lo[k] : FLT_MAX;  // an unused slot is rejected by its token (the walk checks it)
             hi[k][j] = used ? s[j].hi[k] : -FLT_MAX;
         }
-        tok[j] = used ? s[j].tok : kTokEmptyBuild;
+        tok[j] = used ? (s[j].tok >= 0 ? s[j].tok + node_base : s[j].tok - leaf_base) : kTokEmptyBuild;
     }
     DevNode4 N;
     N.lox = make_float4(lo[0][0], lo[0][1], lo[0][2], lo[0][3]);
@@ -244,7 +302,8 @@ __device__ __forceinline__ int unpack2(const DevNode2& N, Slot4* s) {
     return 2;
 }
 
-__global__ void k_collapse4(int n, const int* __restrict__ parent, const DevNode2* __restrict__ nodes2, DevNode4* __restrict__ nodes4) {
+__global__ void k_collapse4(int n, const int* __restrict__ parent, const DevNode2* __restrict__ nodes2, DevNode4* __restrict__ nodes4,
+                            int node_base, int leaf_base) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n - 1) return;
     int depth = 0;
@@ -261,14 +320,14 @@ __global__ void k_collapse4(int n, const int* __restrict__ parent, const DevNode
             out[m++] = ch[j];
         }
     }
-    write_node4(nodes4 + i, out, m);
+    write_node4(nodes4 + i, out, m, node_base, leaf_base);
 }
 
 // single-leaf mesh: one wide node with that leaf as its only child
-__global__ void k_single4(const DevNode2* __restrict__ nodes2, DevNode4* __restrict__ nodes4) {
+__global__ void k_single4(const DevNode2* __restrict__ nodes2, DevNode4* __restrict__ nodes4, int node_base, int leaf_base) {
     Slot4 ch[2];
     unpack2(nodes2[0], ch);
-    write_node4(nodes4, ch, 1);
+    write_node4(nodes4, ch, 1, node_base, leaf_base);
 }
 
 }  // namespace
@@ -279,13 +338,14 @@ inline size_t align256(size_t b) { return (b + 255) & ~size_t(255); }
 
 // carve the build's scratch arrays out of one workspace (same order in the size query and the build)
 struct Scratch {
-    uint32_t *keys, *vals, *keys2, *vals2, *leaf_keys;
-    float *box_lo, *box_hi;
+    uint32_t *keys, *vals, *keys2, *vals2, *leaf_keys, *bounds;
+    float *box_lo, *box_hi, *wpos;
     int2* children;
     int *parent, *arrivals;
+    DevNode2* nodes2;
     void* sort_tmp;
     size_t sort_bytes, total;
-    Scratch(void* base, int n_tris, int n, size_t sort_b) : sort_bytes(sort_b) {
+    Scratch(void* base, int n_tris, int n, int n_verts, size_t sort_b) : sort_bytes(sort_b) {
         size_t off = 0;
         auto take = [&](size_t bytes) {
             void* p = base ? static_cast<char*>(base) + off : nullptr;
@@ -297,11 +357,14 @@ struct Scratch {
         keys2 = static_cast<uint32_t*>(take(sizeof(uint32_t) * n_tris));
         vals2 = static_cast<uint32_t*>(take(sizeof(uint32_t) * n_tris));
         leaf_keys = static_cast<uint32_t*>(take(sizeof(uint32_t) * n));
+        bounds = static_cast<uint32_t*>(take(sizeof(uint32_t) * 8));
         box_lo = static_cast<float*>(take(sizeof(float) * 3 * (2 * size_t(n))));
         box_hi = static_cast<float*>(take(sizeof(float) * 3 * (2 * size_t(n))));
+        wpos = static_cast<float*>(take(sizeof(float) * 3 * size_t(n_verts)));
         children = static_cast<int2*>(take(sizeof(int2) * n));
         parent = static_cast<int*>(take(sizeof(int) * 2 * size_t(n)));
         arrivals = static_cast<int*>(take(sizeof(int) * n));
+        nodes2 = static_cast<DevNode2*>(take(sizeof(DevNode2) * size_t(n > 1 ? n - 1 : 1)));
         sort_tmp = take(sort_bytes);
         total = off;
     }
@@ -316,37 +379,76 @@ size_t sort_temp_bytes(int n_tris) {
 
 }  // namespace
 
-size_t lbvh_workspace_bytes(int n_tris, int n_leaves) {
-    return Scratch(nullptr, n_tris, n_leaves, sort_temp_bytes(n_tris)).total;
+namespace {
+
+// flag[0] |= 1: a vertex index out of range; |= 2: a leaf slot of the uploaded reference tree out of range
+__global__ void k_check_idx(const uint32_t* __restrict__ idx, size_t n, uint32_t n_verts, int* __restrict__ flag) {
+    bool bad = false;
+    for (size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += size_t(gridDim.x) * blockDim.x) bad |= idx[i] >= n_verts;
+    if (__any_sync(0xffffffffu, bad) && (threadIdx.x & 31) == 0) atomicOr(flag, 1);
 }
 
-cudaError_t build_mesh_lbvh(cudaStream_t stream, const float* d_pos, const uint32_t* d_idx, int n_tris,
-                            const int32_t* d_slot_of_tri, const float lo[3], const float hi[3], DevNode2* d_nodes,
-                            DevNode4* d_nodes4, DevTri* d_tris, int n_leaves, void* workspace, size_t workspace_bytes,
+// slot_of_tri[ind[s]] = s: the reference tree's leaf slot of every triangle (a triangle sits in one slot; the highest wins otherwise, as on the host)
+__global__ void k_slots(const int32_t* __restrict__ ind, int n_slots, int n_tris, int32_t* __restrict__ slot_of_tri, int* __restrict__ flag) {
+    const int s = blockIdx.x * blockDim.x + threadIdx.x;
+    if (s >= n_slots) return;
+    const int t = ind[s];
+    if (t < -1 || t >= n_tris) {
+        atomicOr(flag, 2);
+        return;
+    }
+    if (t >= 0) atomicMax(slot_of_tri + t, s);
+}
+
+}  // namespace
+
+void check_indices(cudaStream_t stream, const uint32_t* d_idx, size_t n, uint32_t n_verts, int* d_flag) {
+    if (!n) return;
+    const int grid = int(std::min<size_t>((n + kB - 1) / kB, 1184));
+    k_check_idx<<<grid, kB, 0, stream>>>(d_idx, n, n_verts, d_flag);
+}
+
+cudaError_t slots_from_leaves(cudaStream_t stream, const int32_t* d_ind, int n_slots, int n_tris, int32_t* d_slot_of_tri, int* d_flag) {
+    cudaError_t e = cudaMemsetAsync(d_slot_of_tri, 0xff, sizeof(int32_t) * size_t(n_tris), stream);  // -1
+    if (e != cudaSuccess) return e;
+    k_slots<<<(n_slots + kB - 1) / kB, kB, 0, stream>>>(d_ind, n_slots, n_tris, d_slot_of_tri, d_flag);
+    return cudaGetLastError();
+}
+
+size_t lbvh_workspace_bytes(int n_tris, int n_leaves, int n_verts) {
+    return Scratch(nullptr, n_tris, n_leaves, n_verts, sort_temp_bytes(n_tris)).total;
+}
+
+cudaError_t build_mesh_lbvh(cudaStream_t stream, const LbvhBuild& b, void* workspace, size_t workspace_bytes,
                             unsigned long long* launches) {
-    const int n = n_leaves;
-    Scratch w(workspace, n_tris, n, sort_temp_bytes(n_tris));
+    const int n = b.n_leaves, n_tris = b.n_tris;
+    Scratch w(workspace, n_tris, n, b.n_verts, sort_temp_bytes(n_tris));
     if (!workspace || w.total > workspace_bytes) return cudaErrorInvalidValue;
-    float3 l3 = make_float3(lo[0], lo[1], lo[2]);
-    float3 ie = make_float3(1.0f / fmaxf(hi[0] - lo[0], 1e-30f), 1.0f / fmaxf(hi[1] - lo[1], 1e-30f),
-                            1.0f / fmaxf(hi[2] - lo[2], 1e-30f));
-    k_morton<<<(n_tris + kB - 1) / kB, kB, 0, stream>>>(d_pos, d_idx, n_tris, l3, ie, w.keys, w.vals);
+    DevNode2* nodes2 = b.d_nodes ? b.d_nodes : w.nodes2;
+    Aff fwd{};
+    if (b.fwd) fwd = *b.fwd;
+    const float* bpos = b.fwd ? w.wpos : b.d_pos;
+    k_bounds_init<<<1, 32, 0, stream>>>(w.bounds);
+    const int vgrid = std::min((b.n_verts + kB - 1) / kB, 1184);
+    k_xform_bounds<<<std::max(vgrid, 1), kB, 0, stream>>>(b.d_pos, b.n_verts, fwd, b.fwd ? 1 : 0, w.wpos, w.bounds);
+    const uint32_t vmax = uint32_t(std::max(b.n_verts, 1) - 1);
+    k_morton<<<(n_tris + kB - 1) / kB, kB, 0, stream>>>(bpos, b.d_idx, n_tris, vmax, w.bounds, w.keys, w.vals);
     size_t sort_bytes = w.sort_bytes;
     cudaError_t e = cub::DeviceRadixSort::SortPairs(w.sort_tmp, sort_bytes, w.keys, w.keys2, w.vals, w.vals2, n_tris, 0, 30, stream);
     if (e != cudaSuccess) return e;
-    k_leaves<<<(n + kB - 1) / kB, kB, 0, stream>>>(d_pos, d_idx, d_slot_of_tri, w.keys2, w.vals2, n_tris, n, d_tris, w.box_lo,
-                                                   w.box_hi, w.leaf_keys);
+    k_leaves<<<(n + kB - 1) / kB, kB, 0, stream>>>(b.d_pos, bpos, b.d_idx, b.d_slot_of_tri, w.keys2, w.vals2, n_tris, vmax, n, b.prim,
+                                                   b.d_tris, w.box_lo, w.box_hi, w.leaf_keys);
     if (n == 1) {
-        k_single<<<1, 1, 0, stream>>>(w.box_lo, w.box_hi, d_nodes);
-        k_single4<<<1, 1, 0, stream>>>(d_nodes, d_nodes4);
-        if (launches) *launches += 4;
+        k_single<<<1, 1, 0, stream>>>(w.box_lo, w.box_hi, nodes2);
+        k_single4<<<1, 1, 0, stream>>>(nodes2, b.d_nodes4, b.node_base, b.leaf_base);
+        if (launches) *launches += 6;
     } else {
         e = cudaMemsetAsync(w.arrivals, 0, sizeof(int) * n, stream);
         if (e != cudaSuccess) return e;
         k_hierarchy<<<(n - 1 + kB - 1) / kB, kB, 0, stream>>>(w.leaf_keys, n, w.children, w.parent);
-        k_fit<<<(n + kB - 1) / kB, kB, 0, stream>>>(n, w.children, w.parent, w.box_lo, w.box_hi, w.arrivals, d_nodes);
-        k_collapse4<<<(n - 1 + kB - 1) / kB, kB, 0, stream>>>(n, w.parent, d_nodes, d_nodes4);
-        if (launches) *launches += 5;
+        k_fit<<<(n + kB - 1) / kB, kB, 0, stream>>>(n, w.children, w.parent, w.box_lo, w.box_hi, w.arrivals, nodes2);
+        k_collapse4<<<(n - 1 + kB - 1) / kB, kB, 0, stream>>>(n, w.parent, nodes2, b.d_nodes4, b.node_base, b.leaf_base);
+        if (launches) *launches += 7;
     }
     return cudaGetLastError();
 }

@@ -241,6 +241,15 @@ __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, 
 #ifndef MCPT_BATCH_DELIVER
 #define MCPT_BATCH_DELIVER 0
 #endif
+// MCPT_FLOW == 2 ("while-while"): the node steps of an iteration are a loop of their own that a warp leaves only
+// when every lane stands at a leaf or is finished, so the leaf stages (primitive / mesh entry, triangle, deliver)
+// run once per iteration with many lanes instead of every iteration with a few.
+#ifndef MCPT_NODE_MIN_LANES
+#define MCPT_NODE_MIN_LANES 0
+#endif
+#ifndef MCPT_WW_NODE_STEPS
+#define MCPT_WW_NODE_STEPS 1
+#endif
 
 template <bool COUNT, bool MESHES, bool EXIT>
 __device__ __forceinline__ void traverse_persistent(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
@@ -306,6 +315,37 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
             }
         }
 #endif
+#if MCPT_FLOW == 2
+        // node phase: every lane pops / steps through nodes until its ray stands at a leaf (a triangle, a primitive) or is
+        // finished; the leaf stages below then run ONCE, with all those lanes in them
+#pragma unroll 1
+        while (true) {
+            const bool want = has_ray && !w.done && (w.cur >= 0 || w.cur == kTokPop);
+            const uint32_t wm = __ballot_sync(0xffffffffu, want);
+            if (!wm) break;
+#if MCPT_NODE_MIN_LANES > 0
+            // few lanes left in the tree while the others wait at their leaves: let the leaves go first
+            if (__popc(wm) < MCPT_NODE_MIN_LANES && __any_sync(0xffffffffu, has_ray && !want)) break;
+#endif
+            if (want && w.cur == kTokPop) walk_pop_one<WIDE>(w, S, st, wsave);
+            if (has_ray && !w.done && w.cur >= 0) {
+                walk_node<COUNT, WIDE>(w, wk, S, st, wsave);
+#pragma unroll
+                for (int r = 1; r < MCPT_WW_NODE_STEPS; ++r)
+                    if (w.cur >= 0) walk_node<COUNT, WIDE>(w, wk, S, st, wsave);
+            }
+        }
+        if (has_ray && walk_kind(w) == WALK_PRIM) walk_prim<COUNT, MESHES, WIDE>(w, wk, S, sm, st, wsave);
+        if (MESHES && has_ray && walk_kind(w) == WALK_TRI) walk_tri<COUNT>(w, wk, S, sm, st, wsave);
+        {  // finished rays: deliver and free the lane
+            const bool fin = has_ray && w.done;
+            if (__any_sync(0xffffffffu, fin)) {
+                deliver<EXIT>(S, wf, sink, s_hits, p, fin, w.best, w.D);
+                if (fin) has_ray = false;
+            }
+        }
+        continue;
+#endif
 #pragma unroll 1
         for (int r = 0; r < MCPT_POPS_PER_ITER && has_ray && w.cur == kTokPop && !w.done; ++r)
             walk_pop_one<WIDE>(w, S, st, wsave);
@@ -347,6 +387,81 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
         else if (kind == WALK_PRIM)
             walk_prim<COUNT, MESHES, WIDE>(w, wk, S, sm, st, wsave);
 #endif
+    }
+}
+
+// Persistent warps over the unified world-space tree (traverse.cuh, UWalk): the same refill / deliver protocol as
+// traverse_persistent, with two kinds of step only. One iteration: take entries off the stack, a run of node steps,
+// the leaf step, deliver.
+#ifndef MCPT_U_POPS
+#define MCPT_U_POPS 2
+#endif
+#ifndef MCPT_U_NODE_STEPS
+#define MCPT_U_NODE_STEPS 2
+#endif
+#ifndef MCPT_U_LOOP
+#define MCPT_U_LOOP 1  // 1: pop -> node run -> leaf in every iteration; 2: the node phase loops until MCPT_U_MIN_LANES lanes or fewer still walk nodes
+#endif
+#ifndef MCPT_U_MIN_LANES
+#define MCPT_U_MIN_LANES 12
+#endif
+template <bool COUNT>
+__device__ __forceinline__ void traverse_unified(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
+                                                 uint32_t len, const HitSink& sink, uint32_t* s_next, uint32_t* s_hits, Work& wk) {
+    MCPT_WALK_STACK_DECL(st, kWalkStackWide);
+    UWalk w;
+    w.done = true;
+    w.cur = 0;
+    w.sp = 0;
+    const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
+    bool has_ray = false, exhausted = false;
+    uint32_t p = 0;
+    while (true) {
+        const uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
+        if (idle) {
+            if (!exhausted && (idle == 0xffffffffu || __popc(idle) >= S.refill_lanes)) {
+                uint32_t first = 0;
+                if (lane == 0) first = atomicAdd(s_next, uint32_t(__popc(idle)));
+                first = __shfl_sync(0xffffffffu, first, 0);
+                if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
+                    float4 o4, d4;
+                    wf.load_ray(p, o4, d4);
+                    uwalk_begin(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+                    has_ray = true;
+                }
+                exhausted = first + __popc(idle) >= len;
+            } else if (idle == 0xffffffffu) {
+                break;
+            }
+        }
+#if MCPT_U_LOOP == 2
+#pragma unroll 1
+        while (true) {
+            const bool want = has_ray && !w.done && (w.cur >= 0 || w.cur == kTokPop);
+            const uint32_t wm = __ballot_sync(0xffffffffu, want);
+            if (!wm) break;
+            if (__popc(wm) < MCPT_U_MIN_LANES && __any_sync(0xffffffffu, has_ray && !want)) break;
+            if (want && w.cur == kTokPop) uwalk_pop_one(w, st);
+            if (has_ray && !w.done && w.cur >= 0) uwalk_node<COUNT>(w, wk, S, st);
+        }
+#else
+#pragma unroll 1
+        for (int r = 0; r < MCPT_U_POPS && has_ray && w.cur == kTokPop && !w.done; ++r) uwalk_pop_one(w, st);
+        if (has_ray && !w.done && w.cur >= 0) {
+            uwalk_node<COUNT>(w, wk, S, st);
+#pragma unroll
+            for (int r = 1; r < MCPT_U_NODE_STEPS; ++r)
+                if (w.cur >= 0) uwalk_node<COUNT>(w, wk, S, st);
+        }
+#endif
+        if (has_ray && !w.done && w.cur < 0 && w.cur != kTokPop) uwalk_leaf<COUNT>(w, wk, S, sm);
+        {  // finished rays: deliver and free the lane
+            const bool fin = has_ray && w.done;
+            if (__any_sync(0xffffffffu, fin)) {
+                deliver<false>(S, wf, sink, s_hits, p, fin, w.best, w.D);
+                if (fin) has_ray = false;
+            }
+        }
     }
 }
 
@@ -397,6 +512,36 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
     }
 }
 
+// the unified walk as a kernel of its own (queue protocol and epilogue of k_traverse)
+template <bool COUNT, int MINB>
+__global__ void __launch_bounds__(kBlock, MINB) k_traverse_unified(DevScene S, Wavefront wf, QueueIn qin, HitSink sink,
+                                                                    unsigned long long* ray_counter, unsigned long long* work) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t s_hits, s_next;
+    const uint32_t len = queue_len(qin);
+    if (len == 0) {
+        if (threadIdx.x == 0 && sink.hitq.items) sink.hitq.counts[blockIdx.x] = 0u;
+        return;
+    }
+    if (threadIdx.x == 0) s_hits = s_next = 0u;
+    SmemScene sm = stage_scene(S, smem_raw);  // ends with a barrier
+    Work wk;
+    traverse_unified<COUNT>(S, sm, wf, qin, len, sink, &s_next, &s_hits, wk);
+    if (ray_counter && threadIdx.x == 0) {
+        unsigned long long rays = len;
+        if (!qin.items) {
+            const uint32_t last_tile = blockIdx.x + (len / kBlock - 1u) * gridDim.x;
+            if (last_tile * kBlock + kBlock > qin.n_identity) rays -= last_tile * kBlock + kBlock - qin.n_identity;
+        }
+        atomicAdd(ray_counter, rays);
+    }
+    if (COUNT) flush_work(wk, work);
+    if (sink.hitq.items) {
+        __syncthreads();
+        if (threadIdx.x == 0) sink.hitq.counts[blockIdx.x] = s_hits;
+    }
+}
+
 template <bool COUNT, int MINB>
 static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const HitSink& sink,
                                  unsigned long long* ray_counter, unsigned long long* work) {
@@ -429,6 +574,19 @@ void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const
         sink.exit_mode = 1;
         sink.flat_face = exit_prm->flat_face;
         sink.refract_ind = exit_prm->refract_ind;
+    }
+    if (S.u_nodes && S.persistent) {
+#define MCPT_TRAVERSE_U(COUNT, MINB) \
+    k_traverse_unified<COUNT, MINB><<<lc.grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink, ray_counter, work)
+        if (work) MCPT_TRAVERSE_U(true, 2);
+        else if (lc.traverse_occ >= 6) MCPT_TRAVERSE_U(false, 6);
+        else if (lc.traverse_occ == 5) MCPT_TRAVERSE_U(false, 5);
+        else if (lc.traverse_occ == 4) MCPT_TRAVERSE_U(false, 4);
+        else if (lc.traverse_occ == 3) MCPT_TRAVERSE_U(false, 3);
+        else MCPT_TRAVERSE_U(false, 2);
+#undef MCPT_TRAVERSE_U
+        lc.count();
+        return;
     }
     if (work)
         launch_traverse_kind<true, 2>(lc, S, wf, qin, sink, ray_counter, work);

@@ -75,9 +75,13 @@ struct DevNode2 {
 // stack operations for the same boxes. 128 bytes = one L2 line, boxes stored per component so that one
 // float4 feeds the same slab plane of all four children. Child j: token tok[j] (>= 0 node index,
 // < 0 ~leaf, kTokEmpty: no child).
+// The two planes of one axis are neighbours (float4 index 2 * axis and 2 * axis + 1), so a ray that keeps the index of
+// the plane it ENTERS through per axis (0 / 1, 2 / 3, 4 / 5, by the sign of its direction) loads entry and exit planes
+// directly and needs no per-axis min / max (walk_node_u).
 struct DevNode4 {
-    float4 lox, loy, loz;  // min of children 0..3
-    float4 hix, hiy, hiz;  // max of children 0..3
+    float4 lox, hix;  // min / max x of children 0..3
+    float4 loy, hiy;
+    float4 loz, hiz;
     int4 tok;
     int4 pad;
 };
@@ -117,6 +121,19 @@ struct DevScene {
     int32_t refill_lanes;      // persistent warps: idle lanes that trigger a refill (MCPT_OPT_REFILL_LANES)
     const DevNode2* top2;      // the top-level tree in two-children node format (persistent warps), root = node 0
     const DevNode4* top4;      // ... and in four-children format (MCPT_WIDE), root = node 0
+    // The unified world-space tree (MCPT_OPT_UNIFIED, scenes with meshes): the top-level tree and, below each placement of
+    // a mesh, a subtree fitted to the WORLD positions of that instance's triangles, all in one array of four-children
+    // nodes (root = node 0). A ray is walked in one frame: no mesh entry / exit, one kind of node, one kind of leaf step.
+    // Leaf token ~L: L < u_n_tris is triangle slot L of u_tris (local vertices; c.w = primitive id of the instance),
+    // else analytic primitive L - u_n_tris. null: the two-level walk.
+    const DevNode4* u_nodes;
+    const DevTri* u_tris;
+    int32_t u_n_tris;
+    // The exact tests run in primitive-local frames reached through the uploaded inverse transforms, which are not the
+    // exact inverses of the forward ones: a hit the exact test accepts lies off the world ray by up to
+    // |fwd * inv - 1| * (|O| + distance). Every box of the unified tree is therefore padded PER RAY by
+    // u_pad_rel * (|O|_1 + u_radius) + u_pad_abs (both bounds computed at upload from the matrices themselves).
+    float u_pad_rel, u_pad_abs, u_radius;
     // shared-memory staging plan (in units of DevNode / DevPrim)
     int32_t smem_top_nodes;    // first N top-level nodes staged
     int32_t smem_prims;        // first N primitive records staged

@@ -622,6 +622,132 @@ MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemSce
     w.cur = kTokPop;
 }
 
+// ---------------------------------------------------------- unified world-space walk
+// Scenes with meshes, MCPT_OPT_UNIFIED (default): ONE tree of four-children nodes in world space (DevScene::u_nodes) --
+// the top-level SAH tree with, below each placement of a mesh, a subtree fitted to the world positions of that
+// instance's triangles. A ray never changes frame while it walks: no mesh-entry step, no exit marker on the stack, no
+// parked world frame, and the state a lane carries shrinks from ~48 to ~30 registers. The exact tests still run in the
+// primitive's own frame (Oi = inv * O, Di = normalize(inv * D), rebuilt at the leaf from the primitive record), with the
+// reference's arithmetic, so hit records are the same bits as with the two-level walk. Two kinds of step remain:
+//   node   four child boxes; the ray keeps, per axis, the index of the plane it enters through, so entry and exit
+//          planes are loaded directly (no per-axis min / max) and every box is padded per ray (DevScene::u_pad_*)
+//          by folding the padding into two offset vectors (odn, odf);
+//   leaf   one triangle of one instance (transform + Moeller-Trumbore + offer), or one analytic primitive.
+struct UWalk {
+    f3 O, D;           // world ray as given
+    f3 idir, odn, odf; // culling frame: t_entry = plane * idir + odn, t_exit = plane * idir + odf
+    float tmax, slack;
+    uint32_t nx, ny, nz;  // float4 index of the entry plane per axis inside a DevNode4 (exit plane: ^ 1)
+    int cur, sp;
+    bool done;
+    Best best;
+};
+
+MCPT_DEV void uwalk_begin(UWalk& w, const DevScene& S, f3 O, f3 D) {
+    best_reset(w.best);
+    w.O = O;
+    w.D = D;
+    w.done = true;
+    w.cur = 0;
+    w.sp = 0;
+    const float len = sqrtf(D.x * D.x + D.y * D.y + D.z * D.z);
+    if (!(len > 0.0f) || !(len < FLT_MAX)) return;  // zero / NaN / inf direction: nothing is hit
+    const float rl = (len < 1e-30f) ? 1.0f / len : cull_rcp(len);
+    const f3 dn = mk3(D.x * rl, D.y * rl, D.z * rl);  // culling only
+    w.idir = safe_rcp3(dn);
+    const f3 od = mk3(-O.x * w.idir.x, -O.y * w.idir.y, -O.z * w.idir.z);
+    const float o1 = fabsf(O.x) + fabsf(O.y) + fabsf(O.z);
+    w.slack = 1e-4f * o1 + 1e-3f;
+    const float eps = S.u_pad_rel * (o1 + S.u_radius) + S.u_pad_abs;
+    const f3 pe = mk3(eps * fabsf(w.idir.x), eps * fabsf(w.idir.y), eps * fabsf(w.idir.z));
+    w.odn = mk3(od.x - pe.x, od.y - pe.y, od.z - pe.z);
+    w.odf = mk3(od.x + pe.x, od.y + pe.y, od.z + pe.z);
+    w.nx = (__float_as_uint(w.idir.x) >> 31);        // direction < 0: the ray enters through the max plane
+    w.ny = 2u + (__float_as_uint(w.idir.y) >> 31);
+    w.nz = 4u + (__float_as_uint(w.idir.z) >> 31);
+    w.tmax = FLT_MAX;
+    w.done = false;
+}
+
+MCPT_DEV float slab_entry_u(float nx, float ny, float nz, float fx, float fy, float fz, int tok, const UWalk& w) {
+    const float tn = fmaxf(fmaxf(__fmaf_rn(nx, w.idir.x, w.odn.x), __fmaf_rn(ny, w.idir.y, w.odn.y)), fmaxf(__fmaf_rn(nz, w.idir.z, w.odn.z), 0.0f));
+    const float tf = fminf(fminf(__fmaf_rn(fx, w.idir.x, w.odf.x), __fmaf_rn(fy, w.idir.y, w.odf.y)), fminf(__fmaf_rn(fz, w.idir.z, w.odf.z), w.tmax));
+    return (tn <= tf && tok != kTokEmpty) ? tn : __int_as_float(0x7f800000);
+}
+
+template <bool COUNT>
+MCPT_DEV void uwalk_node(UWalk& w, Work& wk, const DevScene& S, const WalkStack& st) {
+    const float4* q = reinterpret_cast<const float4*>(S.u_nodes + w.cur);
+    const float4 nxp = __ldg(q + w.nx), fxp = __ldg(q + (w.nx ^ 1u));
+    const float4 nyp = __ldg(q + w.ny), fyp = __ldg(q + (w.ny ^ 1u));
+    const float4 nzp = __ldg(q + w.nz), fzp = __ldg(q + (w.nz ^ 1u));
+    const int4 tok = __ldg(reinterpret_cast<const int4*>(q + 6));
+    int c0 = tok.x, c1 = tok.y, c2 = tok.z, c3 = tok.w;
+    float t0 = slab_entry_u(nxp.x, nyp.x, nzp.x, fxp.x, fyp.x, fzp.x, c0, w);
+    float t1 = slab_entry_u(nxp.y, nyp.y, nzp.y, fxp.y, fyp.y, fzp.y, c1, w);
+    float t2 = slab_entry_u(nxp.z, nyp.z, nzp.z, fxp.z, fyp.z, fzp.z, c2, w);
+    float t3 = slab_entry_u(nxp.w, nyp.w, nzp.w, fxp.w, fyp.w, fzp.w, c3, w);
+    if (COUNT) wk.boxes += 4;
+    order2(t0, c0, t1, c1);
+    order2(t2, c2, t3, c3);
+    order2(t0, c0, t2, c2);
+    order2(t1, c1, t3, c3);
+    order2(t1, c1, t2, c2);
+    const float inf = __int_as_float(0x7f800000);
+    if (t3 < inf) st.put(w.sp++, c3, t3);
+    if (t2 < inf) st.put(w.sp++, c2, t2);
+    if (t1 < inf) st.put(w.sp++, c1, t1);
+    w.cur = (t0 < inf) ? c0 : kTokPop;
+}
+
+// one entry off the stack: dropped if it can no longer hold a closer hit
+MCPT_DEV void uwalk_pop_one(UWalk& w, const WalkStack& st) {
+    if (w.sp == 0) {
+        w.done = true;
+        return;
+    }
+    --w.sp;
+    int tok;
+    float tok_t;
+    st.get(w.sp, tok, tok_t);
+    if (tok_t <= w.tmax) w.cur = tok;
+}
+
+// leaf token: a triangle slot of a mesh instance, or an analytic primitive
+template <bool COUNT>
+MCPT_DEV void uwalk_leaf(UWalk& w, Work& wk, const DevScene& S, const SmemScene& sm) {
+    const int L = ~w.cur;
+    if (L < S.u_n_tris) {
+        const DevTri* tp = S.u_tris + L;
+        const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+        const int tri = __float_as_int(ta.w);
+        if (tri >= 0) {
+            if (COUNT) ++wk.tris;
+            const int pid = __float_as_int(tc.w);
+            const DevPrim* pp = (pid < S.smem_prims) ? (sm.prims + pid) : (S.prims + pid);
+            Aff inv;
+            inv.r0 = pp->inv.r0;
+            inv.r1 = pp->inv.r1;
+            inv.r2 = pp->inv.r2;
+            // intersect_prim + Mesh_intersect prologue (raytracer_func.frag:681-705)
+            const f3 Oi = xform_point(inv, w.O);
+            const f3 Di = normalize3(xform_vector(inv, w.D));
+            float a;
+            if (triangle_param(mk3(ta.x, ta.y, ta.z), mk3(tb.x, tb.y, tb.z), mk3(tc.x, tc.y, tc.z), Oi, Di, a)) {
+                Aff fwd;
+                fwd.r0 = pp->fwd.r0;
+                fwd.r1 = pp->fwd.r1;
+                fwd.r2 = pp->fwd.r2;
+                offer_at(w.best, fwd, Oi, Di, a, w.O, pid, tri, pp->slot, __float_as_int(tb.w));
+            }
+        }
+    } else {
+        prim_test<COUNT, false>(wk, S, sm, L - S.u_n_tris, w.O, w.D, w.slack, w.best);
+    }
+    if (w.best.h.prim >= 0) w.tmax = w.best.h.dist * 1.0001f + w.slack;
+    w.cur = kTokPop;
+}
+
 // Warp-coherent walk for scenes with a handful of primitives (the reference's box
 // scenes and the four-sphere scene): the leaf boxes form one flat list that every
 // lane of the warp steps through TOGETHER. Each lane culls the box against its own
