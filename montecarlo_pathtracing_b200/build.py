@@ -97,6 +97,14 @@ def build_ref(force=False, verbose=False):
         sys.stderr.write(r.stdout + r.stderr)
     if r.returncode != 0:
         raise RuntimeError("oracle/_ref build failed")
+    # ... and the same sources with the INTEGRATION.md patch compiled in, linked against libmcpt.so
+    integ = ORACLE / "build_integration.py"
+    if integ.exists():
+        r = subprocess.run([sys.executable, str(integ)] + (["--force"] if force else []), capture_output=True, text=True)
+        if verbose or r.returncode != 0:
+            sys.stderr.write(r.stdout + r.stderr)
+        if r.returncode != 0:
+            raise RuntimeError("oracle/_ref integration build failed")
     out = ORACLE / "_ref" / "libref.so"
     return out if out.exists() else None
 

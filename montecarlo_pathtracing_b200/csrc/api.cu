@@ -11,6 +11,7 @@
 #include <algorithm>
 #include <array>
 #include <cfloat>
+#include <chrono>
 #include <climits>
 #include <cmath>
 #include <cstdarg>
@@ -37,6 +38,11 @@ struct mcpt_ctx {
     cudaStream_t own_stream = nullptr;
     cudaStream_t stream = nullptr;
     std::string err;
+
+    // side streams of the upload-time tree builds (created on first use)
+    static constexpr int kSideStreams = 4;
+    cudaStream_t side[kSideStreams] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[kSideStreams] = {nullptr, nullptr, nullptr, nullptr};
 
     // scene
     std::vector<void*> scene_allocs;
@@ -159,6 +165,16 @@ void trim_cache(mcpt_ctx* c) {
         c->alloc_bytes.erase(e.second);
     }
     c->alloc_cache.clear();
+}
+
+int ensure_side_streams(mcpt_ctx* c) {
+    if (c->ev_fork) return MCPT_OK;
+    for (int k = 0; k < mcpt_ctx::kSideStreams; ++k) {
+        CK(c, cudaStreamCreateWithFlags(&c->side[k], cudaStreamNonBlocking));
+        CK(c, cudaEventCreateWithFlags(&c->ev_join[k], cudaEventDisableTiming));
+    }
+    CK(c, cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+    return MCPT_OK;
 }
 
 // register cap of the traversal kernel: the flat walk fits 64 registers without spilling (4 CTAs
@@ -285,6 +301,11 @@ int mcpt_destroy(mcpt_ctx* c) {
         cudaEventDestroy(sp.b);
     }
     for (cudaEvent_t e : c->free_events) cudaEventDestroy(e);
+    for (int k = 0; k < mcpt_ctx::kSideStreams; ++k) {
+        if (c->side[k]) cudaStreamDestroy(c->side[k]);
+        if (c->ev_join[k]) cudaEventDestroy(c->ev_join[k]);
+    }
+    if (c->ev_fork) cudaEventDestroy(c->ev_fork);
     if (c->own_stream) cudaStreamDestroy(c->own_stream);
     delete c;
     return MCPT_OK;

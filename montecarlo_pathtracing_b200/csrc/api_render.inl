@@ -88,9 +88,11 @@ struct StageSpan {
         c->spans.push_back(sp);
         idx = int(c->spans.size()) - 1;
     }
-    ~StageSpan() {
+    void end() {
         if (idx >= 0) cudaEventRecord(c->spans[idx].b, c->stream);
+        idx = -1;
     }
+    ~StageSpan() { end(); }
 };
 
 // raytracer.vert:9-22 evaluated for the four strip vertices, in fp32

@@ -119,6 +119,7 @@ struct DevScene {
     int32_t n_meshes;
     int32_t persistent;        // 1: tree scenes are traced by persistent warps (MCPT_OPT_PERSISTENT)
     int32_t refill_lanes;      // persistent warps: idle lanes that trigger a refill (MCPT_OPT_REFILL_LANES)
+    int32_t refill_first;      // ... on the identity queue (camera rays: the 32 rays of a warp are neighbours in the image)
     const DevNode2* top2;      // the top-level tree in two-children node format (persistent warps), root = node 0
     const DevNode4* top4;      // ... and in four-children format (MCPT_WIDE), root = node 0
     // The unified world-space tree (MCPT_OPT_UNIFIED, scenes with meshes): the top-level tree and, below each placement of

@@ -633,6 +633,9 @@ MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemSce
 //          planes are loaded directly (no per-axis min / max) and every box is padded per ray (DevScene::u_pad_*)
 //          by folding the padding into two offset vectors (odn, odf);
 //   leaf   one triangle of one instance (transform + Moeller-Trumbore + offer), or one analytic primitive.
+#ifndef MCPT_U_TOPREG
+#define MCPT_U_TOPREG 0
+#endif
 struct UWalk {
     f3 O, D;           // world ray as given
     f3 idir, odn, odf; // culling frame: t_entry = plane * idir + odn, t_exit = plane * idir + odf
@@ -640,8 +643,23 @@ struct UWalk {
     uint32_t nx, ny, nz;  // float4 index of the entry plane per axis inside a DevNode4 (exit plane: ^ 1)
     int cur, sp;
     bool done;
+#if MCPT_U_TOPREG
+    int top_tok;     // entry sp - 1 of the stack lives in these two registers (memory holds the ones below): the
+    float top_t;     // load that refills them is issued when an entry is taken and used one pop later
+#endif
     Best best;
 };
+
+#if MCPT_U_TOPREG
+MCPT_DEV void upush(UWalk& w, const WalkStack& st, int tok, float t) {
+    if (w.sp > 0) st.put(w.sp - 1, w.top_tok, w.top_t);
+    w.top_tok = tok;
+    w.top_t = t;
+    ++w.sp;
+}
+#else
+MCPT_DEV void upush(UWalk& w, const WalkStack& st, int tok, float t) { st.put(w.sp++, tok, t); }
+#endif
 
 MCPT_DEV void uwalk_begin(UWalk& w, const DevScene& S, f3 O, f3 D) {
     best_reset(w.best);
@@ -694,9 +712,9 @@ MCPT_DEV void uwalk_node(UWalk& w, Work& wk, const DevScene& S, const WalkStack&
     order2(t1, c1, t3, c3);
     order2(t1, c1, t2, c2);
     const float inf = __int_as_float(0x7f800000);
-    if (t3 < inf) st.put(w.sp++, c3, t3);
-    if (t2 < inf) st.put(w.sp++, c2, t2);
-    if (t1 < inf) st.put(w.sp++, c1, t1);
+    if (t3 < inf) upush(w, st, c3, t3);
+    if (t2 < inf) upush(w, st, c2, t2);
+    if (t1 < inf) upush(w, st, c1, t1);
     w.cur = (t0 < inf) ? c0 : kTokPop;
 }
 
@@ -709,7 +727,13 @@ MCPT_DEV void uwalk_pop_one(UWalk& w, const WalkStack& st) {
     --w.sp;
     int tok;
     float tok_t;
+#if MCPT_U_TOPREG
+    tok = w.top_tok;
+    tok_t = w.top_t;
+    if (w.sp > 0) st.get(w.sp - 1, w.top_tok, w.top_t);
+#else
     st.get(w.sp, tok, tok_t);
+#endif
     if (tok_t <= w.tmax) w.cur = tok;
 }
 

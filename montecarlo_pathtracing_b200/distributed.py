@@ -26,6 +26,46 @@ def reduce_accum(accum, root: int = 0, group=None):
     return accum
 
 
+def make_nccl_comm(rank: int, world: int):
+    """An ncclComm_t of our own over the ranks of the (already initialised) torch process group, for the C ABI's
+    mcpt_reduce_nccl: rank 0 draws the unique id, torch broadcasts it, every rank joins. The library resolves NCCL's
+    symbols from the copy already loaded in the process (torch's), which is promoted to the global namespace here.
+    Returns a ctypes.c_void_p (pass .value); the caller ends it with destroy_nccl_comm."""
+    import ctypes as C
+    import glob
+    import site
+
+    import torch
+    import torch.distributed as dist
+
+    paths = [p for sp in site.getsitepackages() for p in glob.glob(sp + "/nvidia/nccl/lib/libnccl.so.2")]
+    nccl = C.CDLL(paths[0] if paths else "libnccl.so.2", mode=C.RTLD_GLOBAL)
+
+    class NcclUniqueId(C.Structure):   # passed BY VALUE to ncclCommInitRank
+        _fields_ = [("internal", C.c_byte * 128)]
+
+    uid = NcclUniqueId()
+    if rank == 0 and nccl.ncclGetUniqueId(C.byref(uid)) != 0:
+        raise RuntimeError("ncclGetUniqueId failed")
+    t = torch.tensor(list(bytes(uid)), dtype=torch.uint8, device="cuda")
+    dist.broadcast(t, 0)
+    uid = NcclUniqueId.from_buffer_copy(t.cpu().numpy().tobytes())
+    comm = C.c_void_p()
+    nccl.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, NcclUniqueId, C.c_int]
+    nccl.ncclCommInitRank.restype = C.c_int
+    rc = nccl.ncclCommInitRank(C.byref(comm), world, uid, rank)
+    if rc != 0:
+        raise RuntimeError(f"ncclCommInitRank -> {rc}")
+    comm._nccl = nccl
+    return comm
+
+
+def destroy_nccl_comm(comm):
+    import ctypes as C
+    comm._nccl.ncclCommDestroy.argtypes = [C.c_void_p]
+    comm._nccl.ncclCommDestroy(comm)
+
+
 class SplitRenderer:
     """Drives one Context per rank. `accum` is a float32 torch tensor of h*w*4 elements on the
     context's device, bound as the library's accumulation target."""

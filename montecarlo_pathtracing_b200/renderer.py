@@ -96,9 +96,20 @@ class Scene:
         self._ck(self._h.mcpth_finalize(self._s), "finalize")
         return self
 
-    def desc(self) -> SceneDesc:
+    def desc(self, mesh_trees=True) -> SceneDesc:
+        """The include/mcpt_scene.h descriptor of the finalized scene. mesh_trees=False: the mesh descriptors carry no
+        BVH (bb = ind = NULL) -- what a host that never ran BVH_KDtree::compute on its meshes would upload; the
+        library then builds every mesh tree on the GPU and ranks equal-distance triangles by index."""
         d = SceneDesc()
         self._ck(self._h.mcpth_desc(self._s, C.byref(d)), "desc (finalize first)")
+        if not mesh_trees and d.n_meshes > 0:
+            from .capi import BvhDesc, MeshDesc
+            arr = (MeshDesc * d.n_meshes)()
+            for i in range(d.n_meshes):
+                m = d.meshes[i]
+                arr[i] = MeshDesc(BvhDesc(None, None, 0), m.tri_idx, m.pos, m.nrm, m.n_tris, m.n_verts, m.mesh_line)
+            d.meshes = C.cast(arr, C.POINTER(MeshDesc))
+            d._keep = arr
         return d
 
     @property

@@ -16,6 +16,7 @@ HIT_DTYPE = np.dtype([("index", "<i4"), ("tri_index", "<i4"), ("shape", "<i4"), 
 
 _libs = {}
 REF_LIB = HERE / "_ref" / "libref.so"
+INTEGRATION_LIB = HERE / "_ref" / "libref_integration.so"   # the same + the INTEGRATION.md patch compiled in (oracle/build_integration.py)
 
 
 def have_reference():
@@ -27,7 +28,7 @@ def lib(kind="port"):
     """kind 'port': liboracle.so, the hand restatement. kind 'reference': oracle/_ref/libref.so, the
     reference's own .cpp / shader text compiled by oracle/build_ref.py. Same entry points."""
     if kind not in _libs:
-        path = REF_LIB if kind == "reference" else HERE / "liboracle.so"
+        path = REF_LIB if kind == "reference" else INTEGRATION_LIB if kind == "integration" else HERE / "liboracle.so"
         if not path.exists():
             raise ImportError(f"{path} missing: run __graft_entry__.build()")
         L = C.CDLL(str(path))
@@ -67,7 +68,9 @@ def lib(kind="port"):
         L.oracle_rng_stream.argtypes = [C.c_float, C.c_float, C.c_int, C.c_float, C.c_int, fp, vp]
         L.oracle_random_rays.argtypes = [fp, C.c_float, C.c_float, C.c_float, C.c_int, fp]
         L.oracle_primary_ray.argtypes = [vp, C.c_int, C.c_int, C.c_int, C.c_int, fp, fp]
-        if kind == "reference":
+        if kind == "integration":
+            L.integration_set_ctx.argtypes = [vp]
+        if kind in ("reference", "integration"):
             L.oracle_build_repo_scene.argtypes = [vp, C.c_int, C.c_float]
             L.oracle_default_camera.argtypes = [C.c_int, C.c_int, fp, fp]
             L.oracle_transfo.argtypes = [C.c_char_p, fp, fp]
@@ -111,19 +114,19 @@ class Oracle:
 
     # ---- only on the 'reference' library: the reference's own scene builders / camera / Transfo
     def build_repo_scene(self, scene_id, light_intensity=1.2):
-        assert self.kind == "reference"
+        assert self.kind in ("reference", "integration")
         rc = self.L.oracle_build_repo_scene(self.h, int(scene_id), light_intensity)
         assert rc == 0, scene_id
         return self
 
     def default_camera(self, w, h):
-        assert self.kind == "reference"
+        assert self.kind in ("reference", "integration")
         iv, ipv = np.zeros(16, np.float32), np.zeros(16, np.float32)
         self.L.oracle_default_camera(w, h, iv.ctypes.data, ipv.ctypes.data)
         return iv, ipv
 
     def transfo(self, ops, *args):
-        assert self.kind == "reference"
+        assert self.kind in ("reference", "integration")
         a, out = _f32(args), np.zeros(16, np.float32)
         self.L.oracle_transfo(ops.encode(), a.ctypes.data, out.ctypes.data)
         return out
@@ -146,7 +149,7 @@ class Oracle:
     def add_mesh(self, pos, tri, nrm):
         p, n = _f32(pos).reshape(-1, 3), _f32(nrm).reshape(-1, 3)
         t = np.ascontiguousarray(tri, dtype=np.uint32).reshape(-1, 3)
-        if self.kind == "reference":
+        if self.kind in ("reference", "integration"):
             with _quiet_stdout():
                 return self.L.oracle_add_mesh(self.h, p.ctypes.data, len(p), n.ctypes.data, t.ctypes.data, len(t))
         return self.L.oracle_add_mesh(self.h, p.ctypes.data, len(p), n.ctypes.data, t.ctypes.data, len(t))
@@ -178,7 +181,7 @@ class Oracle:
         return self
 
     def finalize(self):
-        if self.kind == "reference":
+        if self.kind in ("reference", "integration"):
             with _quiet_stdout():
                 self.L.oracle_finalize(self.h)
         else:
@@ -214,7 +217,7 @@ class Oracle:
     def texture(self, k):
         """k: 0 prim, 1 bb, 2 ind, 3 tri, 4 pos, 5 nrm -> (height, 1024, comps) array."""
         hgt, comps = self.L.oracle_tex_height(self.h, k), self.L.oracle_tex_comps(self.h, k)
-        wid = self.L.oracle_tex_width(self.h, k) if self.kind == "reference" else 1024
+        wid = self.L.oracle_tex_width(self.h, k) if self.kind in ("reference", "integration") else 1024
         ctype = C.c_int32 if k in (2, 3) else C.c_float
         if hgt == 0:
             return np.zeros((0, 1024, comps), np.int32 if k in (2, 3) else np.float32)
