@@ -78,7 +78,11 @@ enum {
 /* tuning knobs for mcpt_set_option */
 enum {
     MCPT_OPT_PASSES_PER_BATCH = 0, /* passes traced together in one wavefront (default auto) */
-    MCPT_OPT_SMEM_STAGING = 1,     /* 1 = stage top BVH levels in shared memory (default 1)  */
+    MCPT_OPT_SMEM_STAGING = 1,     /* shared-memory staging of scene data in the traversal kernels: 0 = none, 1 = the leaf
+                                      boxes of small scenes (all of them, once per ray octant), the first 64 primitive
+                                      records, and the top levels of the trees the one-ray-per-lane walk reads (default),
+                                      2 = also the top levels (256 nodes) of the unified tree (measured slower: those
+                                      nodes already sit in L1). Set before mcpt_upload_scene. */
     MCPT_OPT_FAST_MATH = 2,        /* 1 = MUFU sin/cos/log/pow in the bounce sampler         */
     MCPT_OPT_MESH_BVH = 3,         /* 1 = rebuild every mesh tree on the GPU at upload (LBVH, one triangle
                                       per leaf; default 1), 0 = walk the uploaded median-split trees;
@@ -94,7 +98,8 @@ enum {
                                       persistent warps whose idle lanes fetch new rays (default), 0 = one ray per
                                       lane per tile. Set before mcpt_upload_scene. Same results. */
     MCPT_OPT_REFILL_LANES = 9,     /* persistent warps: idle lanes of a warp that trigger a refill from the queue,
-                                      1..32; 0 = auto (8 with meshes, 32 without). Set before mcpt_upload_scene. */
+                                      1..32; 0 = auto (8 with meshes, 12 on other unified trees, 32 else; camera rays 32).
+                                      Set before mcpt_upload_scene. */
     MCPT_OPT_TOP_SAH = 10,         /* 1 = the persistent warps walk a top-level tree built at upload by a full-sweep
                                       SAH over the primitives' leaf boxes (default), 0 = the topology of the uploaded
                                       median-split tree. Set before mcpt_upload_scene. Same results. */
@@ -102,12 +107,14 @@ enum {
                                       mcpt_render with whatever walker the scene selected (default), 1 = the
                                       one-ray-per-lane walk over the uploaded trees in the reference's visit order.
                                       any_hit always takes the latter. Same records. */
-    MCPT_OPT_UNIFIED = 12          /* scenes with meshes: 1 = one world-space tree over the top level and every mesh
-                                      instance, built on the GPU at upload, walked in a single frame (default; needs
+    MCPT_OPT_UNIFIED = 12          /* scenes with meshes, and trees of more than 256 leaves: 1 = one world-space tree of
+                                      four-children nodes over the top level and every mesh instance (instance subtrees
+                                      built on the GPU at upload), walked in a single frame (default; needs
                                       MCPT_OPT_MESH_BVH and MCPT_OPT_PERSISTENT), 0 = two-level walk (top-level tree,
                                       then the mesh's own tree in mesh space). Set before mcpt_upload_scene. Same
-                                      records. With 1, mcpt_mesh_desc.bvh may be empty (bb == ind == NULL): no host
-                                      tree is needed, triangles of equal distance are then ranked by index. */
+                                      records. mcpt_mesh_desc.bvh may be empty (bb == ind == NULL) whenever
+                                      MCPT_OPT_MESH_BVH is 1: no host tree is needed, triangles hit at exactly the
+                                      same distance are then ranked by index instead of by the reference's leaf slot. */
 };
 
 /* wavefront stages, in launch order inside one bounce */

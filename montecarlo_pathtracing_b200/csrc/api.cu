@@ -332,7 +332,7 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
             c->opt_passes_per_batch = value;
             return MCPT_OK;
         case MCPT_OPT_SMEM_STAGING:
-            c->opt_smem_staging = value ? 1 : 0;
+            c->opt_smem_staging = std::min(std::max(value, 0), 2);
             if (c->have_scene) return fail(c, MCPT_E_INVALID, "set MCPT_OPT_SMEM_STAGING before mcpt_upload_scene");
             return MCPT_OK;
         case MCPT_OPT_FAST_MATH: c->opt_fast_math = value ? 1 : 0; return MCPT_OK;

@@ -434,8 +434,16 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
         if (build_ws_bytes && (rc = dev_alloc(c, build_allocs, &build_ws, build_ws_bytes * kSide))) return rc;
     }
     // one world-space tree over the top level and every mesh instance (traverse.cuh, UWalk)?
-    const bool unified = c->opt_unified && c->opt_mesh_bvh && c->opt_persistent && !c->opt_trace_walker && d->n_meshes > 0 &&
-                         kMeshLeafTris == 1 && flat.empty();
+    // ... also for large trees of analytic primitives (more than kUnifiedMinLeaves leaves): the four-children walk with
+    // its lean lane state and a refill at 12 idle lanes beats the two-children walk that waits for the whole warp there
+    // (repo scenes 3 / 7 / 8, 410 / 491 / 895 primitives: 4175 -> 4320, 1777 -> 2047, 606 -> 691 Msamples/s), while small
+    // trees lose (122 primitives: scene 5 6662 -> 5730, divergence stress 3626 -> 3363) and keep the two-children walk
+    constexpr size_t kUnifiedMinLeaves = 256;
+    size_t top_leaves = 0;
+    for (const DevNode4& N : top4)
+        for (int j = 0; j < 4; ++j) top_leaves += ((&N.tok.x)[j] < 0 && (&N.tok.x)[j] != INT_MIN) ? 1 : 0;
+    const bool unified = c->opt_unified && c->opt_mesh_bvh && c->opt_persistent && !c->opt_trace_walker &&
+                         (d->n_meshes > 0 || top_leaves > kUnifiedMinLeaves) && kMeshLeafTris == 1 && flat.empty() && d->n_prims > 0;
     // ---- plan of the unified world-space tree: [top-level four-children nodes | subtree of instance 0 | instance 1 | ...]
     struct Inst {
         int prim, mesh, node_base, leaf_base;
@@ -443,7 +451,7 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     std::vector<Inst> inst;
     DevNode4* d_unodes = nullptr;
     DevTri* d_utris = nullptr;
-    int u_n_tris = 0;
+    int u_n_tris = 0, n_top_compact = 0;
     float u_pad_rel = 0.0f, u_pad_abs = 0.0f, u_radius = 0.0f;
     if (unified) {
         std::vector<int> inst_of_prim(d->n_prims, -1);
@@ -462,7 +470,38 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
         u_n_tris = int(n_tris_total);
         // leaf tokens of the top-level tree: a mesh instance becomes a link to the root of its subtree, an analytic
         // primitive moves behind the triangle slots
-        std::vector<DevNode4> utop = top4;
+        // ... stored in breadth-first order without the unused entries of top4, so that "the first N nodes" are the
+        // top levels (what the traversal kernel stages in shared memory)
+        std::vector<DevNode4> utop;
+        {
+            std::vector<int> order{0}, new_id(top4.size(), -1);
+            new_id[0] = 0;
+            for (size_t hd = 0; hd < order.size(); ++hd) {
+                const DevNode4& N = top4[order[hd]];
+                for (int j = 0; j < 4; ++j) {
+                    const int tok = (&N.tok.x)[j];
+                    if (tok >= 0 && new_id[tok] < 0) {
+                        new_id[tok] = int(order.size());
+                        order.push_back(tok);
+                    }
+                }
+            }
+            utop.resize(order.size());
+            for (size_t k = 0; k < order.size(); ++k) {
+                utop[k] = top4[order[k]];
+                for (int j = 0; j < 4; ++j) {
+                    int& tok = (&utop[k].tok.x)[j];
+                    if (tok >= 0) tok = new_id[tok];
+                }
+            }
+        }
+        n_top_compact = int(utop.size());
+        // the instances' subtrees follow the compacted top part
+        {
+            const int shift = int(top4.size()) - n_top_compact;
+            for (Inst& in : inst) in.node_base -= shift;
+            n_nodes -= size_t(shift);
+        }
         for (DevNode4& N : utop)
             for (int j = 0; j < 4; ++j) {
                 int& tok = (&N.tok.x)[j];
@@ -666,11 +705,20 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
             S.smem_mesh_nodes = off;
         }
     }
+    S.u_smem_nodes = 0;
+    if (unified && c->opt_smem_staging >= 2) {
+        // MCPT_OPT_SMEM_STAGING = 2: also the top levels of the unified tree, what fits 32 KB next to the primitive records
+        // (4 CTAs per SM stay resident). Off by default -- measured with 0 / 64 / 256 staged nodes (Msamples/s): repo scene 8
+        // 686 / 661 / 644, scene 7 2046 / 2005 / 2031, scene 3 4344 / 4275 / 4341, 1 M triangles 1587 / 1563 / 1558: the top
+        // levels already live in L1, and the walk pays a branch per node for the second address space.
+        S.u_smem_nodes = std::min(n_top_compact, 256);
+    }
     if (!flat.empty()) {
         S.smem_top_nodes = 8 * int(flat.size()) - 1;  // the flat list, once per ray octant (stage_scene), takes the tree's place ...
         S.smem_prims = d->n_prims;                // ... and so do all (<= 16) primitive records
     }
-    S.smem_bytes = int(sizeof(DevNode)) * (S.smem_top_nodes + 1 + S.smem_mesh_nodes) + int(sizeof(DevPrim)) * S.smem_prims;
+    S.smem_bytes = int(sizeof(DevNode)) * (S.smem_top_nodes + 1 + S.smem_mesh_nodes) + int(sizeof(DevPrim)) * S.smem_prims +
+                   int(sizeof(DevNode4)) * S.u_smem_nodes;
 
     DevNode* d_top = nullptr;
     DevPrim* d_prims = nullptr;
@@ -705,7 +753,7 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.n_prims = d->n_prims;
     S.n_meshes = d->n_meshes;
     S.persistent = persistent ? 1 : 0;
-    S.refill_lanes = c->opt_refill_lanes > 0 ? c->opt_refill_lanes : (d->n_meshes > 0 ? 8 : 32);
+    S.refill_lanes = c->opt_refill_lanes > 0 ? c->opt_refill_lanes : (d->n_meshes > 0 ? 8 : (unified ? 12 : 32));
     // camera rays: the 32 rays of a warp are neighbours in the image and finish together; they are replaced together
     // (the unified walk on the 1 M-triangle workload: 8 / 16 / 24 / 32 idle lanes -> 1548 / 1564 / 1571 / 1578 Msamples/s)
     S.refill_first = (c->opt_refill_lanes > 0) ? c->opt_refill_lanes : 32;

@@ -26,12 +26,13 @@ static inline int grid_for(const LaunchCfg& lc, uint64_t n, int blocks_per_sm) {
 // ------------------------------------------------------------------ staging
 // Copy the staged part of the scene (top-level nodes, primitive records, top
 // levels of every mesh tree) into dynamic shared memory. Layout:
-//   [top nodes: 1 + smem_top_nodes][mesh nodes: smem_mesh_nodes][prims: smem_prims]
+//   [top nodes: 1 + smem_top_nodes][mesh nodes: smem_mesh_nodes][prims: smem_prims][unified nodes: u_smem_nodes]
 // Index 0 of the top-node block is unused so heap indices stay 1-based.
 __device__ __forceinline__ SmemScene stage_scene(const DevScene& S, unsigned char* smem) {
     DevNode* top = reinterpret_cast<DevNode*>(smem);
     DevNode* mesh = top + (S.smem_top_nodes + 1);
     DevPrim* prims = reinterpret_cast<DevPrim*>(mesh + S.smem_mesh_nodes);
+    DevNode4* unodes = reinterpret_cast<DevNode4*>(prims + S.smem_prims);
     if (S.n_flat > 0) {
         // the flat leaf list of a small scene, once per ray octant: copy `oct` holds each box as {planes the
         // ray enters through, planes it leaves through} for directions with sign bits oct (bit 0: x < 0, bit 1:
@@ -66,11 +67,19 @@ __device__ __forceinline__ SmemScene stage_scene(const DevScene& S, unsigned cha
         const int n4 = S.smem_prims * int(sizeof(DevPrim) / sizeof(float4));
         for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);
     }
+    if (S.u_smem_nodes > 0) {
+        // the top levels of the unified tree (its top part is stored breadth-first)
+        const float4* src = reinterpret_cast<const float4*>(S.u_nodes);
+        float4* dst = reinterpret_cast<float4*>(unodes);
+        const int n4 = S.u_smem_nodes * int(sizeof(DevNode4) / sizeof(float4));
+        for (int i = threadIdx.x; i < n4; i += blockDim.x) dst[i] = __ldg(src + i);
+    }
     __syncthreads();
     SmemScene sm;
     sm.top_nodes = top;
     sm.prims = prims;
     sm.mesh_nodes = mesh;
+    sm.u_nodes = unodes;
     return sm;
 }
 
@@ -408,7 +417,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
 #ifndef MCPT_U_MIN_LANES
 #define MCPT_U_MIN_LANES 12
 #endif
-template <bool COUNT>
+template <bool COUNT, bool EXIT>
 __device__ __forceinline__ void traverse_unified(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
                                                  uint32_t len, const HitSink& sink, uint32_t* s_next, uint32_t* s_hits, Work& wk) {
     MCPT_WALK_STACK_DECL(st, kWalkStackWide);
@@ -446,23 +455,23 @@ __device__ __forceinline__ void traverse_unified(const DevScene& S, const SmemSc
             if (!wm) break;
             if (__popc(wm) < MCPT_U_MIN_LANES && __any_sync(0xffffffffu, has_ray && !want)) break;
             if (want && w.cur == kTokPop) uwalk_pop_one(w, st);
-            if (has_ray && !w.done && w.cur >= 0) uwalk_node<COUNT>(w, wk, S, st);
+            if (has_ray && !w.done && w.cur >= 0) uwalk_node<COUNT>(w, wk, S, sm, st);
         }
 #else
 #pragma unroll 1
         for (int r = 0; r < MCPT_U_POPS && has_ray && w.cur == kTokPop && !w.done; ++r) uwalk_pop_one(w, st);
         if (has_ray && !w.done && w.cur >= 0) {
-            uwalk_node<COUNT>(w, wk, S, st);
+            uwalk_node<COUNT>(w, wk, S, sm, st);
 #pragma unroll
             for (int r = 1; r < MCPT_U_NODE_STEPS; ++r)
-                if (w.cur >= 0) uwalk_node<COUNT>(w, wk, S, st);
+                if (w.cur >= 0) uwalk_node<COUNT>(w, wk, S, sm, st);
         }
 #endif
         if (has_ray && !w.done && w.cur < 0 && w.cur != kTokPop) uwalk_leaf<COUNT>(w, wk, S, sm);
         {  // finished rays: deliver and free the lane
             const bool fin = has_ray && w.done;
             if (__any_sync(0xffffffffu, fin)) {
-                deliver<false>(S, wf, sink, s_hits, p, fin, w.best, w.D);
+                deliver<EXIT>(S, wf, sink, s_hits, p, fin, w.best, w.D);
                 if (fin) has_ray = false;
             }
         }
@@ -517,7 +526,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
 }
 
 // the unified walk as a kernel of its own (queue protocol and epilogue of k_traverse)
-template <bool COUNT, int MINB>
+template <bool COUNT, int MINB, bool EXIT>
 __global__ void __launch_bounds__(kBlock, MINB) k_traverse_unified(DevScene S, Wavefront wf, QueueIn qin, HitSink sink,
                                                                     unsigned long long* ray_counter, unsigned long long* work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -530,7 +539,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse_unified(DevScene S, W
     if (threadIdx.x == 0) s_hits = s_next = 0u;
     SmemScene sm = stage_scene(S, smem_raw);  // ends with a barrier
     Work wk;
-    traverse_unified<COUNT>(S, sm, wf, qin, len, sink, &s_next, &s_hits, wk);
+    traverse_unified<COUNT, EXIT>(S, sm, wf, qin, len, sink, &s_next, &s_hits, wk);
     if (ray_counter && threadIdx.x == 0) {
         unsigned long long rays = len;
         if (!qin.items) {
@@ -580,8 +589,13 @@ void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const
         sink.refract_ind = exit_prm->refract_ind;
     }
     if (S.u_nodes && S.persistent) {
-#define MCPT_TRAVERSE_U(COUNT, MINB) \
-    k_traverse_unified<COUNT, MINB><<<lc.grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink, ray_counter, work)
+#define MCPT_TRAVERSE_U(COUNT, MINB)                                                                                              \
+    do {                                                                                                                          \
+        if (sink.exit_mode)                                                                                                       \
+            k_traverse_unified<COUNT, MINB, true><<<lc.grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink, ray_counter, work);  \
+        else                                                                                                                      \
+            k_traverse_unified<COUNT, MINB, false><<<lc.grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink, ray_counter, work); \
+    } while (0)
         if (work) MCPT_TRAVERSE_U(true, 2);
         else if (lc.traverse_occ >= 6) MCPT_TRAVERSE_U(false, 6);
         else if (lc.traverse_occ == 5) MCPT_TRAVERSE_U(false, 5);

@@ -135,6 +135,8 @@ struct DevScene {
     // |fwd * inv - 1| * (|O| + distance). Every box of the unified tree is therefore padded PER RAY by
     // u_pad_rel * (|O|_1 + u_radius) + u_pad_abs (both bounds computed at upload from the matrices themselves).
     float u_pad_rel, u_pad_abs, u_radius;
+    int32_t u_smem_nodes;      // the first N nodes of u_nodes are staged in shared memory (the top part is stored in
+                               // breadth-first order, so these are the top levels of the tree); 0: none
     // shared-memory staging plan (in units of DevNode / DevPrim)
     int32_t smem_top_nodes;    // first N top-level nodes staged
     int32_t smem_prims;        // first N primitive records staged

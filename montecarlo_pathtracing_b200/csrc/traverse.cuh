@@ -42,6 +42,7 @@ struct SmemScene {
     const DevNode* top_nodes;   // staged top-level nodes, index 1-based like global
     const DevPrim* prims;       // staged primitive records
     const DevNode* mesh_nodes;  // staged per-mesh top levels, concatenated
+    const DevNode4* u_nodes;    // staged top levels of the unified tree (DevScene::u_smem_nodes of them)
 };
 
 MCPT_DEV DevNode load_node(const DevNode* p) {
@@ -694,12 +695,22 @@ MCPT_DEV float slab_entry_u(float nx, float ny, float nz, float fx, float fy, fl
 }
 
 template <bool COUNT>
-MCPT_DEV void uwalk_node(UWalk& w, Work& wk, const DevScene& S, const WalkStack& st) {
-    const float4* q = reinterpret_cast<const float4*>(S.u_nodes + w.cur);
-    const float4 nxp = __ldg(q + w.nx), fxp = __ldg(q + (w.nx ^ 1u));
-    const float4 nyp = __ldg(q + w.ny), fyp = __ldg(q + (w.ny ^ 1u));
-    const float4 nzp = __ldg(q + w.nz), fzp = __ldg(q + (w.nz ^ 1u));
-    const int4 tok = __ldg(reinterpret_cast<const int4*>(q + 6));
+MCPT_DEV void uwalk_node(UWalk& w, Work& wk, const DevScene& S, const SmemScene& sm, const WalkStack& st) {
+    float4 nxp, fxp, nyp, fyp, nzp, fzp;
+    int4 tok;
+    if (w.cur < S.u_smem_nodes) {  // the top levels: shared memory
+        const float4* q = reinterpret_cast<const float4*>(sm.u_nodes + w.cur);
+        nxp = q[w.nx], fxp = q[w.nx ^ 1u];
+        nyp = q[w.ny], fyp = q[w.ny ^ 1u];
+        nzp = q[w.nz], fzp = q[w.nz ^ 1u];
+        tok = *reinterpret_cast<const int4*>(q + 6);
+    } else {
+        const float4* q = reinterpret_cast<const float4*>(S.u_nodes + w.cur);
+        nxp = __ldg(q + w.nx), fxp = __ldg(q + (w.nx ^ 1u));
+        nyp = __ldg(q + w.ny), fyp = __ldg(q + (w.ny ^ 1u));
+        nzp = __ldg(q + w.nz), fzp = __ldg(q + (w.nz ^ 1u));
+        tok = __ldg(reinterpret_cast<const int4*>(q + 6));
+    }
     int c0 = tok.x, c1 = tok.y, c2 = tok.z, c3 = tok.w;
     float t0 = slab_entry_u(nxp.x, nyp.x, nzp.x, fxp.x, fyp.x, fzp.x, c0, w);
     float t1 = slab_entry_u(nxp.y, nyp.y, nzp.y, fxp.y, fyp.y, fzp.y, c1, w);
