@@ -213,6 +213,14 @@ int mcpt_trace_rays(mcpt_ctx* ctx, int64_t n, const float* o, const float* d,
 int mcpt_trace_rays_device(mcpt_ctx* ctx, int64_t n, const float* o4, const float* d4,
                            mcpt_hit* out_dev, int any_hit);
 
+/* The bounce sampler on its own: n consecutive random_ray(D, roughness) draws (tp/montecarlo.frag:49-89) of the RNG
+ * stream srand() seeds from screen_tc = (tcx, tcy), numero_pass and date (shaders/raytracer_func.frag:105-110), written
+ * to out_host as float[3*n]. This is what the reference's DrawSampling program draws (tp/hsphere.vert:1-41: the same
+ * two functions, one point per draw, the picture of the roughness cone in README.md:5-14); here it feeds the sampler
+ * parity test and montecarlo_pathtracing_b200.imageio.sampling_plot. Transcendentals as MCPT_OPT_FAST_MATH says. */
+int mcpt_sample_directions(mcpt_ctx* ctx, const float D[3], float roughness, float tcx, float tcy, int numero_pass,
+                           float date, int64_t n, float* out_host);
+
 /* The same closest-hit search as mcpt_trace_rays_device for callers that cannot allocate device memory (code under
  * CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc). NO COUNTERPART IN THE REFERENCE.
  * The ray / hit sectors the traversal kernel works in live in a fixed block

@@ -75,7 +75,7 @@ MCPT_SYMBOLS = [
     "mcpt_synchronize", "mcpt_set_option", "mcpt_upload_scene", "mcpt_resize", "mcpt_set_camera", "mcpt_set_params",
     "mcpt_clear", "mcpt_render", "mcpt_resolve", "mcpt_get_accum", "mcpt_bind_accum", "mcpt_read_accum",
     "mcpt_write_accum", "mcpt_reduce_nccl", "mcpt_trace_rays", "mcpt_trace_rays_device", "mcpt_get_stats",
-    "mcpt_reset_stats", "mcpt_get_stage_times", "mcpt_inspect_walk_tree", "mcpt_trace_rays_static",
+    "mcpt_reset_stats", "mcpt_get_stage_times", "mcpt_inspect_walk_tree", "mcpt_trace_rays_static", "mcpt_sample_directions",
 ]
 # every symbol include/mcpt_host.h declares
 MCPTH_SYMBOLS = [
@@ -127,6 +127,7 @@ def lib():
         L.mcpt_trace_rays.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mcpt_trace_rays_device.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int]
         L.mcpt_trace_rays_static.argtypes = [C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p]
+        L.mcpt_sample_directions.argtypes = [C.c_void_p, C.c_void_p, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float, C.c_int64, C.c_void_p]
         L.mcpt_get_stats.argtypes = [C.c_void_p, C.POINTER(Stats)]
         L.mcpt_reset_stats.argtypes = [C.c_void_p]
         L.mcpt_get_stage_times.argtypes = [C.c_void_p, C.POINTER(StageTimes)]

@@ -414,6 +414,25 @@ int mcpt_trace_rays(mcpt_ctx* c, int64_t n, const float* o, const float* d, mcpt
     return MCPT_OK;
 }
 
+int mcpt_sample_directions(mcpt_ctx* c, const float D[3], float roughness, float tcx, float tcy, int numero_pass, float date,
+                           int64_t n, float* out_host) {
+    if (!c || !D || n < 0 || (n > 0 && !out_host)) return MCPT_E_INVALID;
+    if (n == 0) return MCPT_OK;
+    if (n > (int64_t(1) << 30)) return fail(c, MCPT_E_INVALID, "too many draws: the RNG state advances modulo 2^32");
+    CK(c, cudaSetDevice(c->device));
+    float* dev = nullptr;
+    cudaError_t e = cudaMalloc(&dev, size_t(n) * 3 * sizeof(float));
+    if (e != cudaSuccess) return fail(c, MCPT_E_NOMEM, "sample buffer: %s", cudaGetErrorString(e));
+    launch_sample_dirs(lcfg(c), D, roughness, tcx, tcy, numero_pass, date, n, dev, c->opt_fast_math != 0);
+    e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpyAsync(out_host, dev, size_t(n) * 3 * sizeof(float), cudaMemcpyDeviceToHost, c->stream);
+    const cudaError_t e2 = cudaStreamSynchronize(c->stream);
+    cudaFree(dev);
+    if (e == cudaSuccess) e = e2;
+    if (e != cudaSuccess) return fail(c, MCPT_E_CUDA, "sample_directions: %s", cudaGetErrorString(e));
+    return MCPT_OK;
+}
+
 int mcpt_get_stats(mcpt_ctx* c, mcpt_stats* out) {
     if (!c || !out) return MCPT_E_INVALID;
     CK(c, cudaSetDevice(c->device));

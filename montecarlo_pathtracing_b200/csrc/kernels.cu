@@ -5,6 +5,7 @@
 // the SM count, so a bounce never needs a host round trip to size its launches.
 #include <cfloat>
 #include <cstdio>
+#include <cstring>
 
 #include "kernels.cuh"
 #include "mcpt.h"

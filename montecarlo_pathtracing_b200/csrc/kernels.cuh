@@ -61,4 +61,8 @@ void launch_trace(const LaunchCfg& lc, const DevScene& S, int64_t n, const float
 void launch_trace_wavefront(const LaunchCfg& lq, const DevScene& S, int64_t n, const float4* o, const float4* d, Wavefront wf,
                             uint32_t cap, void* hits_out);
 
+// n consecutive random_ray(D, roughness) draws of the RNG stream seeded by srand(screen_tc = (tcx, tcy), numero_pass, date)
+void launch_sample_dirs(const LaunchCfg& lc, const float D[3], float roughness, float tcx, float tcy, int numero_pass, float date,
+                        int64_t n, float* out_dev, bool fast_math);
+
 }  // namespace mcpt

@@ -243,3 +243,36 @@ void launch_resolve(const LaunchCfg& lc, const float4* accum, int w, int h, floa
                                                                  rgba8 ? static_cast<uchar4*>(dst) : nullptr);
     lc.count();
 }
+
+// ---- the bounce sampler on its own (mcpt_sample_directions)
+// n consecutive random_ray(D, roughness) draws of ONE RNG stream -- what tp/hsphere.vert:1-41 (DrawSampling, the
+// reference's picture of the sampling cone) and the sampler fixtures draw sequentially: draw i starts from the state
+// after 2 i random_float() calls, which is seed0 + 2 i (11, 43, 67), so the draws are independent threads here.
+template <bool FAST>
+__global__ void __launch_bounds__(kBlock) k_sample_dirs(float3 D, float roughness, uint3 seed0, int64_t n, float* __restrict__ out) {
+    for (int64_t i = int64_t(blockIdx.x) * blockDim.x + threadIdx.x; i < n; i += int64_t(gridDim.x) * blockDim.x) {
+        const uint32_t k = 2u * uint32_t(i);
+        uint3 s = make_uint3(seed0.x + 11u * k, seed0.y + 43u * k, seed0.z + 67u * k);
+        const f3 r = random_ray<FAST>(mk3(D.x, D.y, D.z), roughness, s);
+        out[3 * i] = r.x;
+        out[3 * i + 1] = r.y;
+        out[3 * i + 2] = r.z;
+    }
+}
+
+void launch_sample_dirs(const LaunchCfg& lc, const float D[3], float roughness, float tcx, float tcy, int numero_pass, float date,
+                        int64_t n, float* out_dev, bool fast_math) {
+    // srand() on the host: the same float products as rng_seed (raytracer_func.frag:105-110)
+    const float k = float(1 + numero_pass);
+    const float wx = tcx * k * 1.125f, wy = (float(numero_pass) * 3.14f + date) * k * 1.125f, wz = tcy * k * 1.125f;
+    uint3 seed0;
+    std::memcpy(&seed0.x, &wx, 4);
+    std::memcpy(&seed0.y, &wy, 4);
+    std::memcpy(&seed0.z, &wz, 4);
+    const float3 d3 = make_float3(D[0], D[1], D[2]);
+    if (fast_math)
+        k_sample_dirs<true><<<grid_for(lc, uint64_t(n), 8), kBlock, 0, lc.stream>>>(d3, roughness, seed0, n, out_dev);
+    else
+        k_sample_dirs<false><<<grid_for(lc, uint64_t(n), 8), kBlock, 0, lc.stream>>>(d3, roughness, seed0, n, out_dev);
+    lc.count();
+}

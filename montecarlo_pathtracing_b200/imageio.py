@@ -143,3 +143,53 @@ def convergence_curve(ctx, ref: np.ndarray, spp_marks, first_pass: int = 0) -> l
         row["spp"] = done
         out.append(row)
     return out
+
+
+# ---- the sampling cone (the reference's DrawSampling artefact, README.md:5-14, tp/hsphere.vert:1-41)
+def cone_stats(dirs: np.ndarray, D) -> dict:
+    """Statistics of sampled directions around the axis D: the angle to D (degrees) at the median / 90 % / 99 % / max,
+    the mean cosine, and the share of samples below the tangent plane (none for a hemisphere sampler)."""
+    d = np.asarray(dirs, np.float64).reshape(-1, 3)
+    a = np.asarray(D, np.float64).reshape(3)
+    a = a / np.linalg.norm(a)
+    cosv = np.clip(d @ a / np.maximum(np.linalg.norm(d, axis=1), 1e-30), -1.0, 1.0)
+    ang = np.degrees(np.arccos(cosv))
+    return {"n": int(len(d)), "mean_cos": float(cosv.mean()), "angle_p50": float(np.percentile(ang, 50)),
+            "angle_p90": float(np.percentile(ang, 90)), "angle_p99": float(np.percentile(ang, 99)), "angle_max": float(ang.max()),
+            "below_plane": float((cosv < 0).mean())}
+
+
+def cone_histogram(dirs: np.ndarray, D, bins: int = 18):
+    """Histogram of the angle to D over [0, 90] degrees: (bin edges, share of the samples per bin)."""
+    d = np.asarray(dirs, np.float64).reshape(-1, 3)
+    a = np.asarray(D, np.float64).reshape(3)
+    a = a / np.linalg.norm(a)
+    ang = np.degrees(np.arccos(np.clip(d @ a / np.maximum(np.linalg.norm(d, axis=1), 1e-30), -1.0, 1.0)))
+    h, edges = np.histogram(ang, bins=bins, range=(0.0, 90.0))
+    return edges, h / max(len(d), 1)
+
+
+def sampling_plot(dirs: np.ndarray, D, size: int = 256) -> np.ndarray:
+    """The DrawSampling picture, headless: the sampled unit directions seen from a point on the axis D, i.e. projected
+    on the plane perpendicular to D (the unit circle is the horizon of the hemisphere). Returns a (size, size, 3) uint8
+    image -- log-scaled point density in white on black, the horizon as a grey circle -- for write_png(bottom_up=False)."""
+    d = np.asarray(dirs, np.float64).reshape(-1, 3)
+    a = np.asarray(D, np.float64).reshape(3)
+    a = a / np.linalg.norm(a)
+    w = np.array([a[0], a[1] + 5.0, a[2] + 3.0])          # the frame random_ray builds (tp/montecarlo.frag:72-89)
+    w /= np.linalg.norm(w)
+    u = np.cross(a, w)
+    u /= np.linalg.norm(u)
+    v = np.cross(a, u)
+    x, y = d @ u, d @ v
+    ix = np.clip(((x * 0.48 + 0.5) * size).astype(int), 0, size - 1)
+    iy = np.clip(((y * 0.48 + 0.5) * size).astype(int), 0, size - 1)
+    dens = np.zeros((size, size), np.float64)
+    np.add.at(dens, (iy, ix), 1.0)
+    img = np.log1p(dens) / max(np.log1p(dens.max()), 1e-9)
+    out = np.repeat((img * 255).astype(np.uint8)[..., None], 3, axis=2)
+    t = np.linspace(0, 2 * np.pi, 4 * size)
+    cx = np.clip(((np.cos(t) * 0.48 + 0.5) * size).astype(int), 0, size - 1)
+    cy = np.clip(((np.sin(t) * 0.48 + 0.5) * size).astype(int), 0, size - 1)
+    out[cy, cx] = np.maximum(out[cy, cx], 96)
+    return out

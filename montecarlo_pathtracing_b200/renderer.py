@@ -261,6 +261,14 @@ class Context:
         """mcpt_trace_rays_static: device buffers in and out, fixed scratch inside the library, no allocation."""
         self._ck(self._L.mcpt_trace_rays_static(self._c, n, C.c_void_p(o4_ptr), C.c_void_p(d4_ptr), C.c_void_p(out_ptr)))
 
+    def sample_directions(self, D, roughness, n, tcx=0.3, tcy=0.7, numero_pass=0, date=0.25) -> np.ndarray:
+        """mcpt_sample_directions: (n, 3) consecutive random_ray(D, roughness) draws of one RNG stream."""
+        d = capi._f32(D).reshape(3)
+        out = np.zeros((int(n), 3), np.float32)
+        self._ck(self._L.mcpt_sample_directions(self._c, d.ctypes.data, float(roughness), float(tcx), float(tcy), int(numero_pass),
+                                                float(date), int(n), out.ctypes.data))
+        return out
+
     def stats(self) -> dict:
         s = Stats()
         self._ck(self._L.mcpt_get_stats(self._c, C.byref(s)))
