@@ -253,6 +253,70 @@ def run_reference(args, result_out):
     result_out.flush()
 
 
+def quick_measure(name, local, rank, world, steps, warmup, strong=False, fast_math=1):
+    """A second workload measured inside the default run, so that the other BASELINE configs are in the driver's own
+    record next to the headline one: same timing rules (warm-up, barrier + synchronize, CUDA events on the launching
+    stream, max over ranks, clocks sampled over the region), library defaults for every option, no host tree for meshes.
+    Returns the sub-record (rank 0) or None."""
+    import torch
+    import torch.distributed as dist
+    from montecarlo_pathtracing_b200 import Context, capi
+    from montecarlo_pathtracing_b200.distributed import pass_range, reduce_accum
+    s, raw, (w, h, spp, bounces, ior, desc) = build_scene(name)
+    iv, ipv = capi.default_camera(w, h)
+    ctx = Context(local)
+    stream = torch.cuda.current_stream()
+    ctx.set_stream(stream.cuda_stream)
+    ctx.set_option(capi.OPT_FAST_MATH, fast_math)
+    ctx.upload_scene(s.desc(mesh_trees=False) if s.nb_meshes else s.desc())
+    ctx.resize(w, h)
+    accum = torch.zeros(h * w * 4, dtype=torch.float32, device="cuda")
+    ctx.bind_accum(accum.data_ptr(), accum.numel() * 4)
+    ctx.set_camera(iv, ipv)
+    ctx.set_params(nb_bounces=bounces, refract_ind=ior, date=DATE)
+    spp_total = strong_spp(name) if strong else spp * world
+    first, count = pass_range(rank, world, spp_total)
+
+    def step():
+        accum.zero_()
+        ctx.render(first, count)
+        reduce_accum(accum, root=0)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(warmup):
+        step()
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    ev0.record(stream)
+    for _ in range(steps):
+        step()
+    ev1.record(stream)
+    barrier()
+    clocks = sampler.stop() if rank == 0 else None
+    ms = ev0.elapsed_time(ev1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    st = ctx.stats()
+    ctx.close()
+    del accum
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    return {"workload": desc, "value": w * h * spp_total * steps / (ms * 1e-3) / 1e6, "unit": "Msamples/s", "ms_per_step": ms / steps,
+            "steps": steps, "warmup": warmup, "n_gpus": world, "scaling": "strong" if strong else "weak", "spp_per_step_total": spp_total,
+            "gpu_launches": int(st["launches"]), "clocks": clocks}
+
+
 def claim_stdout():
     """Keep stdout for the ONE JSON line: everything else a library writes to fd 1 (NCCL prints its version
     banner there) goes to stderr. Returns the file to print the result line to."""
@@ -284,6 +348,7 @@ def main():
     ap.add_argument("--unified", type=int, default=1, help="scenes with meshes: 1 = one world-space tree over the top level and every mesh instance, 0 = two-level walk")
     ap.add_argument("--host-tree", type=int, default=0, help="mesh workloads: 1 = upload the reference's median-split mesh trees too (tie-break ranks = its leaf slots), 0 = no host tree at all")
     ap.add_argument("--occ", type=int, default=0, help="traversal kernel register cap: CTAs per SM (0 = library default)")
+    ap.add_argument("--other-configs", type=int, default=1, help="default workload only: 1 = also measure BASELINE configs 1, 3, 5 (N = 1) and the strong split of config 4 (every N) in short runs and report them under `other_configs`")
     ap.add_argument("--sustain-s", type=float, default=2.0, help="after the timed steps, keep stepping for this long and report the throughput and clocks of that region too (0 = off)")
     args = ap.parse_args()
     if args.impl == "reference":
@@ -419,9 +484,12 @@ def main():
     ctx.stage_times()
     n_prof = min(args.steps, 10)
     red_ev = []
+    tiny = torch.zeros(1, device="cuda")
     for _ in range(n_prof):
         accum.zero_()
         ctx.render(first, count)
+        if world > 1:
+            dist.all_reduce(tiny)        # device-side rendezvous: the reduce below is timed without the ranks' skew
         a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         a.record(stream)
         reduce_step()
@@ -491,6 +559,22 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         e2e_s = float(t.item())
     e2e_val = paths_per_step * n_e2e / e2e_s / 1e6
+
+    accum_bytes = int(accum.numel() * 4)
+    # ---- the other BASELINE configs, in short runs of the same kind (only next to the default headline workload)
+    other = None
+    if args.other_configs and args.workload == "c2" and args.scaling == "weak":
+        other = {}
+        ctx.close()                      # free the headline context's wavefront buffers first
+        accum = None
+        torch.cuda.empty_cache()
+        torch.cuda.set_stream(stream)
+        if world == 1:
+            other["c1"] = quick_measure("c1", local, rank, world, 50, 5, fast_math=args.fast_math)
+            other["c3_16spp"] = quick_measure("mesh", local, rank, world, 10, 3, fast_math=args.fast_math)
+            other["c5_64spp"] = quick_measure("c5", local, rank, world, 10, 3, fast_math=args.fast_math)
+        # BASELINE config 4 as written: 3840x2160, a FIXED 1024 spp split over the N ranks, one reduce, rank 0 holds the sum
+        other["c4_strong"] = quick_measure("c4", local, rank, world, 1 if world == 1 else 2, 1, strong=True, fast_math=args.fast_math)
 
     if rank != 0:
         if world > 1:
@@ -606,8 +690,8 @@ def main():
         "e2e": {"value": e2e_val, "unit": "Msamples/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
                 "steps": n_e2e, "upload_ms": upload_ms, "first_image_ms": first_image_ms,
                 "host_buffers": f"scene tables page-locked with cudaHostRegister ({len(pinned)} arrays), image in pinned memory"},
-        "reduce": {"ms": reduce_ms, "bytes": int(accum.numel() * 4), "through": args.reduce} if world > 1 else None,
-        "sustained": sustained,
+        "reduce": {"ms": reduce_ms, "bytes": accum_bytes, "through": args.reduce} if world > 1 else None,
+        "sustained": sustained, "other_configs": other,
         "roofline": roofline, "cpu_baseline": cpu, "clocks": clocks,
     }
     result_out.write(json.dumps(out) + "\n")

@@ -113,65 +113,100 @@ bool slice_loose_primitive(const DevPrim& P, const DevNode& full, int prim, std:
     return true;
 }
 
-// items[begin, end) -> token of the subtree (>= 0: node index, < 0: ~primitive). Full-sweep SAH on the three
-// axes (items sorted by box centre); below `depth_left` levels of head room the split is the median of the
-// longest axis, which bounds the depth (the walk's stack holds one entry per level).
-int build_top_sah_rec(std::vector<TopItem>& it, int begin, int end, int depth_left, std::vector<DevNode2>& nodes) {
-    const int n = end - begin;
-    if (n == 1) return ~it[begin].prim;
-    const int idx = int(nodes.size());
-    nodes.push_back(DevNode2{});
-    int best_axis = -1, best_split = begin + n / 2;
-    int balanced_levels = 0;
-    while ((1 << balanced_levels) < n) ++balanced_levels;
-    auto by_axis = [&](int ax) {
-        std::stable_sort(it.begin() + begin, it.begin() + end, [ax](const TopItem& a, const TopItem& b) {
-            return a.lo[ax] + a.hi[ax] < b.lo[ax] + b.hi[ax];
-        });
-    };
-    if (depth_left > balanced_levels) {
-        double best = 1e300;
-        std::vector<double> right(n + 1, 0.0);
+// Full-sweep SAH over the items' boxes, one item per leaf. The items are sorted ONCE per axis by box centre (ties in
+// item order); a node owns the same range [begin, end) of the three orders, sweeps each for the cheapest split
+// (cost = area(left) * n_left + area(right) * n_right, first axis and first position win ties), and hands its
+// children their sub-ranges by a stable partition of the other two orders: O(n log n) in all (the first version
+// re-sorted every node's range four times: 11 ms for the 3163 leaves of repo scene 8, 0.9 ms now). Below `depth_left`
+// levels of head room the split is the median of the longest axis, which bounds the depth (the walk's stack holds one
+// entry per level).
+struct TopSahBuilder {
+    const std::vector<TopItem>& it;
+    std::vector<DevNode2>& nodes;
+    std::vector<int> ord[3], tmp;
+    std::vector<char> side;
+    std::vector<double> right;
+
+    TopSahBuilder(const std::vector<TopItem>& items, std::vector<DevNode2>& out) : it(items), nodes(out) {
+        const int n = int(it.size());
         for (int ax = 0; ax < 3; ++ax) {
-            by_axis(ax);
-            float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-            for (int i = n - 1; i >= 1; --i) {
-                for (int k = 0; k < 3; ++k) {
-                    lo[k] = std::min(lo[k], it[begin + i].lo[k]);
-                    hi[k] = std::max(hi[k], it[begin + i].hi[k]);
+            ord[ax].resize(n);
+            for (int i = 0; i < n; ++i) ord[ax][i] = i;
+            std::stable_sort(ord[ax].begin(), ord[ax].end(), [&](int a, int b) { return it[a].lo[ax] + it[a].hi[ax] < it[b].lo[ax] + it[b].hi[ax]; });
+        }
+        tmp.resize(n);
+        side.assign(n, 0);
+        right.assign(n + 1, 0.0);
+    }
+
+    DevNode box_of_range(int ax, int begin, int end) const {
+        DevNode b = empty_node();
+        for (int i = begin; i < end; ++i) {
+            const TopItem& t = it[ord[ax][i]];
+            b.lo.x = std::min(b.lo.x, t.lo[0]); b.lo.y = std::min(b.lo.y, t.lo[1]); b.lo.z = std::min(b.lo.z, t.lo[2]);
+            b.hi.x = std::max(b.hi.x, t.hi[0]); b.hi.y = std::max(b.hi.y, t.hi[1]); b.hi.z = std::max(b.hi.z, t.hi[2]);
+        }
+        return b;
+    }
+
+    int build(int begin, int end, int depth_left) {
+        const int n = end - begin;
+        if (n == 1) return ~it[ord[0][begin]].prim;
+        const int idx = int(nodes.size());
+        nodes.push_back(DevNode2{});
+        int best_axis = -1, best_split = begin + n / 2;
+        int balanced_levels = 0;
+        while ((1 << balanced_levels) < n) ++balanced_levels;
+        if (depth_left > balanced_levels) {
+            double best = 1e300;
+            for (int ax = 0; ax < 3; ++ax) {
+                const int* o = ord[ax].data() + begin;
+                float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+                for (int i = n - 1; i >= 1; --i) {
+                    for (int k = 0; k < 3; ++k) {
+                        lo[k] = std::min(lo[k], it[o[i]].lo[k]);
+                        hi[k] = std::max(hi[k], it[o[i]].hi[k]);
+                    }
+                    right[i] = half_area(lo, hi);
                 }
-                right[i] = half_area(lo, hi);
-            }
-            float llo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, lhi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
-            for (int i = 1; i < n; ++i) {
-                for (int k = 0; k < 3; ++k) {
-                    llo[k] = std::min(llo[k], it[begin + i - 1].lo[k]);
-                    lhi[k] = std::max(lhi[k], it[begin + i - 1].hi[k]);
-                }
-                const double cost = half_area(llo, lhi) * i + right[i] * (n - i);
-                if (cost < best) {
-                    best = cost;
-                    best_axis = ax;
-                    best_split = begin + i;
+                float llo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, lhi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+                for (int i = 1; i < n; ++i) {
+                    for (int k = 0; k < 3; ++k) {
+                        llo[k] = std::min(llo[k], it[o[i - 1]].lo[k]);
+                        lhi[k] = std::max(lhi[k], it[o[i - 1]].hi[k]);
+                    }
+                    const double cost = half_area(llo, lhi) * i + right[i] * (n - i);
+                    if (cost < best) {
+                        best = cost;
+                        best_axis = ax;
+                        best_split = begin + i;
+                    }
                 }
             }
         }
+        if (best_axis < 0) {  // no head room left (or degenerate boxes): median of the longest axis
+            const DevNode b = box_of_range(0, begin, end);
+            const float ex = b.hi.x - b.lo.x, ey = b.hi.y - b.lo.y, ez = b.hi.z - b.lo.z;
+            best_axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
+            best_split = begin + n / 2;
+        }
+        for (int i = begin; i < end; ++i) side[ord[best_axis][i]] = (i < best_split) ? 0 : 1;
+        for (int ax = 0; ax < 3; ++ax) {
+            if (ax == best_axis) continue;
+            int l = begin, r = best_split;
+            for (int i = begin; i < end; ++i) tmp[(side[ord[ax][i]] ? r : l)++] = ord[ax][i];
+            std::copy(tmp.begin() + begin, tmp.begin() + end, ord[ax].begin() + begin);
+        }
+        const DevNode b0 = box_of_range(0, begin, best_split), b1 = box_of_range(0, best_split, end);
+        const int t0 = build(begin, best_split, depth_left - 1);
+        const int t1 = build(best_split, end, depth_left - 1);
+        DevNode2 N{};
+        set_child2(N, 0, b0, t0);
+        set_child2(N, 1, b1, t1);
+        nodes[idx] = N;
+        return idx;
     }
-    if (best_axis < 0) {  // no head room left (or degenerate boxes): median of the longest axis
-        const DevNode b = box_of(it, begin, end);
-        const float ex = b.hi.x - b.lo.x, ey = b.hi.y - b.lo.y, ez = b.hi.z - b.lo.z;
-        best_axis = (ex >= ey && ex >= ez) ? 0 : (ey >= ez ? 1 : 2);
-        best_split = begin + n / 2;
-    }
-    by_axis(best_axis);
-    const int t0 = build_top_sah_rec(it, begin, best_split, depth_left - 1, nodes);
-    const int t1 = build_top_sah_rec(it, best_split, end, depth_left - 1, nodes);
-    DevNode2 N{};
-    set_child2(N, 0, box_of(it, begin, best_split), t0);
-    set_child2(N, 1, box_of(it, best_split, end), t1);
-    nodes[idx] = N;
-    return idx;
-}
+};
 
 void build_top_sah(std::vector<TopItem>& items, std::vector<DevNode2>& nodes) {
     nodes.clear();
@@ -183,7 +218,8 @@ void build_top_sah(std::vector<TopItem>& items, std::vector<DevNode2>& nodes) {
         return;
     }
     nodes.reserve(items.size());
-    build_top_sah_rec(items, 0, int(items.size()), 30, nodes);  // <= 30 levels: one stack entry per level (kWalkStack)
+    TopSahBuilder b(items, nodes);
+    b.build(0, int(items.size()), 30);  // <= 30 levels: one stack entry per level (kWalkStack)
 }
 
 // fold every second level of a two-children tree (root = node 0) into four-children nodes
@@ -815,7 +851,11 @@ static int inspect_walk_tree_impl(const mcpt_scene_desc* d, int top_sah, mcpt_tr
     }
     std::vector<DevNode2> top2;
     std::vector<DevNode4> top4;
+    const auto t_build = std::chrono::steady_clock::now();
     build_walk_trees(d, prims, top, top_sah != 0, top2, top4);
+    if (std::getenv("MCPT_DUMP_UPLOAD"))
+        std::fprintf(stderr, "walk trees of %d primitives built on the host in %.3f ms\n", d->n_prims,
+                     std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_build).count());
     out->nodes = int(top2.size());
     for (int i = 0; i < d->n_prims; ++i) out->prims_expected += prims[i].slot >= 0 ? 1 : 0;
 

@@ -52,3 +52,22 @@ def test_golden_converged_image_writes_a_png(tmp_path):
     back = imageio.read_png(p)
     h, w, _ = cv["image"].shape
     assert back.shape == (h, w, 3) and back.max() > 100
+
+
+def test_cone_statistics_and_sampling_plot_of_the_oracle_sampler(tmp_path):
+    """The DrawSampling artefact on the CPU side (tp/hsphere.vert:1-41, README.md:5-14): the cone narrows with the
+    roughness; statistics, histogram and plot come out of imageio without a GPU."""
+    from oracle.binding import Oracle
+    D = np.float32([0.0, 0.6, 0.8])
+    med = {}
+    for rough in (1.0, 0.5, 0.1):
+        d = Oracle().random_rays(D, rough, n=20_000)
+        s = imageio.cone_stats(d, D)
+        med[rough] = s["angle_p50"]
+        assert s["below_plane"] == 0.0 and abs(np.linalg.norm(d, axis=1) - 1).max() < 1e-5
+        edges, h = imageio.cone_histogram(d, D, bins=18)
+        assert len(edges) == 19 and abs(h.sum() - 1.0) < 1e-9
+        img = imageio.sampling_plot(d, D, size=128)
+        assert img.shape == (128, 128, 3) and img.max() == 255
+        assert imageio.read_png(imageio.write_png(tmp_path / "s.png", img, bottom_up=False)).shape[:2] == (128, 128)
+    assert 35 < med[1.0] < 45 and 10 < med[0.5] < 13.5 and 0.3 < med[0.1] < 0.7

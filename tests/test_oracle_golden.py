@@ -180,3 +180,34 @@ def test_scene8_waiver_is_the_noise_floor_of_the_transcendentals():
     assert drift[1, 9] <= 0.002 and drift[6, 9] <= 0.002
     assert drift[8, 2] <= 0.002
     assert 0.01 <= drift[8, 9] <= 0.10
+
+
+@pytest.mark.parametrize("name", ["c2", "c5", "scene3"])
+def test_bench_reference_arm_builds_the_same_scene_by_itself(name):
+    """bench.py --impl reference builds repo scenes (and the two configs derived from them) with the reference's own
+    scene builders, BVH builder and camera; the tables must equal the host mirror's that the GPU arm uploads
+    (records bit for bit except the inverse transform, which every stand-in for Eigen's inverse rounds differently)."""
+    from oracle.binding import have_reference
+    if not have_reference():
+        pytest.skip("oracle/_ref/libref.so not built")
+    import bench
+    from common import host_scene
+    from montecarlo_pathtracing_b200 import capi
+    kind = bench.WORKLOADS[name][0]
+    o, iv, ipv, how = bench.reference_scene(name)
+    assert o.cpu_kind == "reference" and "own code" in how
+    s = host_scene(kind, 0.4)
+    s.finalize()
+    a, b = o.prim_data(), s.prim_data()
+    assert a.shape == b.shape
+    keep = np.r_[0:16, 32:64]
+    assert np.array_equal(a[:, keep].view(np.uint32), b[:, keep].view(np.uint32))
+    assert np.abs(a[:, 16:32] - b[:, 16:32]).max() <= 1e-4
+    w, h = bench.WORKLOADS[name][2:4]
+    hv, hpv = capi.default_camera(w, h)
+    # (the camera matrices are inverses too: equal to the rounding of the two inverse routines)
+    assert np.allclose(np.float32(iv), np.float32(hv).ravel(), rtol=1e-5, atol=1e-5)
+    assert np.allclose(np.float32(ipv), np.float32(hpv).ravel(), rtol=1e-5, atol=1e-5)
+    t = s.tables()["root"]
+    rb = o.bvh()
+    assert int(rb["depth"]) == int(t["depth"]) and np.array_equal(rb["ind"], t["ind"])
