@@ -107,7 +107,7 @@ enum {
                                       mcpt_render with whatever walker the scene selected (default), 1 = the
                                       one-ray-per-lane walk over the uploaded trees in the reference's visit order.
                                       any_hit always takes the latter. Same records. */
-    MCPT_OPT_UNIFIED = 12          /* scenes with meshes, and trees of more than 256 leaves: 1 = one world-space tree of
+    MCPT_OPT_UNIFIED = 12,         /* scenes with meshes, and trees of more than 256 leaves: 1 = one world-space tree of
                                       four-children nodes over the top level and every mesh instance (instance subtrees
                                       built on the GPU at upload), walked in a single frame (default; needs
                                       MCPT_OPT_MESH_BVH and MCPT_OPT_PERSISTENT), 0 = two-level walk (top-level tree,
@@ -115,6 +115,14 @@ enum {
                                       records. mcpt_mesh_desc.bvh may be empty (bb == ind == NULL) whenever
                                       MCPT_OPT_MESH_BVH is 1: no host tree is needed, triangles hit at exactly the
                                       same distance are then ranked by index instead of by the reference's leaf slot. */
+    MCPT_OPT_NEE = 13              /* 1 = next-event estimation: every vertex whose next ray is drawn from a cone also
+                                      samples one point on one emissive quad (the emissive-first records with
+                                      emissivity > 0.5, picked by mat_info.a) and delivers the light's contribution
+                                      through a shadow ray, balance-weighted against the bounce ray. A NEW estimator
+                                      (the reference's light sampler is commented out, raytracer_func.frag:908-956):
+                                      same expectation per pixel -- it converges to the same image -- with less
+                                      noise at equal spp where lights are small; the bounce rays are unchanged.
+                                      Default 0 (the reference's estimator, bit-level parity). */
 };
 
 /* wavefront stages, in launch order inside one bounce */

@@ -71,7 +71,9 @@ struct mcpt_ctx {
     std::vector<std::pair<size_t, void*>> alloc_cache;     // parked blocks (size, pointer)
     uint64_t wf_capacity = 0;  // path slots
     uint32_t batch_gen = 0;    // generation of the last batch traced in these buffers (path tags)
-    uint32_t* queue[3] = {nullptr, nullptr, nullptr};
+    uint32_t* queue[4] = {nullptr, nullptr, nullptr, nullptr};  // next / hit / interior / shadow (MCPT_OPT_NEE)
+    Wavefront nee{};           // next-event estimation: shadow ray, its hit record, sums (three sectors per slot)
+    uint64_t nee_capacity = 0;
     uint32_t* counters = nullptr;  // per-CTA region lengths of the three queues
     int counters_len = 0;
     unsigned long long* dev_stats = nullptr;  // [0] rays, [1] segments, [2] boxes, [3] records, [4] triangles
@@ -89,6 +91,7 @@ struct mcpt_ctx {
     int opt_traverse_occ = 0;  // 0 = auto
     int opt_count_work = 0;
     int opt_trace_walker = 0;  // mcpt_trace_rays: 0 = the production kernel (k_traverse), 1 = the reference-order walk (k_trace)
+    int opt_nee = 0;           // next-event estimation on the emissive quads (a new estimator, off by default)
     int opt_unified = 1;       // scenes with meshes: one world-space tree (traverse.cuh, UWalk) instead of the two-level walk
 
     // stage profiling: (stage, start, stop) triples waiting to be read, plus a free list
@@ -345,6 +348,7 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
         case MCPT_OPT_TOP_SAH: c->opt_top_sah = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TRACE_WALKER: c->opt_trace_walker = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_UNIFIED: c->opt_unified = value ? 1 : 0; return MCPT_OK;
+        case MCPT_OPT_NEE: c->opt_nee = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_TRAVERSE_OCC:
             if (value != 0 && (value < 2 || value > 6))
                 return fail(c, MCPT_E_INVALID, "traverse occupancy must be 0 (auto) or 2..6 CTAs per SM");

@@ -26,6 +26,7 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
         CK(c, cudaStreamSynchronize(c->stream));
         free_all(c, c->wf_allocs);
         c->wf_capacity = 0;
+        c->nee_capacity = 0;
         c->counters = nullptr;
         c->counters_len = 0;
         Wavefront& w = c->wf;
@@ -48,7 +49,19 @@ int ensure_wavefront(mcpt_ctx* c, uint64_t slots, int bounces) {
         trim_cache(c);
     }
     (void)bounces;
-    const int need = 3 * wavefront_grid_max(c);  // region lengths of the three queues
+    if (c->opt_nee && c->nee_capacity < c->wf_capacity) {
+        // next-event estimation: three more sectors per slot and the shadow queue (allocated on first use)
+        CK(c, cudaStreamSynchronize(c->stream));
+        char* rec = nullptr;
+        int rc;
+        if ((rc = dev_alloc(c, c->wf_allocs, &rec, size_t(c->wf_capacity) * 96)) ||
+            (rc = dev_alloc(c, c->wf_allocs, &c->queue[3], queue_entries(c, c->wf_capacity))))
+            return rc;
+        c->nee.rec = rec;
+        c->nee.plane = size_t(c->wf_capacity) * 32;
+        c->nee_capacity = c->wf_capacity;
+    }
+    const int need = 4 * wavefront_grid_max(c);  // region lengths of the four queues
     if (need > c->counters_len) {
         int rc = dev_alloc(c, c->wf_allocs, &c->counters, size_t(need));
         if (rc) return rc;
@@ -212,6 +225,10 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
         const QueueIn in_identity{nullptr, nullptr, slots, cap}, in_next{q_next.items, q_next.counts, 0, cap},
             in_hit{q_hit.items, q_hit.counts, 0, cap}, in_int{q_int.items, q_int.counts, 0, cap};
         const bool mc = (c->prm.mode == 0);
+        const bool nee = mc && c->opt_nee && S.n_lights > 0;
+        const QueueOut q_shadow{c->queue[3], c->counters + 3 * gmax, cap};
+        const QueueIn in_shadow{q_shadow.items, q_shadow.counts, 0, cap};
+        if (nee) CK(c, cudaMemsetAsync(c->nee.rec + 2 * c->nee.plane, 0, size_t(slots) * 32, c->stream));  // sums and densities of this batch
         for (int it = 0; it < iters; ++it) {
             const bool last = (it == iters - 1);
             const QueueIn& cur = (it == 0) ? in_identity : in_next;
@@ -221,10 +238,21 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
             }
             {
                 StageSpan sp(c, MCPT_STAGE_SHADE);
-                launch_shade(lq, S, c->prm, c->wf, mc ? in_hit : cur, q_next, q_int, it == 0, last, first_pass + b0, npix,
-                             c->opt_fast_math != 0, c->dev_stats + 1);
+                if (nee)
+                    launch_shade_nee(lq, S, c->prm, c->wf, c->nee, in_hit, q_next, q_int, q_shadow, it == 0, last, first_pass + b0, npix,
+                                     c->opt_fast_math != 0, c->dev_stats + 1);
+                else
+                    launch_shade(lq, S, c->prm, c->wf, mc ? in_hit : cur, q_next, q_int, it == 0, last, first_pass + b0, npix,
+                                 c->opt_fast_math != 0, c->dev_stats + 1);
             }
             if (last) break;
+            if (nee) {
+                // the shadow rays of this bounce: the production traversal kernel over their own ray / hit sectors
+                // (every record is delivered, as for the debug shaders), then the visible light samples are delivered
+                StageSpan sp(c, MCPT_STAGE_TRAVERSE_INTERIOR);
+                launch_traverse(lq, S, c->nee, in_shadow, q_none, nullptr, c->dev_stats + 0, work);
+                launch_nee_resolve(lq, c->nee, in_shadow);
+            }
             // interior rays: traced and turned into their exit rays by the same kernel, except in scenes
             // with meshes (measured: +4 % at C2, +7 % on the divergence-stress scene, but -5 % on the mesh
             // workload, where the exit's normal fetches stall the persistent warps)
@@ -240,7 +268,10 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
         }
         {
             StageSpan sp(c, MCPT_STAGE_ACCUMULATE);
-            launch_accumulate(lc, c->wf, c->accum, npix, nb, c->prm.batch);
+            if (nee)
+                launch_accumulate_nee(lc, c->wf, c->nee, c->accum, npix, nb, c->prm.batch);
+            else
+                launch_accumulate(lc, c->wf, c->accum, npix, nb, c->prm.batch);
         }
         c->paths_started += slots;
     }

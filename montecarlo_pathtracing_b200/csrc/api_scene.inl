@@ -756,6 +756,44 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.smem_bytes = int(sizeof(DevNode)) * (S.smem_top_nodes + 1 + S.smem_mesh_nodes) + int(sizeof(DevPrim)) * S.smem_prims +
                    int(sizeof(DevNode4)) * S.u_smem_nodes;
 
+    // ---- lights of next-event estimation: emissive quads (emissivity > 0.5: the ones that END a path) among the
+    // emissive-first records, picked with probability proportional to the reference's area figure mat_info.a
+    std::vector<DevLight> lights;
+    {
+        double wsum = 0.0;
+        const int n_emi = std::min(std::max(d->nb_emissives, 0), d->n_prims);
+        for (int i = 0; i < n_emi && lights.size() < 256; ++i) {
+            const DevPrim& P = prims[i];
+            if (P.type != MCPT_PRIM_ORIENTED_QUAD || !(mat[i].z > 0.5f) || P.slot < 0) continue;
+            const float ex[3] = {P.fwd.r0.x, P.fwd.r1.x, P.fwd.r2.x}, ey[3] = {P.fwd.r0.y, P.fwd.r1.y, P.fwd.r2.y};
+            const float nx = ex[1] * ey[2] - ex[2] * ey[1], ny = ex[2] * ey[0] - ex[0] * ey[2], nz = ex[0] * ey[1] - ex[1] * ey[0];
+            const float nl = std::sqrt(nx * nx + ny * ny + nz * nz);
+            if (!(nl > 1e-20f) || !std::isfinite(nl)) continue;
+            const float area = 4.0f * nl;                       // the unit quad spans [-1, 1]^2
+            const float w = mat[i].w > 0.0f ? mat[i].w : area;  // mat_info.a
+            DevLight L;
+            L.c = make_float4(P.fwd.r0.w, P.fwd.r1.w, P.fwd.r2.w, 1.0f / area);
+            L.ex = make_float4(ex[0], ex[1], ex[2], w);
+            L.ey = make_float4(ey[0], ey[1], ey[2], 0.0f);
+            L.n = make_float4(nx / nl, ny / nl, nz / nl, 0.0f);
+            std::memcpy(&L.n.w, &i, sizeof(int));
+            L.emit = make_float4(0.1f * color[i].x, 0.1f * color[i].y, 0.1f * color[i].z, mat[i].z * (1.0f - mat[i].x) * color[i].w);
+            lights.push_back(L);
+            wsum += w;
+        }
+        double cum = 0.0;
+        for (DevLight& L : lights) {
+            L.ex.w = float(L.ex.w / wsum);
+            cum += L.ex.w;
+            L.ey.w = float(cum);
+        }
+        if (!lights.empty()) lights.back().ey.w = 1.0f;
+    }
+    DevLight* d_lights = nullptr;
+    if ((rc = upload_vec(c, lights, &d_lights))) return rc;
+    S.lights = lights.empty() ? nullptr : d_lights;
+    S.n_lights = int(lights.size());
+
     DevNode* d_top = nullptr;
     DevPrim* d_prims = nullptr;
     float4 *d_color = nullptr, *d_mat = nullptr;

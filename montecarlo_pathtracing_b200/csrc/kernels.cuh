@@ -49,6 +49,13 @@ void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const
 void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin,
                   const QueueOut& next, const QueueOut& interior, bool first_bounce, bool last_bounce, int first_pass,
                   uint32_t npix, bool fast_math, unsigned long long* seg_counter);
+// next-event estimation (MCPT_OPT_NEE): `nee` holds three sectors per path slot (shadow ray, its hit record, sums);
+// shade_nee also appends the slots with a shadow ray to `shadow`; nee_resolve delivers the visible ones
+void launch_shade_nee(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, Wavefront nee, const QueueIn& qin,
+                      const QueueOut& next, const QueueOut& interior, const QueueOut& shadow, bool first_bounce, bool last_bounce,
+                      int first_pass, uint32_t npix, bool fast_math, unsigned long long* seg_counter);
+void launch_nee_resolve(const LaunchCfg& lc, Wavefront nee, const QueueIn& qin);
+void launch_accumulate_nee(const LaunchCfg& lc, Wavefront wf, Wavefront nee, float4* accum, uint32_t npix, int n_passes, uint32_t batch);
 void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin);
 void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes, uint32_t batch);
 void launch_resolve(const LaunchCfg& lc, const float4* accum, int w, int h, float divisor, int subsampling, void* dst,

@@ -136,6 +136,227 @@ void launch_shade(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, 
     lc.count();
 }
 
+// ---------------------------------------------------- next-event estimation (MCPT_OPT_NEE)
+// A NEW estimator on top of the reference's random_path (which has none: its light sampler is commented out,
+// shaders/raytracer_func.frag:908-956; the data it would use -- emissive records first, mat_info.a -- is what
+// DevLight is built from). In random_path a path only DELIVERS its `total` when it ends: on an emissive surface
+// (emissivity > 0.5), or in the sky. The event "the next ray hits light L" is here also estimated directly: at every
+// vertex whose continuation ray is drawn from a cone (diffuse and reflective cases), one point y on one light quad is
+// sampled, and (total + what the hit on L would add along that direction) is delivered at once if y is visible, weighted
+// against the continuation ray by the balance heuristic of the two densities (the cone's, cone_pdf, and the light
+// sampler's converted to solid angle); a continuation ray that does hit a sampled light delivers its value with the
+// complementary weight. The expectation of every pixel is unchanged; the bounce rays themselves are the SAME rays as
+// without NEE (the light sampler draws from a stream of its own), only the bookkeeping differs.
+// Extra state per path slot, three 32-byte sectors (`nee`): 0 shadow ray, 1 its hit record (written by the traversal
+// kernel), 2 {delivered sum.xyz, density of the continuation ray | pending contribution.xyz, expected primitive}.
+MCPT_DEV int find_light(const DevScene& S, int prim) {
+    for (int i = 0; i < S.n_lights; ++i)
+        if (__float_as_int(__ldg(&S.lights[i].n).w) == prim) return i;
+    return -1;
+}
+
+template <bool FAST>
+__global__ void __launch_bounds__(kBlock, 3) k_shade_nee(DevScene S, DevParams prm, Wavefront wf, Wavefront nee, QueueIn qin, QueueOut next,
+                                                         QueueOut interior, QueueOut shadow, int first_bounce, int last_bounce,
+                                                         int first_pass, uint32_t npix, unsigned long long* seg_counter) {
+    __shared__ uint32_t s_count[3];
+    const uint32_t len = queue_len(qin);
+    if (len == 0) {
+        if (threadIdx.x == 0) {
+            if (next.items) next.counts[blockIdx.x] = interior.counts[blockIdx.x] = 0u;
+            shadow.counts[blockIdx.x] = 0u;
+        }
+        return;
+    }
+    if (threadIdx.x < 3) s_count[threadIdx.x] = 0u;
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u;
+    const float tag_alive = __uint_as_float(2u * prm.batch), tag_ended = __uint_as_float(2u * prm.batch + 1u);
+    unsigned int my_segments = 0;
+    for (uint32_t base = 0; base < len; base += kBlock) {
+        uint32_t kind = 0, p;
+        bool shadow_job = false;
+        if (queue_item(qin, base + threadIdx.x, len, p)) {
+            f3 pl, D;
+            int2 hb;
+            wf.load_hit(p, pl, hb.x, hb.y, D);
+            float4 o4, d4;
+            wf.load_ray(p, o4, d4);
+            const f3 O = mk3(o4.x, o4.y, o4.z);
+            f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
+            uint32_t n_draws = 0u;
+            if (!first_bounce) {
+                float4 a4, t4;
+                wf.load_rad(p, a4, t4);
+                total = mk3(t4.x, t4.y, t4.z);
+                attenu = mk3(a4.x, a4.y, a4.z);
+                n_draws = __float_as_uint(t4.w);
+            }
+            PathSector ns = *nee.sec(p, 2);   // zeroed at the start of the batch
+            const float p_prev = first_bounce ? 0.0f : ns.a.w;
+            ++my_segments;
+            const uint3 seed0 = path_seed(p, npix, prm.width, prm.height, first_pass, prm.date, n_draws);
+            uint3 seed = seed0;
+            f3 N = mk3(0, 0, 0), P = mk3(0, 0, 0);
+            intersection_info(S, hb.x, hb.y, pl, prm.flat_face, N, P);
+            const float4 mat = __ldg(S.mat + hb.x);
+            const float4 col = __ldg(S.color + hb.x);
+            NeeInfo ni;
+            BounceOut bo = bounce<FAST>(O, D, N, P, mat, col, attenu, total, seed, prm.refract_ind, &ni);
+            if (bo.kind == 0) {
+                // the path ends on an emissive surface. If that surface is a sampled light and the ray came from a cone
+                // that next-event estimation also covered, the value carries the continuation ray's share of the weight
+                float w_b = 1.0f;
+                if (p_prev > 0.0f) {
+                    const int li = find_light(S, hb.x);
+                    if (li >= 0) {
+                        const DevLight L = S.lights[li];
+                        const f3 w = P - O;
+                        const float d2 = dot3(w, w);
+                        const float cy = fabsf(dot3(mk3(L.n.x, L.n.y, L.n.z), w)) * rsqrtf(fmaxf(d2, 1e-30f));
+                        const float p_l = L.ex.w * L.c.w * d2 / fmaxf(cy, 1e-8f);
+                        w_b = p_prev / (p_prev + p_l);
+                    }
+                }
+                wf.store_rad(p, make_float4(0.0f, 0.0f, 0.0f, tag_ended), make_float4(total.x * w_b, total.y * w_b, total.z * w_b, 0.0f));
+            } else if (last_bounce) {
+                wf.store_rad(p, make_float4(0.0f, 0.0f, 0.0f, tag_ended), make_float4(0.0f, 0.0f, 0.0f, 0.0f));
+            } else {
+                const uint32_t nd = n_draws + draws_between(seed0, seed);
+                wf.store_ray(p, make_float4(bo.nO.x, bo.nO.y, bo.nO.z, 0.0f), make_float4(bo.nD.x, bo.nD.y, bo.nD.z, __uint_as_float(nd)));
+                wf.store_rad(p, make_float4(bo.new_att.x, bo.new_att.y, bo.new_att.z, tag_alive),
+                             make_float4(total.x, total.y, total.z, __uint_as_float(nd)));
+                if (bo.kind == 2) wf.store_keep(p, make_float4(N.x, N.y, N.z, 0.0f), make_float4(P.x, P.y, P.z, 0.0f));
+                kind = uint32_t(bo.kind);
+                float p_next = 0.0f;
+                if (ni.cone != 0 && S.n_lights > 0 && ni.rho * ni.rho > 1e-3f) {
+                    p_next = cone_pdf(dot3(ni.axis, Tm<FAST>::normalize_(bo.nD)), ni.rho);
+                    // the light sampler's own random numbers: the bounce rays must not depend on MCPT_OPT_NEE
+                    uint3 ls = make_uint3(seed0.x ^ 0x9E3779B9u, seed0.y ^ 0x85EBCA6Bu, seed0.z ^ 0xC2B2AE35u);
+                    const float r0 = random_float(ls), r1 = random_float(ls), r2 = random_float(ls);
+                    int li = 0;
+                    while (li + 1 < S.n_lights && r0 >= __ldg(&S.lights[li].ey).w) ++li;
+                    const DevLight L = S.lights[li];
+                    const f3 y = mk3(L.c.x, L.c.y, L.c.z) + mk3(L.ex.x, L.ex.y, L.ex.z) * (2.0f * r1 - 1.0f) + mk3(L.ey.x, L.ey.y, L.ey.z) * (2.0f * r2 - 1.0f);
+                    const f3 w = y - bo.nO;
+                    const float d2 = dot3(w, w);
+                    if (d2 > 1e-12f) {
+                        const f3 wn = w * rsqrtf(d2);
+                        const float cy = fabsf(dot3(mk3(L.n.x, L.n.y, L.n.z), wn));
+                        const float pc = cone_pdf(dot3(ni.axis, wn), ni.rho);
+                        if (pc > 0.0f && cy > 1e-6f) {
+                            const float p_l = L.ex.w * L.c.w * d2 / cy;
+                            float spec = 1.0f;
+                            if (ni.cone == 1) spec = Tm<FAST>::pow_(fmaxf(0.0f, dot3(ni.E, reflect3(-wn, ni.N))), ni.se);
+                            const f3 att = ni.base + ni.gain * spec;
+                            const f3 value = total + mk3(L.emit.x, L.emit.y, L.emit.z) + att * L.emit.w;
+                            const float wgt = pc / (pc + p_l);
+                            ns.b = make_float4(value.x * wgt, value.y * wgt, value.z * wgt, L.n.w);
+                            nee.store_ray(p, make_float4(bo.nO.x, bo.nO.y, bo.nO.z, 0.0f), make_float4(wn.x, wn.y, wn.z, 0.0f));
+                            shadow_job = true;
+                        }
+                    }
+                }
+                ns.a.w = p_next;
+                *nee.sec(p, 2) = ns;
+            }
+        }
+        if (next.items) {
+            warp_append(&s_count[0], next, kind != 0u, p);
+            warp_append(&s_count[1], interior, kind == 2u, p);
+        }
+        warp_append(&s_count[2], shadow, shadow_job, p);
+    }
+    if (seg_counter) {
+        for (int off = 16; off > 0; off >>= 1) my_segments += __shfl_down_sync(0xffffffffu, my_segments, off);
+        if (lane == 0 && my_segments) atomicAdd(seg_counter, (unsigned long long)my_segments);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        if (next.items) {
+            next.counts[blockIdx.x] = s_count[0];
+            interior.counts[blockIdx.x] = s_count[1];
+        }
+        shadow.counts[blockIdx.x] = s_count[2];
+    }
+}
+
+// after the shadow rays were traced: a sampled light point is visible when the closest hit along the shadow ray is
+// that light; its pending contribution is then delivered
+__global__ void __launch_bounds__(kBlock) k_nee_resolve(Wavefront nee, QueueIn qin) {
+    const uint32_t len = queue_len(qin);
+    for (uint32_t i = threadIdx.x; i < len; i += kBlock) {
+        uint32_t p;
+        if (!queue_item(qin, i, len, p)) continue;
+        f3 pl, D;
+        int prim, sub;
+        nee.load_hit(p, pl, prim, sub, D);
+        PathSector ns = *nee.sec(p, 2);
+        if (prim >= 0 && prim == __float_as_int(ns.b.w)) {
+            ns.a.x += ns.b.x;
+            ns.a.y += ns.b.y;
+            ns.a.z += ns.b.z;
+            *nee.sec(p, 2) = ns;
+        }
+    }
+}
+
+// k_accumulate with the delivered next-event sums added per path
+__global__ void __launch_bounds__(kBlock) k_accumulate_nee(Wavefront wf, Wavefront nee, float4* __restrict__ accum, uint32_t npix, int n_passes,
+                                                            uint32_t batch) {
+    for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
+        float4 a = accum[pix];
+        for (int k = 0; k < n_passes; ++k) {
+            const uint64_t p = uint64_t(k) * npix + pix;
+            float4 a4, t4;
+            wf.load_rad(p, a4, t4);
+            const uint32_t tag = __float_as_uint(a4.w);
+            f3 r;
+            if (tag == 2u * batch + 1u) {
+                r = mk3(t4.x, t4.y, t4.z);
+            } else {
+                f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
+                if (tag == 2u * batch) {
+                    total = mk3(t4.x, t4.y, t4.z);
+                    attenu = mk3(a4.x, a4.y, a4.z);
+                }
+                const float4 d4 = wf.load_ray_d(p);
+                r = sky(total, attenu, mk3(d4.x, d4.y, d4.z));
+            }
+            const float4 s4 = nee.sec(p, 2)->a;
+            a.x += r.x + s4.x;
+            a.y += r.y + s4.y;
+            a.z += r.z + s4.z;
+        }
+        accum[pix] = a;
+    }
+}
+
+void launch_shade_nee(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, Wavefront nee, const QueueIn& qin,
+                      const QueueOut& next, const QueueOut& interior, const QueueOut& shadow, bool first_bounce, bool last_bounce,
+                      int first_pass, uint32_t npix, bool fast_math, unsigned long long* seg_counter) {
+    const QueueOut none{nullptr, nullptr, 0};
+    const QueueOut& nx = last_bounce ? none : next;
+    const QueueOut& in = last_bounce ? none : interior;
+    if (fast_math)
+        k_shade_nee<true><<<lc.grid, kBlock, 0, lc.stream>>>(S, prm, wf, nee, qin, nx, in, shadow, first_bounce ? 1 : 0, last_bounce ? 1 : 0,
+                                                             first_pass, npix, seg_counter);
+    else
+        k_shade_nee<false><<<lc.grid, kBlock, 0, lc.stream>>>(S, prm, wf, nee, qin, nx, in, shadow, first_bounce ? 1 : 0, last_bounce ? 1 : 0,
+                                                              first_pass, npix, seg_counter);
+    lc.count();
+}
+
+void launch_nee_resolve(const LaunchCfg& lc, Wavefront nee, const QueueIn& qin) {
+    k_nee_resolve<<<lc.grid, kBlock, 0, lc.stream>>>(nee, qin);
+    lc.count();
+}
+
+void launch_accumulate_nee(const LaunchCfg& lc, Wavefront wf, Wavefront nee, float4* accum, uint32_t npix, int n_passes, uint32_t batch) {
+    k_accumulate_nee<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(wf, nee, accum, npix, n_passes, batch);
+    lc.count();
+}
+
 // --------------------------------------------------------------- shade_exit
 // Scenes with meshes only (elsewhere the interior traversal does this itself, deliver() in kernels.cu:
 // inside the persistent mesh walk the smooth-normal fetches of a few finished lanes would hold the warp).

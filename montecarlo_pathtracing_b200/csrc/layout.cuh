@@ -105,6 +105,17 @@ struct DevMesh {
     int64_t pad2;
 };
 
+// One light of next-event estimation (MCPT_OPT_NEE): an emissive oriented quad among the first nb_emissives records
+// (the reference sorts emissive primitives first, bvh_gpu/scene.cpp:70-88, and stores an area figure in mat_info.a,
+// bvh_gpu/scene.h:128-172, for a light sampler it never finished, shaders/raytracer_func.frag:908-956).
+struct DevLight {
+    float4 c;      // centre (world), w = 1 / true area of the quad
+    float4 ex;     // half edge along local x (world), w = selection probability of this light
+    float4 ey;     // half edge along local y (world), w = cumulative selection probability up to and including it
+    float4 n;      // unit normal (world), w = primitive id (int bits)
+    float4 emit;   // colour * 0.1 (what a hit adds to `total` besides the emission), w = emissivity * (1 - shininess) * alpha
+};
+
 struct DevScene {
     const DevNode* top_nodes;  // 2^(depth+1) - 1 nodes, heap order
     const DevPrim* prims;
@@ -135,6 +146,8 @@ struct DevScene {
     // |fwd * inv - 1| * (|O| + distance). Every box of the unified tree is therefore padded PER RAY by
     // u_pad_rel * (|O|_1 + u_radius) + u_pad_abs (both bounds computed at upload from the matrices themselves).
     float u_pad_rel, u_pad_abs, u_radius;
+    const DevLight* lights;    // next-event estimation: the quads that are sampled directly (null: none)
+    int32_t n_lights;
     int32_t u_smem_nodes;      // the first N nodes of u_nodes are staged in shared memory (the top part is stored in
                                // breadth-first order, so these are the top levels of the tree); 0: none
     // shared-memory staging plan (in units of DevNode / DevPrim)

@@ -192,9 +192,30 @@ struct BounceOut {
     f3 nO, nD, new_att;
 };
 
+// What next-event estimation needs to know about the ray a bounce continues with (MCPT_OPT_NEE): the cone it was drawn
+// from -- random_ray(axis, rho) -- and the attenuation the path would carry along ANY direction w of that cone:
+// new_att(w) = base + gain * spec(w), spec(w) = pow(max(0, dot(E, reflect(-w, N))), se) in the diffuse case (the
+// shader's `spec` is a function of the sampled ray there), spec = 1 in the reflective case (gain already holds it).
+struct NeeInfo {
+    int cone;  // 0: no cone (interior ray, path end), 1: diffuse case, 2: reflective case
+    f3 axis, E, N, base, gain;
+    float rho, se;
+};
+
+// solid-angle density of random_ray(axis, rho) at a unit direction whose cosine to the axis is c (0 behind the
+// axis plane): sample_hemisphere draws tan^2(theta) = -a^2 ln(1 - u), a = rho^2, and a uniform azimuth
+MCPT_DEV float cone_pdf(float c, float rho) {
+    const float a2 = rho * rho * rho * rho;
+    if (!(c > 1e-6f) || !(a2 > 1e-12f)) return 0.0f;
+    const float c2 = c * c, t2 = (1.0f - c2) / c2;
+    return __expf(-t2 / a2) / (MCPT_PI * a2 * c2 * c);
+}
+
 template <bool FAST>
-MCPT_DEV BounceOut bounce(f3 O, f3 D, f3 N, f3 P, float4 mat, float4 col, f3 attenu, f3& total, uint3& seed, float refract_ind) {
+MCPT_DEV BounceOut bounce(f3 O, f3 D, f3 N, f3 P, float4 mat, float4 col, f3 attenu, f3& total, uint3& seed, float refract_ind,
+                          NeeInfo* ni = nullptr) {
     BounceOut out;
+    if (ni) ni->cone = 0;
     f3 c3 = mk3(col.x, col.y, col.z);
     f3 ray = random_ray<FAST>(N, 1.0f - mat.y, seed);
     float rs = r_schlick(D, N, refract_ind);
@@ -235,6 +256,16 @@ MCPT_DEV BounceOut bounce(f3 O, f3 D, f3 N, f3 P, float4 mat, float4 col, f3 att
         out.nO = P + N * MCPT_BIAS;
         out.nD = random_ray<FAST>(reflect3(D, N), 1.0f - mat.x * mat.y, seed);
         out.kind = 1;
+        if (ni) {
+            ni->cone = 2;
+            ni->axis = Tm<FAST>::normalize_(reflect3(D, N));
+            ni->rho = 1.0f - mat.x * mat.y;
+            ni->base = out.new_att;
+            ni->gain = mk3(0.0f, 0.0f, 0.0f);
+            ni->E = E;
+            ni->N = N;
+            ni->se = se;
+        }
     } else if (interior) {
         out.new_att = c3 * attenu + attenu * (1.0f - col.w) * (1.0f - rs) * spec * mixed;
         out.nO = P - N * MCPT_BIAS;
@@ -245,6 +276,16 @@ MCPT_DEV BounceOut bounce(f3 O, f3 D, f3 N, f3 P, float4 mat, float4 col, f3 att
         out.nO = P + N * MCPT_BIAS;
         out.nD = ray;
         out.kind = 1;
+        if (ni) {
+            ni->cone = 1;
+            ni->axis = N;
+            ni->rho = 1.0f - mat.y;
+            ni->base = c3 * attenu;
+            ni->gain = attenu * mixed;
+            ni->E = E;
+            ni->N = N;
+            ni->se = se;
+        }
     }
     return out;
 }
