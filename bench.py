@@ -36,6 +36,7 @@ WORKLOADS = {
     "c2": ("c2", {}, 1920, 1080, 64, 8, 1.5, "BASELINE config 2: repo scene 6, 1920x1080, 64 spp, IOR 1.5, roughness 0.5, light 0.4, 8 bounces"),
     "c5": ("c5", {}, 1920, 1080, 64, 16, 1.5, "BASELINE config 5 (divergence stress) at 64 spp per step: all transparent+reflective, roughness 0.1, 16 bounces, 1080p"),
     "mesh": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 1920, 1080, 16, 8, 1.5, "BASELINE config 3 at 16 spp per step: 16 meshes x 65536 triangles, 1080p, 8 bounces"),
+    "c3": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 1920, 1080, 256, 8, 1.5, "BASELINE config 3: synthetic 1M-triangle scene (16 meshes x 65536 triangles), 1920x1080, 256 spp, 8 bounces"),
     # the repo's eight scenes (hot keys Q..I, MontecarloGPU/montecarlo.cpp:236-290) at the metric's settings
     **{f"scene{k}": (k, {}, 1920, 1080, 32, 8, 1.0, f"repo scene {k}, 1920x1080, 32 spp per step, light 0.4, IOR 1.0, 8 bounces")
        for k in range(1, 9)},
@@ -195,7 +196,8 @@ def workload_config(args, world):
     return {"workload": desc, "name": args.workload, "width": w, "height": h,
             "spp_per_step_per_gpu": (strong_spp(args.workload) / world) if strong else spp, "bounces": bounces, "ior": ior,
             "parallelism": (f"spp-split x{world}, one ncclReduce(sum) per step" if world > 1 else "single GPU"),
-            "l2": "wavefront state of a batch (>1 GB) exceeds the 126 MB L2; no flush needed", "fast_math": args.fast_math}
+            "l2": "wavefront state of a batch (>1 GB) exceeds the 126 MB L2; no flush needed", "fast_math": args.fast_math,
+            "host_tree": getattr(args, "host_tree", 0), "unified": getattr(args, "unified", 1)}
 
 
 def strong_spp(name):
@@ -226,7 +228,7 @@ def run_reference(args, result_out):
     # torchrun exports OMP_NUM_THREADS=1: ask for every core this process may run on explicitly
     cores = o.set_threads(len(os.sched_getaffinity(0)))
     # bounded sample per step: the full frame at 1 spp (mesh workloads: every 8th of the rows)
-    rows = h if args.workload not in ("mesh", "c4") else max(8, h // 8)
+    rows = h if args.workload not in ("mesh", "c3", "c4") else max(8, h // 8)
     y0 = (h - rows) // 2
     acc = np.zeros((h, w, 3), np.float32)
     for i in range(args.warmup):
@@ -238,15 +240,15 @@ def run_reference(args, result_out):
     paths = rows * w * args.steps
     val = paths / dt / 1e6
     sample = f"{rows} rows x {w} px x 1 spp per step (centre band of the {w}x{h} frame), {args.steps} steps"
-    cfg = workload_config(args, 1)
-    cfg["note"] = ("CPU arm: " + how + "; shader text compiled as C++ on the host cores (GLSL through a graphics API is unavailable on this box). "
-                   "Each timed step is a bounded sample of the workload -- the frame at 1 spp -- in the same unit (paths per second) "
-                   "as the GPU arm's 64-spp steps")
+    cfg = workload_config(args, args.gpus)       # the same object as the GPU arm's line
+    note = ("CPU arm: " + how + "; shader text compiled as C++ on the host cores (GLSL through a graphics API is unavailable on this box). "
+            "Each timed step is a bounded sample of the workload -- the frame at 1 spp -- in the same unit (paths per second) "
+            "as the GPU arm's 64-spp steps")
     result_out.write(json.dumps({
         "impl": "reference", "metric": "Msamples/s", "value": val, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True,
         "scaling": args.scaling, "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": cfg,
+        "config": cfg, "note": note,
         "cpu_baseline": {"value": val, "unit": "Msamples/s", "cores": cores, "kind": o.cpu_kind, "sample": sample},
         "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }) + "\n")
@@ -464,8 +466,6 @@ def main():
                      "unit": "Msamples/s", "ms_per_step": ms_sus / n_sus, "clocks": clocks2}
 
     config = workload_config(args, world)
-    config["host_tree"] = args.host_tree
-    config["unified"] = args.unified
     if args.no_extras:
         if rank == 0:
             result_out.write(json.dumps({"metric": "Msamples/s", "value": value, "unit": "Msamples/s", "n_gpus": world, "steps": args.steps,
@@ -601,7 +601,10 @@ def main():
     sm_file = ROOT / "profiles" / "r02_step_metrics.json"
     m = json.loads(sm_file.read_text()).get(args.workload) if sm_file.exists() else None
     mt = (m or {}).get("by_stage", {}).get("traverse")
-    same_launches = bool(mt) and mt["launches"] * n_prof == trav_launches
+    # the committed counters belong to the library's default option set; any tuning switch on the command line voids them
+    default_opts = (args.unified == 1 and args.persistent == 1 and args.mesh_bvh == 1 and args.top_sah == 1 and args.flat_walk == 1 and
+                    args.refill == 0 and args.occ == 0 and args.ppb == 0 and args.fast_math == 1 and not os.environ.get("MCPT_LIBRARY"))
+    same_launches = bool(mt) and default_opts and mt["launches"] * n_prof == trav_launches
     roofline = {"kernel": "k_traverse_unified" if (s.nb_meshes and args.unified and args.persistent and args.mesh_bvh) else "k_traverse",
                 "bound": "issue", "unit": "Gwarp-inst/s", "peak": issue_peak,
                 "peak_source": f"{sm_count} SMs x 4 schedulers x {clk:.0f} MHz (SM clock sampled under load)"}
@@ -664,7 +667,7 @@ def main():
         o, r_iv, r_ipv, how = reference_scene(args.workload)
         o.set_uniforms(bounces, ior, DATE, 0, r_iv, r_ipv)
         cores = o.set_threads(len(os.sched_getaffinity(0)))
-        rows = h if args.workload not in ("mesh", "c4") else max(8, h // 8)
+        rows = h if args.workload not in ("mesh", "c3", "c4") else max(8, h // 8)
         y0 = (h - rows) // 2
         acc = np.zeros((h, w, 3), np.float32)
         t0 = time.perf_counter()
