@@ -571,6 +571,7 @@ def main():
         torch.cuda.set_stream(stream)
         if world == 1:
             other["c1"] = quick_measure("c1", local, rank, world, 50, 5, fast_math=args.fast_math)
+            other["c3"] = quick_measure("c3", local, rank, world, 4, 1, fast_math=args.fast_math)          # 256 spp per step, as BASELINE states it
             other["c3_16spp"] = quick_measure("mesh", local, rank, world, 10, 3, fast_math=args.fast_math)
             other["c5_64spp"] = quick_measure("c5", local, rank, world, 10, 3, fast_math=args.fast_math)
         # BASELINE config 4 as written: 3840x2160, a FIXED 1024 spp split over the N ranks, one reduce, rank 0 holds the sum

@@ -637,6 +637,11 @@ MCPT_DEV void walk_prim(WalkState& w, Work& wk, const DevScene& S, const SmemSce
 #ifndef MCPT_U_TOPREG
 #define MCPT_U_TOPREG 0
 #endif
+#ifndef MCPT_U_PREFETCH
+#define MCPT_U_PREFETCH 0  // bit 0: prefetch the triangle slot of a leaf when it is reached; bit 1: the second nearest child node
+// (measured on the 1 M-triangle workload / repo scene 8, Msamples/s: off 1586 / 688, bit 0 1544 / 667, bit 1 1549 / 666, both 1529 / 655;
+// triangle slots loaded around L1, MCPT_TRI_NO_L1: 1560 / 688 -- the loads these would hide are not what the warps wait for)
+#endif
 struct UWalk {
     f3 O, D;           // world ray as given
     f3 idir, odn, odf; // culling frame: t_entry = plane * idir + odn, t_exit = plane * idir + odf
@@ -727,6 +732,19 @@ MCPT_DEV void uwalk_node(UWalk& w, Work& wk, const DevScene& S, const SmemScene&
     if (t2 < inf) upush(w, st, c2, t2);
     if (t1 < inf) upush(w, st, c1, t1);
     w.cur = (t0 < inf) ? c0 : kTokPop;
+#if MCPT_U_PREFETCH & 1
+    // the triangle of a leaf that was just reached: the lane waits for the other lanes' node steps before the leaf stage
+    // runs, the L2 -> L1 transfer of the slot overlaps them
+    if (t0 < inf && c0 < 0 && ~c0 < S.u_n_tris) {
+        const char* tp = reinterpret_cast<const char*>(S.u_tris + ~c0);
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(tp));
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(tp + 32));
+    }
+#endif
+#if MCPT_U_PREFETCH & 2
+    // the second nearest child, which is the entry most likely to be taken off the stack next
+    if (t1 < inf && c1 >= 0) asm volatile("prefetch.global.L1 [%0];" ::"l"(reinterpret_cast<const char*>(S.u_nodes + c1)));
+#endif
 }
 
 // one entry off the stack: dropped if it can no longer hold a closer hit
@@ -748,13 +766,28 @@ MCPT_DEV void uwalk_pop_one(UWalk& w, const WalkStack& st) {
     if (tok_t <= w.tmax) w.cur = tok;
 }
 
+// A triangle slot is read once per ray that reaches it and 48 MB of them stream through a 256 KB L1 that also has to
+// hold the nodes: MCPT_TRI_NO_L1 = 1 loads them around L1 (they stay in L2).
+#ifndef MCPT_TRI_NO_L1
+#define MCPT_TRI_NO_L1 0
+#endif
+MCPT_DEV float4 ldg_tri(const float4* p) {
+#if MCPT_TRI_NO_L1
+    float4 v;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+    return v;
+#else
+    return __ldg(p);
+#endif
+}
+
 // leaf token: a triangle slot of a mesh instance, or an analytic primitive
 template <bool COUNT>
 MCPT_DEV void uwalk_leaf(UWalk& w, Work& wk, const DevScene& S, const SmemScene& sm) {
     const int L = ~w.cur;
     if (L < S.u_n_tris) {
         const DevTri* tp = S.u_tris + L;
-        const float4 ta = __ldg(&tp->a), tb = __ldg(&tp->b), tc = __ldg(&tp->c);
+        const float4 ta = ldg_tri(&tp->a), tb = ldg_tri(&tp->b), tc = ldg_tri(&tp->c);
         const int tri = __float_as_int(ta.w);
         if (tri >= 0) {
             if (COUNT) ++wk.tris;

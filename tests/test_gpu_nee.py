@@ -107,3 +107,26 @@ def test_nee_off_is_the_default_image_bit_for_bit(ctx):
     c = ctx.read_accum()
     assert np.array_equal(a, c) and not np.array_equal(a, b)
     assert abs(b[..., :3].mean() - a[..., :3].mean()) < 0.05 * a[..., :3].mean()
+
+
+def test_nee_agrees_with_the_plain_estimator_on_a_mesh_scene(ctx):
+    """Meshes, interior rays, the unified tree and a quad light of emissivity 12: NEE and the plain estimator are two
+    unbiased estimates of the same image (4096 spp each, disjoint passes: the difference is Monte Carlo noise)."""
+    from common import host_scene
+    s = host_scene("mesh", n_meshes=4, tris_log2=10)
+    s.finalize()
+    ctx.upload_scene(s)
+    ctx.resize(96, 54)
+    ctx.set_camera(*capi.default_camera(96, 54))
+    ctx.set_params(nb_bounces=8, refract_ind=1.5, date=float(DATE))
+    imgs = {}
+    for nee in (0, 1):
+        ctx.set_option(capi.OPT_NEE, nee)
+        try:
+            imgs[nee] = _mean_image(ctx, 10_000 * nee, 4096)
+        finally:
+            ctx.set_option(capi.OPT_NEE, 0)
+    rmse = _rmse(imgs[0], imgs[1])
+    dlum = abs(imgs[0].mean() - imgs[1].mean()) / imgs[0].mean()
+    print(f"mesh scene, 4096 spp: plain vs NEE RMSE {rmse:.3e}, mean luminance {imgs[0].mean():.4f} / {imgs[1].mean():.4f}")
+    assert dlum <= 5e-3 and rmse <= 2e-2

@@ -61,3 +61,19 @@ def test_two_ranks_equal_one(tmp_path):
     assert np.isfinite(got).all()
     assert np.allclose(got, ref, rtol=1e-5, atol=1e-6)                      # fp32 reassociation only
     assert got.mean() > 0.05
+
+
+def test_strong_split_of_the_bench_covers_the_budget_exactly():
+    """bench.py --scaling strong: BASELINE config 4's 1024 spp (8 default steps' worth elsewhere) split over N ranks --
+    disjoint, ordered, exhaustive for every N the driver uses, and the per-rank shares differ by at most one pass."""
+    import sys
+    sys.path.insert(0, str(__import__("pathlib").Path(__file__).resolve().parent.parent))
+    import bench
+    assert bench.strong_spp("c4") == 1024 and bench.strong_spp("c2") == 8 * bench.WORKLOADS["c2"][4]
+    for name in ("c4", "c2"):
+        total = bench.strong_spp(name)
+        for world in (1, 2, 3, 4, 8):
+            parts = [pass_range(r, world, total) for r in range(world)]
+            assert parts[0][0] == 0 and sum(c for _, c in parts) == total
+            assert all(parts[r][0] + parts[r][1] == parts[r + 1][0] for r in range(world - 1))
+            assert max(c for _, c in parts) - min(c for _, c in parts) <= 1
