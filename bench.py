@@ -35,6 +35,7 @@ WORKLOADS = {
     "c1": (1, {}, 512, 512, 16, 8, 1.0, "BASELINE config 1: repo scene 1, 512x512, 16 spp, light 0.4, IOR 1.0, 8 bounces"),
     "c2": ("c2", {}, 1920, 1080, 64, 8, 1.5, "BASELINE config 2: repo scene 6, 1920x1080, 64 spp, IOR 1.5, roughness 0.5, light 0.4, 8 bounces"),
     "c5": ("c5", {}, 1920, 1080, 64, 16, 1.5, "BASELINE config 5 (divergence stress) at 64 spp per step: all transparent+reflective, roughness 0.1, 16 bounces, 1080p"),
+    "c5_256": ("c5", {}, 1920, 1080, 256, 16, 1.5, "BASELINE config 5: divergence stress, all transparent+reflective, roughness 0.1, 16 bounces, 1920x1080, 256 spp"),
     "mesh": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 1920, 1080, 16, 8, 1.5, "BASELINE config 3 at 16 spp per step: 16 meshes x 65536 triangles, 1080p, 8 bounces"),
     "c3": ("mesh", {"n_meshes": 16, "tris_log2": 16}, 1920, 1080, 256, 8, 1.5, "BASELINE config 3: synthetic 1M-triangle scene (16 meshes x 65536 triangles), 1920x1080, 256 spp, 8 bounces"),
     # the repo's eight scenes (hot keys Q..I, MontecarloGPU/montecarlo.cpp:236-290) at the metric's settings
@@ -573,6 +574,7 @@ def main():
             other["c1"] = quick_measure("c1", local, rank, world, 50, 5, fast_math=args.fast_math)
             other["c3"] = quick_measure("c3", local, rank, world, 4, 1, fast_math=args.fast_math)          # 256 spp per step, as BASELINE states it
             other["c3_16spp"] = quick_measure("mesh", local, rank, world, 10, 3, fast_math=args.fast_math)
+            other["c5"] = quick_measure("c5_256", local, rank, world, 3, 1, fast_math=args.fast_math)     # 256 spp per step, as BASELINE states it
             other["c5_64spp"] = quick_measure("c5", local, rank, world, 10, 3, fast_math=args.fast_math)
         # BASELINE config 4 as written: 3840x2160, a FIXED 1024 spp split over the N ranks, one reduce, rank 0 holds the sum
         other["c4_strong"] = quick_measure("c4", local, rank, world, 1 if world == 1 else 2, 1, strong=True, fast_math=args.fast_math)
@@ -624,6 +626,23 @@ def main():
     else:
         roofline.update({"achieved": None, "frac": None, "traffic": None,
                          "counters_source": "no ncu pass committed for this workload / option set (launch counts differ)" if mt else "no ncu pass committed for this workload"})
+    if s.nb_meshes and roofline.get("l2_gbs"):
+        # the mesh trees are served from L2 -- its bandwidth measured here with a resident-set copy
+        # (32 MB -> 32 MB inside the 126 MB L2, read + write bytes, best of 5 runs of 20 copies)
+        a_l2 = torch.empty(8 << 20, dtype=torch.float32, device="cuda")
+        b_l2 = torch.empty_like(a_l2)
+        best = 0.0
+        for _ in range(5):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record(stream)
+            for _ in range(20):
+                b_l2.copy_(a_l2)
+            e1.record(stream)
+            torch.cuda.synchronize()
+            best = max(best, 20 * 2 * a_l2.numel() * 4 / (e0.elapsed_time(e1) * 1e-3) / 1e9)
+        roofline["l2_peak_gbs"] = best
+        roofline["l2_frac"] = roofline["l2_gbs"] / best if best > 0 else None
+        del a_l2, b_l2
     roofline.update({"launches": trav_launches // n_prof, "avg_launch_ms": trav_ms / max(trav_launches, 1),
                      "rays_per_launch": rays_step / max(trav_launches // n_prof, 1),
                      "share_of_kernel_time": trav_ms / total_kernel_ms if total_kernel_ms else None,

@@ -110,23 +110,58 @@ def test_nee_off_is_the_default_image_bit_for_bit(ctx):
 
 
 def test_nee_agrees_with_the_plain_estimator_on_a_mesh_scene(ctx):
-    """Meshes, interior rays, the unified tree and a quad light of emissivity 12: NEE and the plain estimator are two
-    unbiased estimates of the same image (4096 spp each, disjoint passes: the difference is Monte Carlo noise)."""
-    from common import host_scene
-    s = host_scene("mesh", n_meshes=4, tris_log2=10)
+    """Meshes (one of them transparent: interior rays), the unified tree, rough surfaces (wide cones) and a small quad
+    light that paths find rarely by chance: NEE and the plain estimator have the same mean image, and two disjoint
+    2048-spp renders differ LESS from each other with NEE than without (that difference is pure noise)."""
+    from test_gpu_unified import _instanced_scene
+    from montecarlo_pathtracing_b200 import Scene
+    base, _ = _instanced_scene()
+    t = base.tables()
+    s = Scene()
+    m = t["meshes"][0]
+    mid = s.add_mesh(m["pos"], m["tri"])
+    s.place_mesh(mid, capi.transfo("tZs", -45, 10, 0, 30, 25, 25, 25), (0.8, 0.7, 0.6, 1.0))
+    s.place_mesh(mid, capi.transfo("tXs", 45, -10, 5, 75, 20, 25, 18), (0.3, 0.7, 0.9, 0.3))                  # transparent
+    s.add_orientedQuad(capi.transfo("tZs", 0, 0, -40, 0, 400, 400, 1), (0.7, 0.7, 0.7, 1.0))                   # floor, roughness 0: cone = hemisphere
+    s.add_orientedQuad(capi.transfo("tXs", 0, 0, 90, 180, 12, 12, 1), (0.9, 0.9, 0.9, 1.0), emissivity=30.0)   # small light, facing down
     s.finalize()
     ctx.upload_scene(s)
     ctx.resize(96, 54)
     ctx.set_camera(*capi.default_camera(96, 54))
     ctx.set_params(nb_bounces=8, refract_ind=1.5, date=float(DATE))
-    imgs = {}
+    imgs, rays = {}, {}
     for nee in (0, 1):
         ctx.set_option(capi.OPT_NEE, nee)
         try:
-            imgs[nee] = _mean_image(ctx, 10_000 * nee, 4096)
+            ctx.reset_stats()
+            imgs[nee] = [_mean_image(ctx, first, 2048) for first in (0, 2048)]
+            rays[nee] = ctx.stats()["rays"]
         finally:
             ctx.set_option(capi.OPT_NEE, 0)
-    rmse = _rmse(imgs[0], imgs[1])
-    dlum = abs(imgs[0].mean() - imgs[1].mean()) / imgs[0].mean()
-    print(f"mesh scene, 4096 spp: plain vs NEE RMSE {rmse:.3e}, mean luminance {imgs[0].mean():.4f} / {imgs[1].mean():.4f}")
-    assert dlum <= 5e-3 and rmse <= 2e-2
+    noise = {k: _rmse(v[0], v[1]) for k, v in imgs.items()}
+    mean = {k: float((v[0].mean() + v[1].mean()) / 2) for k, v in imgs.items()}
+    print(f"mesh scene, 2 x 2048 spp: noise plain {noise[0]:.3e}, NEE {noise[1]:.3e}; mean luminance {mean[0]:.4f} / {mean[1]:.4f}; rays {rays}")
+    assert rays[1] > rays[0]                                  # shadow rays were traced
+    assert abs(mean[0] - mean[1]) <= 2e-2 * mean[0]
+    assert noise[1] < 0.8 * noise[0]
+
+
+def test_nee_without_a_sampled_light_changes_nothing(ctx):
+    """Scenes whose lights are not quads (or that have none), and a descriptor whose nb_emissives is 0 or too large:
+    the option is a no-op, or clamps -- never an error and never a different image than the plain estimator."""
+    cv, keep = _setup(ctx, 1)
+    g = np.load(GOLD / "scene1.npz")
+    imgs = []
+    for nb_emi in (int(g["nb_emissives"]), 0, 10_000):
+        d, keep2 = desc_from_arrays(g["prims"], {"depth": g["bvh_depth"], "bb": g["bvh_bb"], "ind": g["bvh_ind"]}, ())
+        d.nb_emissives = nb_emi
+        ctx.set_option(capi.OPT_NEE, 1 if nb_emi != int(g["nb_emissives"]) else 0)
+        try:
+            ctx.upload_scene(d)
+            ctx.clear()
+            ctx.render(0, 8)
+            imgs.append(ctx.read_accum())
+        finally:
+            ctx.set_option(capi.OPT_NEE, 0)
+    assert np.array_equal(imgs[0], imgs[1])                 # nb_emissives = 0: no light table, plain estimator
+    assert np.isfinite(imgs[2]).all() and not np.array_equal(imgs[0], imgs[2])   # clamped to n_prims: NEE on the real light

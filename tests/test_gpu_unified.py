@@ -137,3 +137,35 @@ def test_bad_vertex_index_is_reported_not_followed(ctx):
     ro, rd = random_rays(o.prim_data(), 10_000, seed=2, clip=150.0)
     got = _trace(ctx, s.desc(), ro, rd, 1)
     assert len(compare_hits(got, o.trace(ro, rd))) == 0
+
+
+def test_edge_meshes_in_the_unified_tree(ctx):
+    """A mesh of ONE triangle, a mesh of two, and a mesh that is added but never placed: the builder's edge cases
+    (single-leaf subtree, single node, an instance list shorter than the mesh list)."""
+    rng = np.random.default_rng(17)
+    s = Scene()
+    ids = []
+    for n_tris in (1, 2, 5):
+        pos = rng.uniform(-1, 1, (3 * n_tris, 3)).astype(np.float32)
+        tri = np.arange(3 * n_tris, dtype=np.uint32).reshape(n_tris, 3)
+        ids.append(s.add_mesh(pos, tri))
+    s.place_mesh(ids[0], capi.transfo("tZs", -40, 0, 10, 30, 25, 25, 25), (0.8, 0.7, 0.6))
+    s.place_mesh(ids[1], capi.transfo("tZs", 40, 0, 10, 60, 25, 25, 25), (0.2, 0.7, 0.6))
+    s.place_mesh(ids[1], capi.transfo("tXs", 0, 50, 10, 45, 20, 30, 20), (0.2, 0.2, 0.6))      # ids[2] stays unplaced
+    s.add_orientedQuad(capi.transfo("tZs", 0, 0, -40, 0, 300, 300, 1), (0.5, 0.5, 0.5))
+    raw = s.prim_data()
+    s.finalize()
+    o = Oracle().load_unsorted(raw, s.tables()["meshes"]).finalize()
+    ro, rd = random_rays(o.prim_data(), 100_000, seed=6, clip=120.0)
+    rng2 = np.random.default_rng(3)
+    k = 20_000
+    for j, c in enumerate([(-40, 0, 10), (40, 0, 10), (0, 50, 10)]):
+        tgt = np.float32(c) + rng2.uniform(-20, 20, (k, 3)).astype(np.float32)
+        org = np.float32(c) + rng2.uniform(-150, 150, (k, 3)).astype(np.float32)
+        ro[j * k:(j + 1) * k], rd[j * k:(j + 1) * k] = org, tgt - org
+    ref = o.trace(ro, rd)
+    for unified in (1, 0):
+        for desc in (s.desc(), s.desc(mesh_trees=False)):
+            got = _trace(ctx, desc, ro, rd, unified)
+            assert len(compare_hits(got, ref)) == 0, unified
+    assert (ref["tri_index"] >= 0).sum() > 500
