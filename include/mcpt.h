@@ -115,7 +115,7 @@ enum {
                                       records. mcpt_mesh_desc.bvh may be empty (bb == ind == NULL) whenever
                                       MCPT_OPT_MESH_BVH is 1: no host tree is needed, triangles hit at exactly the
                                       same distance are then ranked by index instead of by the reference's leaf slot. */
-    MCPT_OPT_NEE = 13              /* 1 = next-event estimation: every vertex whose next ray is drawn from a cone also
+    MCPT_OPT_NEE = 13,             /* 1 = next-event estimation: every vertex whose next ray is drawn from a cone also
                                       samples one point on one emissive quad (the emissive-first records with
                                       emissivity > 0.5, picked by mat_info.a) and delivers the light's contribution
                                       through a shadow ray, balance-weighted against the bounce ray. A NEW estimator
@@ -123,6 +123,10 @@ enum {
                                       same expectation per pixel -- it converges to the same image -- with less
                                       noise at equal spp where lights are small; the bounce rays are unchanged.
                                       Default 0 (the reference's estimator, bit-level parity). */
+    MCPT_OPT_FLAT_POOL = 14        /* scenes of <= 16 primitives, bounces after the first: 1 = a warp pools the exact
+                                      tests of 64 rays per primitive type and runs them 32 at a time (default),
+                                      0 = the warp-coherent walk of the first bounce everywhere. Set before
+                                      mcpt_upload_scene. Same records. */
 };
 
 /* wavefront stages, in launch order inside one bounce */
@@ -201,7 +205,9 @@ int mcpt_resolve(mcpt_ctx* ctx, float divisor, int subsampling, void* dst, int d
 /* Accumulation buffer access (new; multi-GPU spp split and checkpoint/resume).
  * Layout: float4 per pixel (rgb sum, w unused), row-major, row 0 = bottom row
  * (gl_FragCoord convention). mcpt_bind_accum makes the library accumulate
- * straight into a caller-owned device buffer (e.g. an NCCL/torch send buffer). */
+ * straight into a caller-owned device buffer (e.g. an NCCL/torch send buffer) of
+ * at least w*h*16 bytes. mcpt_resize ENDS the binding: the size changed, the context
+ * goes back to a zeroed buffer of its own and the caller binds again if it wants to. */
 int mcpt_get_accum(mcpt_ctx* ctx, float** dev_ptr, size_t* bytes);
 int mcpt_bind_accum(mcpt_ctx* ctx, float* dev_ptr, size_t bytes);
 int mcpt_read_accum(mcpt_ctx* ctx, float* host_rgba, size_t bytes);

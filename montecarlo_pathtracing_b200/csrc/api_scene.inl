@@ -823,6 +823,7 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.leaf_bb = d_leaf_bb;
     S.flat = flat.empty() ? nullptr : d_flat;
     S.n_flat = int(flat.size());
+    S.flat_pool = c->opt_flat_pool;
     S.top_depth = td;
     S.n_prims = d->n_prims;
     S.n_meshes = d->n_meshes;

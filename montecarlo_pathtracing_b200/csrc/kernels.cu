@@ -556,6 +556,215 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse_unified(DevScene S, W
     }
 }
 
+// ---- flat scenes after the first bounce: exact tests pooled per warp and per primitive TYPE
+// The warp-coherent flat walk (scene_walk_flat) runs the exact test of primitive k whenever ANY of the warp's 32 rays
+// passes box k. Camera rays agree on their boxes (31 of 32 lanes active); the rays of later bounces do not: every
+// test body then runs for 6 .. 12 lanes (ncu, config 2: 16.9 active lanes in the second bounce, 10.8 in the fifth,
+// with the exact tests -- 60 % of the issued instructions -- at ~10). Here a warp takes kPoolR rays per lane, culls all
+// of them against the box list first (no test in that loop), turns every (ray, passing box) pair into a work item,
+// and runs the items of one primitive TYPE 32 at a time: one instruction stream (no type switch inside a round),
+// lanes filled with items of different primitives of that type and of different rays. Rays live in the warp's slice
+// of shared memory; a candidate is ranked by a 64-bit key -- distance bits, then the reference's visit order -- with
+// atomicMin, and the winner of a round writes the payload (local hit point, primitive, face) behind it. No CTA
+// barrier is involved (the regrouping of a 256-ray tile by primitive through shared bins needed three per tile and
+// lost, profiles/README.md). What is given up is the shrinking tmax of the sequential walk: every passing box is
+// tested. The total order of offer() (intersect.cuh) -- smaller distance, then higher leaf slot, then the candidate
+// offered first -- is the order of the keys, so the records are the same bits.
+#ifndef MCPT_POOL_R
+#define MCPT_POOL_R 2
+#endif
+constexpr int kPoolR = MCPT_POOL_R;
+constexpr int kPoolSlots = 32 * kPoolR;
+// per warp: ray origins (+ slack), directions, keys, payloads, items
+MCPT_DEV size_t pool_bytes_per_warp(int n_flat) { return size_t(kPoolSlots) * (16 + 16 + 8 + 16) + size_t(kPoolSlots) * size_t(n_flat) * 2; }
+static inline size_t pool_bytes_per_warp_host(int n_flat) { return size_t(kPoolSlots) * (16 + 16 + 8 + 16) + size_t(kPoolSlots) * size_t(n_flat) * 2; }
+
+struct PoolCand {
+    float a1, a2;
+    int cl;
+    bool c1, c2;
+};
+
+template <bool COUNT, int MINB, bool EXIT>
+__global__ void __launch_bounds__(kBlock, MINB) k_traverse_flat_pooled(DevScene S, Wavefront wf, QueueIn qin, HitSink sink,
+                                                                        unsigned long long* ray_counter, unsigned long long* work) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t s_hits;
+    __shared__ uint32_t s_tm[8];   // per primitive type: the list positions that hold a primitive of that type
+    const uint32_t len = queue_len(qin);
+    if (len == 0) {
+        if (threadIdx.x == 0 && sink.hitq.items) sink.hitq.counts[blockIdx.x] = 0u;
+        return;
+    }
+    if (threadIdx.x == 0) s_hits = 0u;
+    if (threadIdx.x < 8) s_tm[threadIdx.x] = 0u;
+    SmemScene sm = stage_scene(S, smem_raw);  // ends with a barrier
+    const int n = S.n_flat;
+    if (int(threadIdx.x) < n) {
+        const int prim = __float_as_int(sm.top_nodes[threadIdx.x].lo.w);
+        const int type = sm.prims[prim].type;
+        if (type >= 0 && type < 8) atomicOr(&s_tm[type], 1u << threadIdx.x);
+    }
+    __syncthreads();
+    const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
+    unsigned char* wbase = smem_raw + ((size_t(S.smem_bytes) + 15) & ~size_t(15)) + size_t(warp) * ((pool_bytes_per_warp(n) + 15) & ~size_t(15));
+    float4* rayO = reinterpret_cast<float4*>(wbase);
+    float4* rayD = rayO + kPoolSlots;
+    float4* pay = rayD + kPoolSlots;
+    unsigned long long* keys = reinterpret_cast<unsigned long long*>(pay + kPoolSlots);
+    unsigned short* items = reinterpret_cast<unsigned short*>(keys + kPoolSlots);
+    const unsigned long long key_none = (static_cast<unsigned long long>(__float_as_uint(MCPT_FLT_MAX)) << 32) | 0xffffffffull;
+    Work wk;
+    const uint32_t tile_rays = kBlock * kPoolR;
+    for (uint32_t tile = 0; tile * tile_rays < len; ++tile) {
+        const uint32_t wfirst = tile * tile_rays + warp * kPoolSlots;
+        // ---- phase 1: load kPoolR rays per lane, cull them against the whole list
+        uint32_t pid[kPoolR], mask[kPoolR];
+        bool valid[kPoolR];
+#pragma unroll
+        for (int j = 0; j < kPoolR; ++j) {
+            const uint32_t slot = uint32_t(j) * 32u + lane;
+            valid[j] = queue_item(qin, wfirst + slot, len, pid[j]);
+            float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
+            if (valid[j]) wf.load_ray(pid[j], o4, d4);
+            const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
+            const float dl = sqrtf(D.x * D.x + D.y * D.y + D.z * D.z);
+            const bool ok = valid[j] && (dl > 0.0f) && (dl < FLT_MAX);
+            const float rl = (dl < 1e-30f) ? 1.0f / dl : cull_rcp(dl);
+            const f3 idir = safe_rcp3(mk3(D.x * rl, D.y * rl, D.z * rl));
+            const f3 od = mk3(-O.x * idir.x, -O.y * idir.y, -O.z * idir.z);
+            const float slack = 1e-4f * (fabsf(O.x) + fabsf(O.y) + fabsf(O.z)) + 1e-3f;
+            const uint32_t oct = (__float_as_uint(idir.x) >> 31) | ((__float_as_uint(idir.y) >> 31) << 1) | ((__float_as_uint(idir.z) >> 31) << 2);
+            const DevNode* boxes = sm.top_nodes + oct * uint32_t(n);
+            uint32_t m = 0u;
+            if (ok)
+                for (int i = 0; i < n; ++i)
+                    if (slab_sorted(boxes[i], idir, od, FLT_MAX)) m |= 1u << i;
+            if (COUNT && ok) wk.boxes += n;
+            mask[j] = m;
+            rayO[slot] = make_float4(O.x, O.y, O.z, slack);
+            rayD[slot] = make_float4(D.x, D.y, D.z, 0.0f);
+            keys[slot] = key_none;
+        }
+        __syncwarp();
+        // ---- phase 2: the items of one primitive type at a time, 32 per round
+#pragma unroll 1
+        for (int type = MCPT_PRIM_SPHERE; type <= MCPT_PRIM_ORIENTED_QUAD; ++type) {
+            const uint32_t tm = s_tm[type];
+            if (!tm) continue;
+            uint32_t mine = 0u;
+#pragma unroll
+            for (int j = 0; j < kPoolR; ++j) mine += uint32_t(__popc(mask[j] & tm));
+            // exclusive prefix over the lanes
+            uint32_t off = mine;
+#pragma unroll
+            for (int d = 1; d < 32; d <<= 1) {
+                const uint32_t v = __shfl_up_sync(0xffffffffu, off, d);
+                if (lane >= uint32_t(d)) off += v;
+            }
+            const uint32_t total = __shfl_sync(0xffffffffu, off, 31);
+            if (!total) continue;
+            off -= mine;
+#pragma unroll
+            for (int j = 0; j < kPoolR; ++j) {
+                uint32_t m = mask[j] & tm;
+                while (m) {
+                    const int i = __ffs(int(m)) - 1;
+                    m &= m - 1u;
+                    items[off++] = (unsigned short)(((uint32_t(j) * 32u + lane) << 4) | uint32_t(i));
+                }
+            }
+            __syncwarp();
+#pragma unroll 1
+            for (uint32_t base = 0; base < total; base += 32u) {
+                const bool has = base + lane < total;
+                const uint32_t it = has ? items[base + lane] : 0u;
+                const uint32_t slot = it >> 4;
+                unsigned long long k1 = key_none, k2 = key_none;
+                f3 Pl1 = mk3(0, 0, 0), Pl2 = mk3(0, 0, 0);
+                int packed = 0;
+                if (has) {
+                    const float4 o4 = rayO[slot], d4 = rayD[slot];
+                    const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
+                    const uint32_t oct0 = 0u;  // the primitive id sits in every octant copy of the list
+                    const int prim = __float_as_int(sm.top_nodes[oct0 * uint32_t(n) + (it & 15u)].lo.w);
+                    const DevPrim* pp = sm.prims + prim;
+                    Aff inv, fwd;
+                    inv.r0 = pp->inv.r0;
+                    inv.r1 = pp->inv.r1;
+                    inv.r2 = pp->inv.r2;
+                    fwd.r0 = pp->fwd.r0;
+                    fwd.r1 = pp->fwd.r1;
+                    fwd.r2 = pp->fwd.r2;
+                    const int tslot = pp->slot;
+                    if (COUNT) ++wk.prims;
+                    const f3 Oi = xform_point(inv, O);
+                    const f3 Di = normalize3(xform_vector(inv, D));
+                    Cand k;
+                    k.a1 = k.a2 = 0.0f;
+                    k.cl = 0;
+                    k.c1 = k.c2 = false;
+                    switch (type) {  // warp-uniform
+                        case MCPT_PRIM_SPHERE: sphere_test(k, Oi, Di, o4.w * pp->inv_smin); break;
+                        case MCPT_PRIM_CUBE: cube_test(k, Oi, Di); break;
+                        case MCPT_PRIM_CYLINDER: cylinder_test(k, Oi, Di); break;
+                        case MCPT_PRIM_CONE: cone_test(k, Oi, Di, O, S.leaf_bb + 6 * prim); break;
+                        default: quad_test(k, Oi, Di, O, S.leaf_bb + 6 * prim); break;
+                    }
+                    // offer_at's arithmetic (intersect.cuh): Pl = Oi + Di a, Pg = fwd Pl, dist = |O - Pg|; offer()'s order as a key:
+                    // smaller distance, then the higher leaf slot, then the candidate offered first
+                    const uint32_t tie = (uint32_t(0xffff - tslot) << 8);
+                    packed = prim | (k.cl << 8);
+                    if (k.c1) {
+                        Pl1 = Oi + Di * k.a1;
+                        const float dist = distance3(O, xform_point(fwd, Pl1));
+                        if (dist < MCPT_FLT_MAX) k1 = (static_cast<unsigned long long>(__float_as_uint(dist)) << 32) | tie;
+                    }
+                    if (k.c2) {
+                        Pl2 = Oi + Di * k.a2;
+                        const float dist = distance3(O, xform_point(fwd, Pl2));
+                        if (dist < MCPT_FLT_MAX) k2 = (static_cast<unsigned long long>(__float_as_uint(dist)) << 32) | tie | 1u;
+                    }
+                    if (k1 != key_none) atomicMin(&keys[slot], k1);
+                    if (k2 != key_none) atomicMin(&keys[slot], k2);
+                }
+                __syncwarp();
+                if (has) {
+                    const unsigned long long kb = keys[slot];
+                    if (k1 != key_none && kb == k1) pay[slot] = make_float4(Pl1.x, Pl1.y, Pl1.z, __int_as_float(packed));
+                    if (k2 != key_none && kb == k2) pay[slot] = make_float4(Pl2.x, Pl2.y, Pl2.z, __int_as_float(packed));
+                }
+                __syncwarp();
+            }
+        }
+        // ---- phase 3: every ray's record
+#pragma unroll
+        for (int j = 0; j < kPoolR; ++j) {
+            const uint32_t slot = uint32_t(j) * 32u + lane;
+            Best best;
+            best_reset(best);
+            const unsigned long long kb = keys[slot];
+            const float4 d4 = rayD[slot];
+            if (kb != key_none) {
+                const float4 pv = pay[slot];
+                const int packed = __float_as_int(pv.w);
+                best.h.dist = __uint_as_float(uint32_t(kb >> 32));
+                best.h.pl = mk3(pv.x, pv.y, pv.z);
+                best.h.prim = packed & 0xff;
+                best.h.sub = packed >> 8;
+            }
+            deliver<EXIT>(S, wf, sink, &s_hits, pid[j], valid[j], best, mk3(d4.x, d4.y, d4.z));
+        }
+        __syncwarp();
+    }
+    if (ray_counter && threadIdx.x == 0) atomicAdd(ray_counter, (unsigned long long)len);
+    if (COUNT) flush_work(wk, work);
+    if (sink.hitq.items) {
+        __syncthreads();
+        if (threadIdx.x == 0) sink.hitq.counts[blockIdx.x] = s_hits;
+    }
+}
+
 template <bool COUNT, int MINB>
 static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const HitSink& sink,
                                  unsigned long long* ray_counter, unsigned long long* work) {
@@ -569,7 +778,15 @@ static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefro
             k_traverse<COUNT, MINB, FLAT, MESHES, PERSIST, false><<<grid, kBlock, S.smem_bytes, lc.stream>>>(S, wf, qin, sink,      \
                                                                                                             ray_counter, work);    \
     } while (0)
-    if (S.n_flat > 0)
+    if (S.n_flat > 0 && S.flat_pool && qin.items && !sink.exit_mode) {
+        // after the first bounce: exact tests pooled per warp and primitive type (k_traverse_flat_pooled). Interior rays keep
+        // the sequential walk: they start inside a primitive whose far side bounds the search at once (measured: config 2
+        // 1.81 vs 1.95 ms per step, scene 2 1.23 vs 1.28, scene 4 0.73 vs 0.76)
+        const size_t smem = ((size_t(S.smem_bytes) + 15) & ~size_t(15)) + (kBlock / 32) * ((pool_bytes_per_warp_host(S.n_flat) + 15) & ~size_t(15));
+        static bool once = false;
+        if (!once) once = cudaFuncSetAttribute(k_traverse_flat_pooled<COUNT, MINB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess;
+        k_traverse_flat_pooled<COUNT, MINB, false><<<grid, kBlock, smem, lc.stream>>>(S, wf, qin, sink, ray_counter, work);
+    } else if (S.n_flat > 0)
         MCPT_TRAVERSE(true, false, false);
     else if (S.n_meshes == 0) {
         if (S.persistent) MCPT_TRAVERSE(false, false, true);

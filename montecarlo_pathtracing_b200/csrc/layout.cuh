@@ -125,6 +125,7 @@ struct DevScene {
     const float* leaf_bb;      // 6 floats per primitive: its un-inflated top-level leaf box
     const DevNode* flat;       // n_flat leaf boxes (aux0 = primitive id) when the scene is small, else null
     int32_t n_flat;            // > 0 selects the warp-coherent flat walk
+    int32_t flat_pool;         // 1: after the first bounce the flat walk pools its exact tests per warp and primitive type
     int32_t top_depth;
     int32_t n_prims;
     int32_t n_meshes;

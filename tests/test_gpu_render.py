@@ -355,3 +355,33 @@ def test_rotated_elongated_primitives_of_every_type():
         assert out[key][1]["rays"] == st["rays"] and out[key][1]["segments"] == st["segments"], key
     ref = o.render(w, h, 0, spp) / np.float32(spp)
     _assert_image_parity(base[..., :3] / np.float32(spp), ref, frac=0.97)
+
+
+@pytest.mark.parametrize("kind,bounces,ior", [(1, 9, 1.0), (2, 9, 1.0), (4, 8, 1.0), (6, 8, 1.5), ("c2", 8, 1.5)])
+def test_pooled_flat_walk_finds_the_same_records(kind, bounces, ior):
+    """MCPT_OPT_FLAT_POOL: after the first bounce a warp pools the exact tests of 64 rays per primitive type instead of
+    walking the list with 32 rays in lock step. The candidates are ranked by the same total order (distance, leaf slot,
+    offer order) through 64-bit keys, so accumulated sums, ray and segment counts are the same bit for bit -- also
+    against the tree walk, which shares no code with either."""
+    s, o = both(kind)
+    iv, ipv = capi.default_camera(240, 135)
+    out = {}
+    for name, opts in (("pooled", {capi.OPT_FLAT_POOL: 1}), ("lockstep", {capi.OPT_FLAT_POOL: 0}), ("tree", {capi.OPT_FLAT_WALK: 0})):
+        c = Context(0)
+        try:
+            for k, v in opts.items():
+                c.set_option(k, v)
+            c.set_option(capi.OPT_PASSES_PER_BATCH, 3)      # ragged batches: 7 passes = 3 + 3 + 1
+            c.upload_scene(s)
+            c.resize(240, 135)
+            c.set_camera(iv, ipv)
+            c.set_params(nb_bounces=bounces, refract_ind=ior, date=float(DATE))
+            c.render(0, 7)
+            out[name] = (c.read_accum(), c.stats())
+        finally:
+            c.close()
+    base, st = out["pooled"]
+    assert base[..., :3].mean() > 0.01 and st["rays"] > 2 * st["paths"]
+    for name in ("lockstep", "tree"):
+        assert np.array_equal(base, out[name][0]), name
+        assert out[name][1]["rays"] == st["rays"] and out[name][1]["segments"] == st["segments"], name
