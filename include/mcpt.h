@@ -123,10 +123,17 @@ enum {
                                       same expectation per pixel -- it converges to the same image -- with less
                                       noise at equal spp where lights are small; the bounce rays are unchanged.
                                       Default 0 (the reference's estimator, bit-level parity). */
-    MCPT_OPT_FLAT_POOL = 14        /* scenes of <= 16 primitives, bounces after the first: 1 = a warp pools the exact
+    MCPT_OPT_FLAT_POOL = 14,       /* scenes of <= 16 primitives, bounces after the first: 1 = a warp pools the exact
                                       tests of 64 rays per primitive type and runs them 32 at a time (default),
                                       0 = the warp-coherent walk of the first bounce everywhere. Set before
                                       mcpt_upload_scene. Same records. */
+    MCPT_OPT_LEAF_POOL = 15        /* scenes traced through the unified world-space tree (meshes, large trees): N > 0 =
+                                      a lane that reaches a leaf queues a (ray, leaf) item and walks on; the warp
+                                      runs the exact tests of the queue 32 at a time once N items (1..32) wait, the
+                                      closest hit of a ray ranked by a 64-bit key in shared memory
+                                      (k_traverse_unified_pooled). 0 = every lane tests its own leaf (default:
+                                      measured 3 .. 6 % faster, csrc/kernels.cu). Set before mcpt_upload_scene. Same
+                                      records. */
 };
 
 /* wavefront stages, in launch order inside one bounce */

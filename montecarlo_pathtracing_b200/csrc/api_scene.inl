@@ -811,6 +811,29 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.u_pad_rel = u_pad_rel;
     S.u_pad_abs = u_pad_abs;
     S.u_radius = u_radius;
+    {   // key layout of the pooled leaf tests (layout.cuh: u_pool)
+        S.u_pool = 0, S.u_key_shift = 0, S.u_slot_max = 0, S.u_rank_max = 0;
+        if (unified && c->opt_leaf_pool > 0) {
+            // a triangle's rank is its leaf slot in the uploaded reference tree (< 2^depth) or its index (< n_tris), -1 if absent
+            long long rank_max = 1, slot_max = 0;
+            for (const Inst& in : inst) {
+                const mcpt_mesh_desc& md = d->meshes[in.mesh];
+                long long r = (long long)md.n_tris;
+                if (md.bvh.ind && md.bvh.depth >= 0 && md.bvh.depth < 31) r = std::max(r, 1ll << md.bvh.depth);
+                rank_max = std::max(rank_max, r + 1);
+            }
+            for (int i = 0; i < d->n_prims; ++i) slot_max = std::max(slot_max, (long long)prims[i].slot);
+            int rb = 0, sb = 0;
+            while ((1ll << rb) <= rank_max) ++rb;
+            while ((1ll << sb) <= slot_max) ++sb;
+            if (rb + sb + 1 <= 32 && size_t(u_n_tris) + size_t(d->n_prims) < (1u << 26)) {
+                S.u_pool = std::min(c->opt_leaf_pool, 32);
+                S.u_key_shift = rb + 1;
+                S.u_slot_max = int(slot_max);
+                S.u_rank_max = int(rank_max);
+            }
+        }
+    }
     if ((rc = upload_vec(c, top, &d_top)) || (rc = upload_vec(c, prims, &d_prims)) || (rc = upload_vec(c, color, &d_color)) ||
         (rc = upload_vec(c, mat, &d_mat)) || (rc = upload_vec(c, meshes, &d_meshes)) || (rc = upload_vec(c, leaf_bb, &d_leaf_bb)) ||
         (rc = upload_vec(c, flat, &d_flat)))

@@ -556,6 +556,290 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse_unified(DevScene S, W
     }
 }
 
+// ---- unified walk, leaf tests pooled per warp (MCPT_OPT_LEAF_POOL)
+// In traverse_unified a lane that reaches a leaf waits until the warp runs its leaf stage, and that stage runs for the
+// few lanes that stand at a leaf (ncu, 1 M triangles: ~30 % of the issued instructions at 4 .. 7 of 32 lanes). Here the
+// lane writes a (ray, leaf) item into a ring in the warp's slice of shared memory and WALKS ON; once S.u_pool items wait
+// the whole warp runs up to 32 exact tests, each lane one item of whichever ray. The rays (origin, direction, slack)
+// live in shared memory, one slot per lane; a candidate is ranked by atomicMin on a 64-bit key -- distance bits, then
+// offer()'s tie order (DevScene::u_pool) -- and the winner writes the payload (local hit point, leaf) behind it; the
+// owner of the ray re-reads its key after every round to shrink tmax. What is given up: between the push of an item
+// and its round the ray walks with the tmax it had. A ray is finished when its stack is empty AND the ring has moved
+// past its last item (sequence numbers). Same tests, same arithmetic, same order: same records.
+// Measured (1 M triangles at 16 spp per step / repo scene 8, Msamples/s; one test per lane: 1584 / 688): trigger 4 / 8 / 16 / 24 / 32
+// items 1356 / 1451 / 1518 / 1536 / 1531 and 561 / 612 / 634 / 651 / 651; with 2 / 3 / 4 pop passes in front of every node step
+// (trigger 24) 1455 / 1422 / 1406 and 599 / 591 / 589. The rounds do run at 21 lanes instead of 4 .. 7, but the exact tests are
+// only ~13 % of the issued instructions (1.4 leaf tests against 7.3 node steps per ray), the node steps stay at 16 .. 18 lanes
+// (a lane without a node is mostly one whose stack entry was culled or whose warp waits for the refill, not one waiting at a
+// leaf), the ring costs a ballot and a branch per iteration, and a ray walks 4 % more boxes with the tmax it had when it queued
+// its item. Off by default (MCPT_OPT_LEAF_POOL = 0); kept because the records are the same and the parity tests cover it.
+#ifndef MCPT_UP_POP_PASSES
+#define MCPT_UP_POP_PASSES 1
+#endif
+constexpr int kUPoolRing = 64;
+constexpr size_t kUPoolBytesPerWarp = 32 * (16 + 16 + 16 + 8) + kUPoolRing * 4;
+struct UPool {
+    float4* rayO;  // xyz origin, w slack
+    float4* rayD;
+    float4* pay;   // xyz local hit point, w = leaf | face << 26
+    unsigned long long* keys;
+    uint32_t* items;  // ray slot << 27 | leaf
+};
+
+template <bool COUNT>
+__device__ __forceinline__ void upool_round(const DevScene& S, const SmemScene& sm, const UPool& q, uint32_t head, uint32_t n_items,
+                                            uint32_t lane, Work& wk) {
+    const unsigned long long key_none = (static_cast<unsigned long long>(__float_as_uint(MCPT_FLT_MAX)) << 32) | 0xffffffffull;
+    const bool has = lane < n_items;
+    const uint32_t it = has ? q.items[(head + lane) & uint32_t(kUPoolRing - 1)] : 0u;
+    const uint32_t r = it >> 27;
+    const int L = int(it & 0x7ffffffu);
+    unsigned long long k1 = key_none, k2 = key_none;
+    f3 Pl1 = mk3(0, 0, 0), Pl2 = mk3(0, 0, 0);
+    uint32_t pw = uint32_t(L);
+    if (has) {
+        const float4 o4 = q.rayO[r], d4 = q.rayD[r];
+        const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
+        if (L < S.u_n_tris) {
+            const DevTri* tp = S.u_tris + L;
+            const float4 ta = ldg_tri(&tp->a), tb = ldg_tri(&tp->b), tc = ldg_tri(&tp->c);
+            if (__float_as_int(ta.w) >= 0) {
+                if (COUNT) ++wk.tris;
+                const int pid = __float_as_int(tc.w);
+                const DevPrim* pp = (pid < S.smem_prims) ? (sm.prims + pid) : (S.prims + pid);
+                Aff inv;
+                inv.r0 = pp->inv.r0;
+                inv.r1 = pp->inv.r1;
+                inv.r2 = pp->inv.r2;
+                const f3 Oi = xform_point(inv, O);
+                const f3 Di = normalize3(xform_vector(inv, D));
+                float a;
+                if (triangle_param(mk3(ta.x, ta.y, ta.z), mk3(tb.x, tb.y, tb.z), mk3(tc.x, tc.y, tc.z), Oi, Di, a)) {
+                    Aff fwd;
+                    fwd.r0 = pp->fwd.r0;
+                    fwd.r1 = pp->fwd.r1;
+                    fwd.r2 = pp->fwd.r2;
+                    Pl1 = Oi + Di * a;  // offer_at (intersect.cuh)
+                    const float dist = distance3(O, xform_point(fwd, Pl1));
+                    const uint32_t low = (uint32_t(S.u_slot_max - pp->slot) << S.u_key_shift) | (uint32_t(S.u_rank_max - (__float_as_int(tb.w) + 1)) << 1);
+                    if (dist < MCPT_FLT_MAX) k1 = (static_cast<unsigned long long>(__float_as_uint(dist)) << 32) | low;
+                }
+            }
+        } else {
+            const int prim = L - S.u_n_tris;
+            const DevPrim* pp = (prim < S.smem_prims) ? (sm.prims + prim) : (S.prims + prim);
+            const int type = pp->type;
+            if (type > MCPT_PRIM_MESH) {
+                Aff inv, fwd;
+                inv.r0 = pp->inv.r0;
+                inv.r1 = pp->inv.r1;
+                inv.r2 = pp->inv.r2;
+                fwd.r0 = pp->fwd.r0;
+                fwd.r1 = pp->fwd.r1;
+                fwd.r2 = pp->fwd.r2;
+                if (COUNT) ++wk.prims;
+                const f3 Oi = xform_point(inv, O);
+                const f3 Di = normalize3(xform_vector(inv, D));
+                Cand k;
+                k.a1 = k.a2 = 0.0f;
+                k.cl = 0;
+                k.c1 = k.c2 = false;
+                switch (type) {
+                    case MCPT_PRIM_SPHERE: sphere_test(k, Oi, Di, o4.w * pp->inv_smin); break;
+                    case MCPT_PRIM_CUBE: cube_test(k, Oi, Di); break;
+                    case MCPT_PRIM_CYLINDER: cylinder_test(k, Oi, Di); break;
+                    case MCPT_PRIM_CONE: cone_test(k, Oi, Di, O, S.leaf_bb + 6 * prim); break;
+                    case MCPT_PRIM_ORIENTED_QUAD: quad_test(k, Oi, Di, O, S.leaf_bb + 6 * prim); break;
+                    default: break;
+                }
+                const uint32_t low = (uint32_t(S.u_slot_max - pp->slot) << S.u_key_shift) | (uint32_t(S.u_rank_max - 1) << 1);  // rank 0
+                pw = uint32_t(L) | (uint32_t(k.cl) << 26);
+                if (k.c1) {
+                    Pl1 = Oi + Di * k.a1;
+                    const float dist = distance3(O, xform_point(fwd, Pl1));
+                    if (dist < MCPT_FLT_MAX) k1 = (static_cast<unsigned long long>(__float_as_uint(dist)) << 32) | low;
+                }
+                if (k.c2) {
+                    Pl2 = Oi + Di * k.a2;
+                    const float dist = distance3(O, xform_point(fwd, Pl2));
+                    if (dist < MCPT_FLT_MAX) k2 = (static_cast<unsigned long long>(__float_as_uint(dist)) << 32) | low | 1u;
+                }
+            }
+        }
+        if (k1 != key_none) atomicMin(&q.keys[r], k1);
+        if (k2 != key_none) atomicMin(&q.keys[r], k2);
+    }
+    __syncwarp();
+    if (has) {
+        const unsigned long long kb = q.keys[r];
+        if (k1 != key_none && kb == k1) q.pay[r] = make_float4(Pl1.x, Pl1.y, Pl1.z, __uint_as_float(pw));
+        if (k2 != key_none && kb == k2) q.pay[r] = make_float4(Pl2.x, Pl2.y, Pl2.z, __uint_as_float(pw));
+    }
+    __syncwarp();
+}
+
+template <bool COUNT, bool EXIT>
+__device__ __forceinline__ void traverse_unified_pooled(const DevScene& S, const SmemScene& sm, const Wavefront& wf, const QueueIn& qin,
+                                                        uint32_t len, const HitSink& sink, uint32_t* s_next, uint32_t* s_hits,
+                                                        const UPool& q, Work& wk) {
+    MCPT_WALK_STACK_DECL(st, kWalkStackWide);
+    const unsigned long long key_none = (static_cast<unsigned long long>(__float_as_uint(MCPT_FLT_MAX)) << 32) | 0xffffffffull;
+    UWalk w;
+    w.done = true;
+    w.cur = 0;
+    w.sp = 0;
+    const uint32_t lane = threadIdx.x & 31u, below = (1u << lane) - 1u;
+    bool has_ray = false, exhausted = false;
+    uint32_t p = 0;
+    uint32_t head = 0, tail = 0, my_end = 0;  // ring sequence numbers: items [head, tail) wait; my_end = one past this ray's last item
+    const int refill = qin.items ? S.refill_lanes : S.refill_first;
+    const uint32_t trigger = uint32_t(S.u_pool);
+    constexpr int passes = MCPT_UP_POP_PASSES;
+    while (true) {
+        const uint32_t idle = __ballot_sync(0xffffffffu, !has_ray);
+        if (idle) {
+            if (!exhausted && (idle == 0xffffffffu || __popc(idle) >= refill)) {
+                uint32_t first = 0;
+                if (lane == 0) first = atomicAdd(s_next, uint32_t(__popc(idle)));
+                first = __shfl_sync(0xffffffffu, first, 0);
+                if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
+                    float4 o4, d4;
+                    wf.load_ray(p, o4, d4);
+                    uwalk_begin(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
+                    q.rayO[lane] = make_float4(o4.x, o4.y, o4.z, w.slack);
+                    q.rayD[lane] = make_float4(d4.x, d4.y, d4.z, 0.0f);
+                    q.keys[lane] = key_none;
+                    my_end = head;
+                    has_ray = true;
+                }
+                exhausted = first + __popc(idle) >= len;
+                __syncwarp();
+            } else if (idle == 0xffffffffu) {
+                break;
+            }
+        }
+#pragma unroll 1
+        while (true) {
+            const bool want = has_ray && !w.done;
+            const uint32_t wm = __ballot_sync(0xffffffffu, want);
+            if (!wm) break;
+            if (__popc(wm) < MCPT_U_MIN_LANES && __any_sync(0xffffffffu, has_ray && !want)) break;
+            // pop passes: a lane without a node takes entries off its stack until one is a node (or the stack is empty); a
+            // leaf -- from the stack or the nearest child of the last node step -- is queued at once, so that as many lanes
+            // as possible enter the node step with a node
+#pragma unroll 1
+            for (int pass = 0; pass < passes; ++pass) {
+                const bool leaf = has_ray && !w.done && w.cur < 0 && w.cur != kTokPop;
+                const uint32_t lm = __ballot_sync(0xffffffffu, leaf);
+                if (lm) {
+                    if (leaf) {
+                        const uint32_t pos = tail + uint32_t(__popc(lm & below));
+                        q.items[pos & uint32_t(kUPoolRing - 1)] = (lane << 27) | uint32_t(~w.cur);
+                        my_end = pos + 1u;
+                        w.cur = kTokPop;
+                    }
+                    tail += uint32_t(__popc(lm));
+                    if (tail - head >= trigger) {
+                        __syncwarp();
+                        do {
+                            const uint32_t n_items = min(tail - head, 32u);
+                            upool_round<COUNT>(S, sm, q, head, n_items, lane, wk);
+                            head += n_items;
+                        } while (tail - head >= trigger);
+                        if (has_ray) {
+                            const unsigned long long kb = q.keys[lane];
+                            if (kb != key_none) w.tmax = __uint_as_float(uint32_t(kb >> 32)) * 1.0001f + w.slack;
+                        }
+                    }
+                }
+                const bool popping = has_ray && !w.done && w.cur == kTokPop;
+                if (!__any_sync(0xffffffffu, popping)) break;
+                if (popping) uwalk_pop_one(w, st);
+            }
+            if (has_ray && !w.done && w.cur >= 0) uwalk_node<COUNT>(w, wk, S, sm, st);
+        }
+        // rays whose walk is over but whose last items still wait: run what is queued
+        if (tail != head && __any_sync(0xffffffffu, has_ray && w.done && int32_t(head - my_end) < 0)) {
+            __syncwarp();
+            while (tail != head) {
+                const uint32_t n_items = min(tail - head, 32u);
+                upool_round<COUNT>(S, sm, q, head, n_items, lane, wk);
+                head += n_items;
+            }
+            if (has_ray) {
+                const unsigned long long kb = q.keys[lane];
+                if (kb != key_none) w.tmax = __uint_as_float(uint32_t(kb >> 32)) * 1.0001f + w.slack;
+            }
+        }
+        {  // finished rays: deliver and free the lane
+            const bool fin = has_ray && w.done && int32_t(head - my_end) >= 0;
+            if (__any_sync(0xffffffffu, fin)) {
+                Best best;
+                best_reset(best);
+                f3 D = mk3(0, 0, 0);
+                if (fin) {
+                    const unsigned long long kb = q.keys[lane];
+                    const float4 d4 = q.rayD[lane];
+                    D = mk3(d4.x, d4.y, d4.z);
+                    if (kb != key_none) {
+                        const float4 pv = q.pay[lane];
+                        const uint32_t pw = __float_as_uint(pv.w);
+                        const int L = int(pw & 0x3ffffffu);
+                        best.h.dist = __uint_as_float(uint32_t(kb >> 32));
+                        best.h.pl = mk3(pv.x, pv.y, pv.z);
+                        if (L < S.u_n_tris) {
+                            const DevTri* tp = S.u_tris + L;
+                            best.h.prim = __float_as_int(__ldg(&tp->c).w);
+                            best.h.sub = __float_as_int(__ldg(&tp->a).w);
+                        } else {
+                            best.h.prim = L - S.u_n_tris;
+                            best.h.sub = int(pw >> 26);
+                        }
+                    }
+                }
+                deliver<EXIT>(S, wf, sink, s_hits, p, fin, best, D);
+                if (fin) has_ray = false;
+            }
+        }
+    }
+}
+
+template <bool COUNT, int MINB, bool EXIT>
+__global__ void __launch_bounds__(kBlock, MINB) k_traverse_unified_pooled(DevScene S, Wavefront wf, QueueIn qin, HitSink sink,
+                                                                           unsigned long long* ray_counter, unsigned long long* work) {
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    __shared__ uint32_t s_hits, s_next;
+    const uint32_t len = queue_len(qin);
+    if (len == 0) {
+        if (threadIdx.x == 0 && sink.hitq.items) sink.hitq.counts[blockIdx.x] = 0u;
+        return;
+    }
+    if (threadIdx.x == 0) s_hits = s_next = 0u;
+    SmemScene sm = stage_scene(S, smem_raw);  // ends with a barrier
+    unsigned char* wbase = smem_raw + ((size_t(S.smem_bytes) + 15) & ~size_t(15)) + size_t(threadIdx.x >> 5) * kUPoolBytesPerWarp;
+    UPool q;
+    q.rayO = reinterpret_cast<float4*>(wbase);
+    q.rayD = q.rayO + 32;
+    q.pay = q.rayD + 32;
+    q.keys = reinterpret_cast<unsigned long long*>(q.pay + 32);
+    q.items = reinterpret_cast<uint32_t*>(q.keys + 32);
+    Work wk;
+    traverse_unified_pooled<COUNT, EXIT>(S, sm, wf, qin, len, sink, &s_next, &s_hits, q, wk);
+    if (ray_counter && threadIdx.x == 0) {
+        unsigned long long rays = len;
+        if (!qin.items) {
+            const uint32_t last_tile = blockIdx.x + (len / kBlock - 1u) * gridDim.x;
+            if (last_tile * kBlock + kBlock > qin.n_identity) rays -= last_tile * kBlock + kBlock - qin.n_identity;
+        }
+        atomicAdd(ray_counter, rays);
+    }
+    if (COUNT) flush_work(wk, work);
+    if (sink.hitq.items) {
+        __syncthreads();
+        if (threadIdx.x == 0) sink.hitq.counts[blockIdx.x] = s_hits;
+    }
+}
+
 // ---- flat scenes after the first bounce: exact tests pooled per warp and per primitive TYPE
 // The warp-coherent flat walk (scene_walk_flat) runs the exact test of primitive k whenever ANY of the warp's 32 rays
 // passes box k. Camera rays agree on their boxes (31 of 32 lanes active); the rays of later bounces do not: every
@@ -805,6 +1089,27 @@ void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const
         sink.exit_mode = 1;
         sink.flat_face = exit_prm->flat_face;
         sink.refract_ind = exit_prm->refract_ind;
+    }
+    if (S.u_nodes && S.persistent && S.u_pool > 0) {
+        const size_t smem = ((size_t(S.smem_bytes) + 15) & ~size_t(15)) + (kBlock / 32) * kUPoolBytesPerWarp;
+#define MCPT_TRAVERSE_UP(COUNT, MINB)                                                                                                   \
+    do {                                                                                                                                \
+        static bool once = false;                                                                                                       \
+        if (!once)                                                                                                                      \
+            once = cudaFuncSetAttribute(k_traverse_unified_pooled<COUNT, MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess && \
+                   cudaFuncSetAttribute(k_traverse_unified_pooled<COUNT, MINB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess; \
+        if (sink.exit_mode)                                                                                                             \
+            k_traverse_unified_pooled<COUNT, MINB, true><<<lc.grid, kBlock, smem, lc.stream>>>(S, wf, qin, sink, ray_counter, work);    \
+        else                                                                                                                            \
+            k_traverse_unified_pooled<COUNT, MINB, false><<<lc.grid, kBlock, smem, lc.stream>>>(S, wf, qin, sink, ray_counter, work);   \
+    } while (0)
+        if (work) MCPT_TRAVERSE_UP(true, 2);
+        else if (lc.traverse_occ >= 4) MCPT_TRAVERSE_UP(false, 4);
+        else if (lc.traverse_occ == 3) MCPT_TRAVERSE_UP(false, 3);
+        else MCPT_TRAVERSE_UP(false, 2);
+#undef MCPT_TRAVERSE_UP
+        lc.count();
+        return;
     }
     if (S.u_nodes && S.persistent) {
 #define MCPT_TRAVERSE_U(COUNT, MINB)                                                                                              \

@@ -147,6 +147,11 @@ struct DevScene {
     // |fwd * inv - 1| * (|O| + distance). Every box of the unified tree is therefore padded PER RAY by
     // u_pad_rel * (|O|_1 + u_radius) + u_pad_abs (both bounds computed at upload from the matrices themselves).
     float u_pad_rel, u_pad_abs, u_radius;
+    // Pooled leaf tests of the unified walk (MCPT_OPT_LEAF_POOL, k_traverse_unified_pooled): u_pool > 0 = the number of queued
+    // (ray, leaf) items at which a warp runs a round of exact tests. A candidate is ranked by a 64-bit key: distance bits,
+    // then (u_slot_max - leaf slot of the primitive) << u_key_shift | (u_rank_max - (rank + 1)) << 1 | candidate number --
+    // offer()'s order (intersect.cuh). 0: the upload found that the three fields do not fit 32 bits, or the option is off.
+    int32_t u_pool, u_key_shift, u_slot_max, u_rank_max;
     const DevLight* lights;    // next-event estimation: the quads that are sampled directly (null: none)
     int32_t n_lights;
     int32_t u_smem_nodes;      // the first N nodes of u_nodes are staged in shared memory (the top part is stored in

@@ -169,3 +169,74 @@ def test_edge_meshes_in_the_unified_tree(ctx):
             got = _trace(ctx, desc, ro, rd, unified)
             assert len(compare_hits(got, ref)) == 0, unified
     assert (ref["tri_index"] >= 0).sum() > 500
+
+
+def _trace_pool(ctx, desc, ro, rd, trigger):
+    ctx.set_option(capi.OPT_LEAF_POOL, trigger)
+    try:
+        ctx.upload_scene(desc)
+        return ctx.trace_rays(ro, rd)
+    finally:
+        ctx.set_option(capi.OPT_LEAF_POOL, LEAF_POOL_DEFAULT)
+
+
+LEAF_POOL_DEFAULT = 0
+
+
+@pytest.mark.parametrize("trigger", [1, 8, 16, 32])
+def test_pooled_leaf_tests_find_the_same_records(ctx, trigger):
+    """MCPT_OPT_LEAF_POOL: a lane that reaches a leaf of the unified tree queues a (ray, leaf) item and walks on, the warp
+    runs the queued exact tests 32 at a time, the closest hit of a ray is kept by atomicMin on a key that encodes
+    offer()'s order. Same tests in another order with the same ranking: the records are the same bits as with one test
+    per lane, on triangles (with and without uploaded trees, instanced meshes) and on analytic primitives (repo scene 8,
+    whose tree is large enough for the unified walk)."""
+    cases = []
+    s, o = both("mesh", n_meshes=4, tris_log2=12)
+    ro, rd = random_rays(o.prim_data(), 300_000, seed=61, clip=150.0)
+    cases.append(("meshes", o.scene_desc(), o, ro, rd))
+    cases.append(("meshes without host trees", s.desc(mesh_trees=False), None, ro, rd))
+    s2, o2 = _instanced_scene()
+    ro2, rd2 = random_rays(o2.prim_data(), 200_000, seed=62, clip=1200.0)
+    cases.append(("instances", o2.scene_desc(), o2, ro2, rd2))
+    s8, o8 = both(8)
+    ro8, rd8 = random_rays(o8.prim_data(), 200_000, seed=63)
+    iv, ipv = capi.default_camera(320, 180)
+    o8.set_uniforms(8, 1.0, DATE, 0, iv, ipv)
+    co, cd = camera_rays(o8, 320, 180)
+    cases.append(("scene 8", o8.scene_desc(), o8, np.concatenate([ro8, co]), np.concatenate([rd8, cd])))
+    for name, desc, orc, a, b in cases:
+        plain = _trace_pool(ctx, desc, a, b, 0)
+        pooled = _trace_pool(ctx, desc, a, b, trigger)
+        assert pooled.tobytes() == plain.tobytes(), name
+        assert (plain["index"] >= 0).sum() > 10_000, name
+        if orc is not None and trigger == 16:
+            ref = orc.trace(a, b)
+            assert len(compare_hits(pooled, ref)) == 0, name
+            assert np.array_equal(pooled["dist"].view(np.uint32), ref["dist"].view(np.uint32)), name
+
+
+@pytest.mark.parametrize("kind,kw,bounces,ior", [("mesh", dict(n_meshes=4, tris_log2=10), 8, 1.5), (8, {}, 9, 1.0), (3, {}, 9, 1.5)])
+def test_pooled_leaf_tests_render_the_same_sums(kind, kw, bounces, ior):
+    """... and so are the accumulated sums, ray and segment counts of a render (interior rays and, on analytic scenes, the
+    fused exit included). Scene 3 has fewer than 256 leaves: the option changes nothing there."""
+    s, o = both(kind, **kw)
+    iv, ipv = capi.default_camera(240, 135)
+    out = {}
+    for name, trigger in (("plain", 0), ("pooled", 16), ("pooled at once", 1)):
+        c = Context(0)
+        try:
+            c.set_option(capi.OPT_LEAF_POOL, trigger)
+            c.set_option(capi.OPT_PASSES_PER_BATCH, 3)
+            c.upload_scene(s)
+            c.resize(240, 135)
+            c.set_camera(iv, ipv)
+            c.set_params(nb_bounces=bounces, refract_ind=ior, date=float(DATE))
+            c.render(0, 5)
+            out[name] = (c.read_accum(), c.stats())
+        finally:
+            c.close()
+    base, st = out["plain"]
+    assert base[..., :3].mean() > 0.005 and st["rays"] > 1.2 * st["paths"]
+    for name in ("pooled", "pooled at once"):
+        assert np.array_equal(base, out[name][0]), name
+        assert out[name][1]["rays"] == st["rays"] and out[name][1]["segments"] == st["segments"], name
