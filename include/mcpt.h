@@ -124,7 +124,9 @@ enum {
                                       noise at equal spp where lights are small; the bounce rays are unchanged.
                                       Default 0 (the reference's estimator, bit-level parity). */
     MCPT_OPT_FLAT_POOL = 14,       /* scenes of <= 16 primitives, bounces after the first: 1 = a warp pools the exact
-                                      tests of 64 rays per primitive type and runs them 32 at a time (default),
+                                      tests of 64 rays per primitive type and runs them 32 at a time, 2 = ... and
+                                      copies the next 64 rays into shared memory with cp.async while it does so
+                                      (default; falls back to 1 where four CTAs of it would not fit one SM),
                                       0 = the warp-coherent walk of the first bounce everywhere. Set before
                                       mcpt_upload_scene. Same records. */
     MCPT_OPT_LEAF_POOL = 15        /* scenes traced through the unified world-space tree (meshes, large trees): N > 0 =

@@ -847,6 +847,15 @@ static int upload_scene_impl(mcpt_ctx* c, const mcpt_scene_desc* d) {
     S.flat = flat.empty() ? nullptr : d_flat;
     S.n_flat = int(flat.size());
     S.flat_pool = c->opt_flat_pool;
+    {
+        int per_type[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+        for (const DevNode& nd : flat) {
+            int prim;
+            std::memcpy(&prim, &nd.lo.w, sizeof(int));
+            if (prim >= 0 && prim < d->n_prims && prims[prim].type >= 0 && prims[prim].type < 8) ++per_type[prims[prim].type];
+        }
+        S.flat_max_type = std::max(1, *std::max_element(per_type, per_type + 8));
+    }
     S.top_depth = td;
     S.n_prims = d->n_prims;
     S.n_meshes = d->n_meshes;

@@ -859,9 +859,27 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse_unified_pooled(DevSce
 #endif
 constexpr int kPoolR = MCPT_POOL_R;
 constexpr int kPoolSlots = 32 * kPoolR;
-// per warp: ray origins (+ slack), directions, keys, payloads, items
-MCPT_DEV size_t pool_bytes_per_warp(int n_flat) { return size_t(kPoolSlots) * (16 + 16 + 8 + 16) + size_t(kPoolSlots) * size_t(n_flat) * 2; }
-static inline size_t pool_bytes_per_warp_host(int n_flat) { return size_t(kPoolSlots) * (16 + 16 + 8 + 16) + size_t(kPoolSlots) * size_t(n_flat) * 2; }
+// per warp: ray origins (+ slack) and directions (two buffers of them when the next tile's rays are copied in asynchronously),
+// payloads, keys, items of one primitive type (at most max_type list entries hold primitives of one type)
+__host__ __device__ inline size_t pool_bytes_per_warp(int max_type, bool async) {
+    const size_t b = size_t(kPoolSlots) * ((async ? 2 : 1) * (16 + 16) + 16 + 8) + size_t(kPoolSlots) * size_t(max_type) * 2;
+    return (b + 15) & ~size_t(15);
+}
+
+#ifndef MCPT_CP_ASYNC_CA
+#define MCPT_CP_ASYNC_CA 0  // 1: through L1 (.ca). Measured: config 2 6172 against 6298 Msamples/s with .cg (direct loads: 6151) -- the rays are read once
+#endif
+// 16 bytes global -> shared without a register in between (LDGSTS); completion: cp_async_wait_all of the issuing thread
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gsrc) {
+    const uint32_t d = static_cast<uint32_t>(__cvta_generic_to_shared(smem_dst));
+#if MCPT_CP_ASYNC_CA
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+#else
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
+#endif
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 struct PoolCand {
     float a1, a2;
@@ -869,7 +887,10 @@ struct PoolCand {
     bool c1, c2;
 };
 
-template <bool COUNT, int MINB, bool EXIT>
+// ASYNC: the rays of tile t + 1 are copied into a second pair of ray buffers with cp.async while tile t is tested (their queue
+// entries are loaded at the top of tile t, the copies are issued after its cull), so that no warp waits for a ray load
+// between two tiles (ncu before: 29 % of the stall samples of this kernel sat on those loads, 68 % of the issue slots busy).
+template <bool COUNT, int MINB, bool EXIT, bool ASYNC>
 __global__ void __launch_bounds__(kBlock, MINB) k_traverse_flat_pooled(DevScene S, Wavefront wf, QueueIn qin, HitSink sink,
                                                                         unsigned long long* ray_counter, unsigned long long* work) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -891,26 +912,56 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse_flat_pooled(DevScene 
     }
     __syncthreads();
     const uint32_t lane = threadIdx.x & 31u, warp = threadIdx.x >> 5;
-    unsigned char* wbase = smem_raw + ((size_t(S.smem_bytes) + 15) & ~size_t(15)) + size_t(warp) * ((pool_bytes_per_warp(n) + 15) & ~size_t(15));
-    float4* rayO = reinterpret_cast<float4*>(wbase);
-    float4* rayD = rayO + kPoolSlots;
-    float4* pay = rayD + kPoolSlots;
+    unsigned char* wbase = smem_raw + ((size_t(S.smem_bytes) + 15) & ~size_t(15)) + size_t(warp) * pool_bytes_per_warp(S.flat_max_type, ASYNC);
+    float4* ray_buf = reinterpret_cast<float4*>(wbase);   // [buffer][O | D][slot]
+    float4* pay = ray_buf + (ASYNC ? 4 : 2) * kPoolSlots;
     unsigned long long* keys = reinterpret_cast<unsigned long long*>(pay + kPoolSlots);
     unsigned short* items = reinterpret_cast<unsigned short*>(keys + kPoolSlots);
     const unsigned long long key_none = (static_cast<unsigned long long>(__float_as_uint(MCPT_FLT_MAX)) << 32) | 0xffffffffull;
     Work wk;
     const uint32_t tile_rays = kBlock * kPoolR;
-    for (uint32_t tile = 0; tile * tile_rays < len; ++tile) {
-        const uint32_t wfirst = tile * tile_rays + warp * kPoolSlots;
-        // ---- phase 1: load kPoolR rays per lane, cull them against the whole list
-        uint32_t pid[kPoolR], mask[kPoolR];
-        bool valid[kPoolR];
+    uint32_t pidn[kPoolR];
+    bool validn[kPoolR];
+    if (ASYNC) {  // the first tile's rays
 #pragma unroll
         for (int j = 0; j < kPoolR; ++j) {
             const uint32_t slot = uint32_t(j) * 32u + lane;
-            valid[j] = queue_item(qin, wfirst + slot, len, pid[j]);
+            validn[j] = queue_item(qin, warp * kPoolSlots + slot, len, pidn[j]);
+            if (validn[j]) {
+                const PathSector* src = wf.sec(pidn[j], 0);
+                cp_async16(ray_buf + slot, &src->a);
+                cp_async16(ray_buf + kPoolSlots + slot, &src->b);
+            }
+        }
+        cp_async_commit();
+    }
+    for (uint32_t tile = 0; tile * tile_rays < len; ++tile) {
+        const uint32_t wfirst = tile * tile_rays + warp * kPoolSlots;
+        float4* rayO = ray_buf + (ASYNC ? (tile & 1u) * 2u * kPoolSlots : 0u);
+        float4* rayD = rayO + kPoolSlots;
+        // ---- phase 1: kPoolR rays per lane, culled against the whole list
+        uint32_t pid[kPoolR], mask[kPoolR];
+        bool valid[kPoolR];
+        if (ASYNC) {
+#pragma unroll
+            for (int j = 0; j < kPoolR; ++j) {
+                pid[j] = pidn[j];
+                valid[j] = validn[j];
+                // queue entries of the next tile: in flight during the cull
+                validn[j] = queue_item(qin, wfirst + tile_rays + uint32_t(j) * 32u + lane, len, pidn[j]);
+            }
+            cp_async_wait_all();
+        }
+#pragma unroll
+        for (int j = 0; j < kPoolR; ++j) {
+            const uint32_t slot = uint32_t(j) * 32u + lane;
             float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
-            if (valid[j]) wf.load_ray(pid[j], o4, d4);
+            if (ASYNC) {
+                if (valid[j]) o4 = rayO[slot], d4 = rayD[slot];
+            } else {
+                valid[j] = queue_item(qin, wfirst + slot, len, pid[j]);
+                if (valid[j]) wf.load_ray(pid[j], o4, d4);
+            }
             const f3 O = mk3(o4.x, o4.y, o4.z), D = mk3(d4.x, d4.y, d4.z);
             const float dl = sqrtf(D.x * D.x + D.y * D.y + D.z * D.z);
             const bool ok = valid[j] && (dl > 0.0f) && (dl < FLT_MAX);
@@ -929,6 +980,19 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse_flat_pooled(DevScene 
             rayO[slot] = make_float4(O.x, O.y, O.z, slack);
             rayD[slot] = make_float4(D.x, D.y, D.z, 0.0f);
             keys[slot] = key_none;
+        }
+        if (ASYNC) {  // the next tile's rays into the other pair of buffers (last read in the tile before this one)
+            float4* nO = ray_buf + ((tile & 1u) ^ 1u) * 2u * kPoolSlots;
+#pragma unroll
+            for (int j = 0; j < kPoolR; ++j) {
+                const uint32_t slot = uint32_t(j) * 32u + lane;
+                if (validn[j]) {
+                    const PathSector* src = wf.sec(pidn[j], 0);
+                    cp_async16(nO + slot, &src->a);
+                    cp_async16(nO + kPoolSlots + slot, &src->b);
+                }
+            }
+            cp_async_commit();
         }
         __syncwarp();
         // ---- phase 2: the items of one primitive type at a time, 32 per round
@@ -1066,10 +1130,18 @@ static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefro
         // after the first bounce: exact tests pooled per warp and primitive type (k_traverse_flat_pooled). Interior rays keep
         // the sequential walk: they start inside a primitive whose far side bounds the search at once (measured: config 2
         // 1.81 vs 1.95 ms per step, scene 2 1.23 vs 1.28, scene 4 0.73 vs 0.76)
-        const size_t smem = ((size_t(S.smem_bytes) + 15) & ~size_t(15)) + (kBlock / 32) * ((pool_bytes_per_warp_host(S.n_flat) + 15) & ~size_t(15));
+        const size_t base = (size_t(S.smem_bytes) + 15) & ~size_t(15);
+        const size_t smem_async = base + (kBlock / 32) * pool_bytes_per_warp(S.flat_max_type, true);
+        const size_t smem_plain = base + (kBlock / 32) * pool_bytes_per_warp(S.flat_max_type, false);
         static bool once = false;
-        if (!once) once = cudaFuncSetAttribute(k_traverse_flat_pooled<COUNT, MINB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess;
-        k_traverse_flat_pooled<COUNT, MINB, false><<<grid, kBlock, smem, lc.stream>>>(S, wf, qin, sink, ray_counter, work);
+        if (!once)
+            once = cudaFuncSetAttribute(k_traverse_flat_pooled<COUNT, MINB, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess &&
+                   cudaFuncSetAttribute(k_traverse_flat_pooled<COUNT, MINB, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess;
+        // the second pair of ray buffers only where MINB CTAs of it still fit one SM (228 KB, 1 KB reserved per CTA)
+        if (S.flat_pool >= 2 && MINB * (smem_async + 1024 + 64) <= size_t(228) * 1024)
+            k_traverse_flat_pooled<COUNT, MINB, false, true><<<grid, kBlock, smem_async, lc.stream>>>(S, wf, qin, sink, ray_counter, work);
+        else
+            k_traverse_flat_pooled<COUNT, MINB, false, false><<<grid, kBlock, smem_plain, lc.stream>>>(S, wf, qin, sink, ray_counter, work);
     } else if (S.n_flat > 0)
         MCPT_TRAVERSE(true, false, false);
     else if (S.n_meshes == 0) {

@@ -12,7 +12,9 @@
 // (Measured and dropped: prefetch.global.L2 of the next path's state at the end of an iteration, +3 % time;
 // a software pipeline that requests the next path's queue entry and sectors before the current path is
 // shaded: +2..9 % time at 64 or 80 registers -- the gathers are limited by DRAM efficiency on scattered
-// 32-byte sectors (45-54 % of peak), not by exposed latency. Filing the rays of the next bounce in two
+// 32-byte sectors (45-54 % of peak), not by exposed latency; the same pipeline through shared memory with cp.async
+// (hit and radiance sectors of every thread's next path as four 16-byte LDGSTS, no registers): TWICE the time (C2 7.8 ->
+// 15.4 ms per step, scene 8 12.4 -> 30.9) -- a 32-byte sector then costs two requests to the L2. Filing the rays of the next bounce in two
 // classes -- leaving upwards / downwards -- at the two ends of the queue region: the flat traversal got 9 %
 // faster on warps of one class (C2 11.6 -> 10.6 ms per step), but the hit queue then walks the path slots
 // in two sparser runs and this kernel lost more through DRAM locality (7.8 -> 9.2 ms).)

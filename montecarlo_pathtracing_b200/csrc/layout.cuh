@@ -126,6 +126,7 @@ struct DevScene {
     const DevNode* flat;       // n_flat leaf boxes (aux0 = primitive id) when the scene is small, else null
     int32_t n_flat;            // > 0 selects the warp-coherent flat walk
     int32_t flat_pool;         // 1: after the first bounce the flat walk pools its exact tests per warp and primitive type
+    int32_t flat_max_type;     // the largest number of list entries that hold primitives of one type (sizes the item list)
     int32_t top_depth;
     int32_t n_prims;
     int32_t n_meshes;

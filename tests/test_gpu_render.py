@@ -366,7 +366,8 @@ def test_pooled_flat_walk_finds_the_same_records(kind, bounces, ior):
     s, o = both(kind)
     iv, ipv = capi.default_camera(240, 135)
     out = {}
-    for name, opts in (("pooled", {capi.OPT_FLAT_POOL: 1}), ("lockstep", {capi.OPT_FLAT_POOL: 0}), ("tree", {capi.OPT_FLAT_WALK: 0})):
+    for name, opts in (("pooled", {capi.OPT_FLAT_POOL: 1}), ("pooled, async ray copies", {capi.OPT_FLAT_POOL: 2}), ("lockstep", {capi.OPT_FLAT_POOL: 0}),
+                       ("tree", {capi.OPT_FLAT_WALK: 0})):
         c = Context(0)
         try:
             for k, v in opts.items():
@@ -382,6 +383,6 @@ def test_pooled_flat_walk_finds_the_same_records(kind, bounces, ior):
             c.close()
     base, st = out["pooled"]
     assert base[..., :3].mean() > 0.01 and st["rays"] > 2 * st["paths"]
-    for name in ("lockstep", "tree"):
+    for name in ("pooled, async ray copies", "lockstep", "tree"):
         assert np.array_equal(base, out[name][0]), name
         assert out[name][1]["rays"] == st["rays"] and out[name][1]["segments"] == st["segments"], name
