@@ -91,10 +91,9 @@ __device__ __forceinline__ SmemScene stage_scene(const DevScene& S, unsigned cha
 // again; the path starts with attenuation 0.8 and total 0 (:105-107).
 __global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam, Wavefront wf, int first_pass, int n_passes,
                                                     uint32_t npix) {
-    const uint64_t total = uint64_t(npix) * uint64_t(n_passes);
-    for (uint64_t p = uint64_t(blockIdx.x) * blockDim.x + threadIdx.x; p < total; p += uint64_t(gridDim.x) * blockDim.x) {
-        const uint32_t k = uint32_t(p / npix);
-        const uint32_t pix = uint32_t(p - uint64_t(k) * npix);
+    // the camera ray of a pixel is the same in every pass (the reference's vertex shader does not see the pass): computed
+    // once, stored n_passes times (one thread per path spent more time on the index arithmetic than on its store)
+    for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
         const int x = int(pix % uint32_t(prm.width));
         const int y = int(pix / uint32_t(prm.width));
         const float u = (float(x) + 0.5f) / float(prm.width);
@@ -112,14 +111,14 @@ __global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam
         // attenuation 0.8, total 0 and the RNG seed of a fresh path are implied (k_shade first bounce,
         // k_accumulate): nothing else is initialised here. (Leaving out the origin too -- it is the
         // camera's for every primary ray -- saved 32 B per path and no time: measured, dropped.)
-        wf.store_ray(p, make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f), make_float4(dir.x, dir.y, dir.z, 0.0f));
+        const float4 o4 = make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f), d4 = make_float4(dir.x, dir.y, dir.z, 0.0f);
+        for (int k = 0; k < n_passes; ++k) wf.store_ray(uint64_t(k) * npix + pix, o4, d4);
     }
 }
 
 void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,
                    int n_passes, uint32_t npix) {
-    uint64_t total = uint64_t(npix) * uint64_t(n_passes);
-    k_raygen<<<grid_for(lc, total, 16), kBlock, 0, lc.stream>>>(prm, cam, wf, first_pass, n_passes, npix);
+    k_raygen<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(prm, cam, wf, first_pass, n_passes, npix);
     lc.count();
 }
 

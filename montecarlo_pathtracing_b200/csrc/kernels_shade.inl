@@ -391,6 +391,9 @@ void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& 
 }
 
 // --------------------------------------------------------------- accumulate
+#ifndef MCPT_ACC_UNROLL
+#define MCPT_ACC_UNROLL 4
+#endif
 // glBlendFunc(GL_ONE, GL_ONE) into the RGB32F target, one draw per pass in pass
 // order (montecarlo.cpp:450-466): accum = ((accum + r0) + r1) + ...
 // The value random_path returns is read off the path's final state: `total` when the path ended
@@ -401,26 +404,37 @@ __global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __r
                                                         int n_passes, uint32_t batch) {
     for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
         float4 a = accum[pix];
-        for (int k = 0; k < n_passes; ++k) {
-            const uint64_t p = uint64_t(k) * npix + pix;
-            float4 a4, t4;
-            wf.load_rad(p, a4, t4);
-            const uint32_t tag = __float_as_uint(a4.w);
-            f3 r;
-            if (tag == 2u * batch + 1u) {
-                r = mk3(t4.x, t4.y, t4.z);
-            } else {
-                f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
-                if (tag == 2u * batch) {
-                    total = mk3(t4.x, t4.y, t4.z);
-                    attenu = mk3(a4.x, a4.y, a4.z);
+        // kAccUnroll passes at a time: their radiance sectors are requested together, then the directions of the ones that
+        // escaped, and only then are they added -- in pass order (one pass per trip left 32 dependent round trips to DRAM
+        // per pixel: 0.65 ms per 33 M paths)
+        constexpr int kAccUnroll = MCPT_ACC_UNROLL;
+        for (int k0 = 0; k0 < n_passes; k0 += kAccUnroll) {
+            float4 a4[kAccUnroll], t4[kAccUnroll], d4[kAccUnroll];
+#pragma unroll
+            for (int j = 0; j < kAccUnroll; ++j)
+                if (k0 + j < n_passes) wf.load_rad(uint64_t(k0 + j) * npix + pix, a4[j], t4[j]);
+#pragma unroll
+            for (int j = 0; j < kAccUnroll; ++j)
+                if (k0 + j < n_passes && __float_as_uint(a4[j].w) != 2u * batch + 1u) d4[j] = wf.load_ray_d(uint64_t(k0 + j) * npix + pix);
+#pragma unroll
+            for (int j = 0; j < kAccUnroll; ++j) {
+                if (k0 + j >= n_passes) break;
+                const uint32_t tag = __float_as_uint(a4[j].w);
+                f3 r;
+                if (tag == 2u * batch + 1u) {
+                    r = mk3(t4[j].x, t4[j].y, t4[j].z);
+                } else {
+                    f3 total = mk3(0.0f, 0.0f, 0.0f), attenu = mk3(0.8f, 0.8f, 0.8f);
+                    if (tag == 2u * batch) {
+                        total = mk3(t4[j].x, t4[j].y, t4[j].z);
+                        attenu = mk3(a4[j].x, a4[j].y, a4[j].z);
+                    }
+                    r = sky(total, attenu, mk3(d4[j].x, d4[j].y, d4[j].z));
                 }
-                const float4 d4 = wf.load_ray_d(p);
-                r = sky(total, attenu, mk3(d4.x, d4.y, d4.z));
+                a.x += r.x;
+                a.y += r.y;
+                a.z += r.z;
             }
-            a.x += r.x;
-            a.y += r.y;
-            a.z += r.z;
         }
         accum[pix] = a;
     }
