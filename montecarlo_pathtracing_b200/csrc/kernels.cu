@@ -853,6 +853,10 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse_unified_pooled(DevSce
 // lost, profiles/README.md). What is given up is the shrinking tmax of the sequential walk: every passing box is
 // tested. The total order of offer() (intersect.cuh) -- smaller distance, then higher leaf slot, then the candidate
 // offered first -- is the order of the keys, so the records are the same bits.
+// (Measured and dropped, config 2 / scene 2 / scene 4 Msamples/s against 6314 / 2266 / 3881: the candidates of a round ranked without
+// atomics -- match.any on the ray slot, two REDUX.MIN over distance and tie bits, one plain compare with the stored key -- 5061 /
+// 1869 / 3116: MATCH.ANY costs far more than the compare-and-swap loop behind the 64-bit atomicMin; the exclusive prefix of the item
+// counts as six independent ballots instead of five dependent shuffles 6278 / 2284 / 3894: noise.)
 #ifndef MCPT_POOL_R
 #define MCPT_POOL_R 2
 #endif

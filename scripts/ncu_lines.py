@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Summarise an .ncu-rep per CUDA source line: executed warp instructions, stall samples.
 
-  python scripts/ncu_lines.py gpurun_out/prof.ncu-rep [--top 40] [--kernel-index 0]
+  python scripts/ncu_lines.py gpurun_out/prof.ncu-rep [--top 40] [--kernel-index 0] [--kernel-name REGEX]
 
 Reads `ncu --page source --csv --print-source cuda,sass` (needs -lineinfo at compile time and
 --import-source on at capture time) and prints the hottest source lines of one profiled launch.
@@ -15,7 +15,8 @@ def main():
     rep = sys.argv[1]
     top = int(sys.argv[sys.argv.index("--top") + 1]) if "--top" in sys.argv else 40
     kidx = int(sys.argv[sys.argv.index("--kernel-index") + 1]) if "--kernel-index" in sys.argv else 0
-    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"],
+    flt = ["-k", "regex:" + sys.argv[sys.argv.index("--kernel-name") + 1]] if "--kernel-name" in sys.argv else []
+    out = subprocess.run(["ncu", "-i", rep, *flt, "--page", "source", "--csv", "--print-source", "cuda,sass"],
                          capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
     # split into kernels: a kernel restarts when a (file, function) header pair repeats for the first file
