@@ -349,6 +349,7 @@ def main():
     ap.add_argument("--top-sah", type=int, default=1, help="1 = SAH-built top-level tree for the persistent walk, 0 = the reference's median-split topology")
     ap.add_argument("--flat-walk", type=int, default=1, help="1 = warp-coherent flat walk for scenes of <= 16 primitives, 0 = tree walk (persistent warps)")
     ap.add_argument("--unified", type=int, default=1, help="scenes with meshes: 1 = one world-space tree over the top level and every mesh instance, 0 = two-level walk")
+    ap.add_argument("--fused-raygen", type=int, default=-1, help="1 = the first traversal makes its camera rays itself, 0 = k_raygen, -1 = library default")
     ap.add_argument("--leaf-pool", type=int, default=-1, help="unified walk: N > 0 = leaf tests queued per warp and run 32 at a time once N items wait, 0 = per-lane leaf tests, -1 = library default")
     ap.add_argument("--flat-pool", type=int, default=2, help="scenes of <= 16 primitives: 1 = exact tests pooled per warp and primitive type after the first bounce, 0 = warp-coherent walk everywhere")
     ap.add_argument("--host-tree", type=int, default=0, help="mesh workloads: 1 = upload the reference's median-split mesh trees too (tie-break ranks = its leaf slots), 0 = no host tree at all")
@@ -393,6 +394,8 @@ def main():
     ctx.set_option(capi.OPT_FLAT_POOL, args.flat_pool)
     if args.leaf_pool >= 0:
         ctx.set_option(capi.OPT_LEAF_POOL, args.leaf_pool)
+    if args.fused_raygen >= 0:
+        ctx.set_option(capi.OPT_FUSED_RAYGEN, args.fused_raygen)
     ctx.set_option(capi.OPT_PERSISTENT, args.persistent)
     ctx.set_option(capi.OPT_REFILL_LANES, args.refill)
     # what upload_scene is given: with --host-tree 0 the mesh descriptors carry no BVH (the library builds its own
@@ -611,7 +614,7 @@ def main():
     mt = (m or {}).get("by_stage", {}).get("traverse")
     # the committed counters belong to the library's default option set; any tuning switch on the command line voids them
     default_opts = (args.unified == 1 and args.persistent == 1 and args.mesh_bvh == 1 and args.top_sah == 1 and args.flat_walk == 1 and
-                    args.flat_pool == 2 and args.leaf_pool == -1 and args.refill == 0 and args.occ == 0 and args.ppb == 0 and args.fast_math == 1 and not os.environ.get("MCPT_LIBRARY"))
+                    args.flat_pool == 2 and args.leaf_pool == -1 and args.fused_raygen == -1 and args.refill == 0 and args.occ == 0 and args.ppb == 0 and args.fast_math == 1 and not os.environ.get("MCPT_LIBRARY"))
     same_launches = bool(mt) and default_opts and mt["launches"] * n_prof == trav_launches
     roofline = {"kernel": "k_traverse_unified" if (s.nb_meshes and args.unified and args.persistent and args.mesh_bvh) else "k_traverse",
                 "bound": "issue", "unit": "Gwarp-inst/s", "peak": issue_peak,

@@ -129,13 +129,16 @@ enum {
                                       (default; falls back to 1 where four CTAs of it would not fit one SM),
                                       0 = the warp-coherent walk of the first bounce everywhere. Set before
                                       mcpt_upload_scene. Same records. */
-    MCPT_OPT_LEAF_POOL = 15        /* scenes traced through the unified world-space tree (meshes, large trees): N > 0 =
+    MCPT_OPT_LEAF_POOL = 15,       /* scenes traced through the unified world-space tree (meshes, large trees): N > 0 =
                                       a lane that reaches a leaf queues a (ray, leaf) item and walks on; the warp
                                       runs the exact tests of the queue 32 at a time once N items (1..32) wait, the
                                       closest hit of a ray ranked by a 64-bit key in shared memory
                                       (k_traverse_unified_pooled). 0 = every lane tests its own leaf (default:
                                       measured 3 .. 6 % faster, csrc/kernels.cu). Set before mcpt_upload_scene. Same
                                       records. */
+    MCPT_OPT_FUSED_RAYGEN = 16     /* 1 (default) = the first traversal of a batch computes the camera ray of every
+                                      path it takes (raytracer.vert's arithmetic) and stores it; 0 = a kernel of its
+                                      own writes all camera rays first. Same rays, same images. */
 };
 
 /* wavefront stages, in launch order inside one bounce */

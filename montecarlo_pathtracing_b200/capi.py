@@ -20,7 +20,7 @@ MCPT_OK = 0
 MCPT_E_INVALID, MCPT_E_CUDA, MCPT_E_NODEVICE, MCPT_E_NOMEM, MCPT_E_NCCL, MCPT_E_UNSUPPORTED = -1, -2, -3, -4, -5, -6
 PRIM_MESH, PRIM_SPHERE, PRIM_CUBE, PRIM_CYLINDER, PRIM_CONE, PRIM_ORIENTED_QUAD = range(6)
 DST_HOST_RGB32F, DST_HOST_RGBA8, DST_DEVICE_RGB32F, DST_DEVICE_RGBA8 = range(4)
-OPT_PASSES_PER_BATCH, OPT_SMEM_STAGING, OPT_FAST_MATH, OPT_MESH_BVH, OPT_PROFILE_STAGES, OPT_COUNT_WORK, OPT_FLAT_WALK, OPT_TRAVERSE_OCC, OPT_PERSISTENT, OPT_REFILL_LANES, OPT_TOP_SAH, OPT_TRACE_WALKER, OPT_UNIFIED, OPT_NEE, OPT_FLAT_POOL, OPT_LEAF_POOL = range(16)
+OPT_PASSES_PER_BATCH, OPT_SMEM_STAGING, OPT_FAST_MATH, OPT_MESH_BVH, OPT_PROFILE_STAGES, OPT_COUNT_WORK, OPT_FLAT_WALK, OPT_TRAVERSE_OCC, OPT_PERSISTENT, OPT_REFILL_LANES, OPT_TOP_SAH, OPT_TRACE_WALKER, OPT_UNIFIED, OPT_NEE, OPT_FLAT_POOL, OPT_LEAF_POOL, OPT_FUSED_RAYGEN = range(17)
 STAGE_NAMES = ("raygen", "traverse", "shade", "bvh_build", "traverse_interior", "shade_exit", "accumulate", "resolve")
 
 

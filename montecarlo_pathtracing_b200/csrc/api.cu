@@ -91,6 +91,7 @@ struct mcpt_ctx {
     int opt_traverse_occ = 0;  // 0 = auto
     int opt_count_work = 0;
     int opt_trace_walker = 0;  // mcpt_trace_rays: 0 = the production kernel (k_traverse), 1 = the reference-order walk (k_trace)
+    int opt_fused_raygen = 1;  // the first traversal of a batch makes its camera rays itself (no k_raygen launch)
     int opt_leaf_pool = 0;     // unified walk: > 0 = leaf tests queued per warp, a round of tests once this many items wait
     int opt_flat_pool = 2;     // flat scenes, bounces after the first: exact tests pooled per warp and primitive type
     int opt_nee = 0;           // next-event estimation on the emissive quads (a new estimator, off by default)
@@ -355,6 +356,7 @@ int mcpt_set_option(mcpt_ctx* c, int option, int value) {
             if (value < 0 || value > 2) return fail(c, MCPT_E_INVALID, "flat pool must be 0, 1 or 2");
             c->opt_flat_pool = value;
             return MCPT_OK;
+        case MCPT_OPT_FUSED_RAYGEN: c->opt_fused_raygen = value ? 1 : 0; return MCPT_OK;
         case MCPT_OPT_LEAF_POOL:
             if (value < 0 || value > 32) return fail(c, MCPT_E_INVALID, "leaf pool trigger must be 0 (off) or 1..32 items");
             c->opt_leaf_pool = value;

@@ -209,7 +209,10 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
             c->batch_gen = 1;
         }
         c->prm.batch = c->batch_gen;
-        {
+        // camera rays: by k_raygen, or (MCPT_OPT_FUSED_RAYGEN, default) by the first traversal itself -- it computes the ray of
+        // every slot it takes and stores it, so the ray sectors are the same afterwards and no kernel only writes them
+        const bool fused_raygen = c->opt_fused_raygen != 0;
+        if (!fused_raygen) {
             StageSpan sp(c, MCPT_STAGE_RAYGEN);
             launch_raygen(lc, c->prm, c->cam, c->wf, first_pass + b0, nb, npix);
         }
@@ -222,10 +225,14 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
         const int gmax = wavefront_grid_max(c);
         const QueueOut q_next{c->queue[0], c->counters + 0 * gmax, cap}, q_hit{c->queue[1], c->counters + 1 * gmax, cap},
             q_int{c->queue[2], c->counters + 2 * gmax, cap}, q_none{nullptr, nullptr, 0};
-        const QueueIn in_identity{nullptr, nullptr, slots, cap}, in_next{q_next.items, q_next.counts, 0, cap},
-            in_hit{q_hit.items, q_hit.counts, 0, cap}, in_int{q_int.items, q_int.counts, 0, cap};
+        QueueIn in_identity{nullptr, nullptr, slots, cap};
         const bool mc = (c->prm.mode == 0);
         const bool nee = mc && c->opt_nee && S.n_lights > 0;
+        // nothing reads a primary ray back except the fake sky (rays that hit nothing) -- unless the shading uses libm (it
+        // rebuilds E from the origin), a debug shader or next-event estimation runs: then every ray is stored
+        if (fused_raygen) in_identity.gen = RayGen{c->cam, c->prm.width, c->prm.height, npix, (mc && !nee && c->opt_fast_math) ? 2 : 1};
+        const QueueIn in_next{q_next.items, q_next.counts, 0, cap}, in_hit{q_hit.items, q_hit.counts, 0, cap},
+            in_int{q_int.items, q_int.counts, 0, cap};
         const QueueOut q_shadow{c->queue[3], c->counters + 3 * gmax, cap};
         const QueueIn in_shadow{q_shadow.items, q_shadow.counts, 0, cap};
         if (nee) CK(c, cudaMemsetAsync(c->nee.rec + 2 * c->nee.plane, 0, size_t(slots) * 32, c->stream));  // sums and densities of this batch

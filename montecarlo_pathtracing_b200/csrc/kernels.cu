@@ -89,29 +89,35 @@ __device__ __forceinline__ SmemScene stage_scene(const DevScene& S, unsigned cha
 // Dir_in is the barycentric interpolation, over the two triangles of the
 // full-screen strip, of the per-corner normalised directions; it is normalised
 // again; the path starts with attenuation 0.8 and total 0 (:105-107).
+MCPT_DEV void camera_ray(const CameraRays& cam, int width, int height, uint32_t pix, float4& o4, float4& d4) {
+    const int x = int(pix % uint32_t(width));
+    const int y = int(pix / uint32_t(width));
+    const float u = (float(x) + 0.5f) / float(width);
+    const float v = (float(y) + 0.5f) / float(height);
+    f3 d0 = mk3(cam.dir[0][0], cam.dir[0][1], cam.dir[0][2]);
+    f3 d1 = mk3(cam.dir[1][0], cam.dir[1][1], cam.dir[1][2]);
+    f3 d2 = mk3(cam.dir[2][0], cam.dir[2][1], cam.dir[2][2]);
+    f3 d3 = mk3(cam.dir[3][0], cam.dir[3][1], cam.dir[3][2]);
+    f3 dir;
+    if (u + v <= 1.0f)
+        dir = d0 * ((1.0f - u) - v) + d1 * u + d2 * v;
+    else
+        dir = d1 * (1.0f - v) + d2 * (1.0f - u) + d3 * ((u + v) - 1.0f);
+    dir = normalize3(dir);
+    // attenuation 0.8, total 0 and the RNG seed of a fresh path are implied (k_shade first bounce,
+    // k_accumulate): nothing else is initialised here. (Leaving out the origin too -- it is the
+    // camera's for every primary ray -- saved 32 B per path and no time: measured, dropped.)
+    o4 = make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f);
+    d4 = make_float4(dir.x, dir.y, dir.z, 0.0f);
+}
+
 __global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam, Wavefront wf, int first_pass, int n_passes,
                                                     uint32_t npix) {
     // the camera ray of a pixel is the same in every pass (the reference's vertex shader does not see the pass): computed
     // once, stored n_passes times (one thread per path spent more time on the index arithmetic than on its store)
     for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
-        const int x = int(pix % uint32_t(prm.width));
-        const int y = int(pix / uint32_t(prm.width));
-        const float u = (float(x) + 0.5f) / float(prm.width);
-        const float v = (float(y) + 0.5f) / float(prm.height);
-        f3 d0 = mk3(cam.dir[0][0], cam.dir[0][1], cam.dir[0][2]);
-        f3 d1 = mk3(cam.dir[1][0], cam.dir[1][1], cam.dir[1][2]);
-        f3 d2 = mk3(cam.dir[2][0], cam.dir[2][1], cam.dir[2][2]);
-        f3 d3 = mk3(cam.dir[3][0], cam.dir[3][1], cam.dir[3][2]);
-        f3 dir;
-        if (u + v <= 1.0f)
-            dir = d0 * ((1.0f - u) - v) + d1 * u + d2 * v;
-        else
-            dir = d1 * (1.0f - v) + d2 * (1.0f - u) + d3 * ((u + v) - 1.0f);
-        dir = normalize3(dir);
-        // attenuation 0.8, total 0 and the RNG seed of a fresh path are implied (k_shade first bounce,
-        // k_accumulate): nothing else is initialised here. (Leaving out the origin too -- it is the
-        // camera's for every primary ray -- saved 32 B per path and no time: measured, dropped.)
-        const float4 o4 = make_float4(cam.ori[0], cam.ori[1], cam.ori[2], 0.0f), d4 = make_float4(dir.x, dir.y, dir.z, 0.0f);
+        float4 o4, d4;
+        camera_ray(cam, prm.width, prm.height, pix, o4, d4);
         for (int k = 0; k < n_passes; ++k) wf.store_ray(uint64_t(k) * npix + pix, o4, d4);
     }
 }
@@ -167,6 +173,17 @@ __device__ __forceinline__ bool queue_item(const QueueIn& q, uint32_t i, uint32_
     return p < q.n_identity;
 }
 
+// the ray of path slot p: read from its ray sector, or -- first traversal of a batch with MCPT_OPT_FUSED_RAYGEN -- made here
+// and stored (k_raygen's arithmetic, so the same bits)
+__device__ __forceinline__ void fetch_ray(const Wavefront& wf, const QueueIn& q, uint32_t p, float4& o4, float4& d4) {
+    if (q.gen.on) {
+        camera_ray(q.gen.cam, q.gen.width, q.gen.height, p % q.gen.npix, o4, d4);
+        if (q.gen.on == 1) wf.store_ray(p, o4, d4);
+    } else {
+        wf.load_ray(p, o4, d4);
+    }
+}
+
 __device__ __forceinline__ void warp_append(uint32_t* s_count, const QueueOut& q, bool take, uint32_t p) {
     const uint32_t m = __ballot_sync(0xffffffffu, take);
     if (!m) return;
@@ -194,6 +211,8 @@ struct HitSink {
     int exit_mode;
     int flat_face;
     float refract_ind;
+    int store_miss;       // camera rays made by this traversal (RayGen::on == 2): a ray that hits nothing is stored here
+    float miss_ori[3];
 };
 
 template <bool EXIT>
@@ -216,6 +235,8 @@ __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, 
     if (hit || (valid && !sink.hitq.items)) {
         wf.store_hit(p, best.h.pl, best.h.prim, best.h.sub, D);
     }
+    if (sink.store_miss && valid && !hit)
+        wf.store_ray(p, make_float4(sink.miss_ori[0], sink.miss_ori[1], sink.miss_ori[2], 0.0f), make_float4(D.x, D.y, D.z, 0.0f));
     if (sink.hitq.items) warp_append(s_count, sink.hitq, hit, p);
 }
 
@@ -295,7 +316,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
                     first = __shfl_sync(0xffffffffu, first, 0);
                     if (!has_ray && queue_item(qin, first + __popc(freeable & below), len, p)) {
                         float4 o4, d4;
-                        wf.load_ray(p, o4, d4);
+                        fetch_ray(wf, qin, p, o4, d4);
                         walk_begin<WIDE>(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
                         has_ray = true;
                     }
@@ -314,7 +335,7 @@ __device__ __forceinline__ void traverse_persistent(const DevScene& S, const Sme
                 first = __shfl_sync(0xffffffffu, first, 0);
                 if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
                     float4 o4, d4;
-                    wf.load_ray(p, o4, d4);
+                    fetch_ray(wf, qin, p, o4, d4);
                     walk_begin<WIDE>(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
                     has_ray = true;
                 }
@@ -438,7 +459,7 @@ __device__ __forceinline__ void traverse_unified(const DevScene& S, const SmemSc
                 first = __shfl_sync(0xffffffffu, first, 0);
                 if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
                     float4 o4, d4;
-                    wf.load_ray(p, o4, d4);
+                    fetch_ray(wf, qin, p, o4, d4);
                     uwalk_begin(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
                     has_ray = true;
                 }
@@ -502,7 +523,7 @@ __global__ void __launch_bounds__(kBlock, MINB) k_traverse(DevScene S, Wavefront
         const bool valid = queue_item(qin, base + threadIdx.x, len, p);
         Best best;
         float4 o4 = make_float4(0, 0, 0, 0), d4 = make_float4(0, 0, 0, 0);
-        if (valid) wf.load_ray(p, o4, d4);
+        if (valid) fetch_ray(wf, qin, p, o4, d4);
         if (FLAT)
             scene_walk_flat<COUNT>(wk, S, sm, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z), false, valid, best);
         else if (valid)
@@ -703,7 +724,7 @@ __device__ __forceinline__ void traverse_unified_pooled(const DevScene& S, const
                 first = __shfl_sync(0xffffffffu, first, 0);
                 if (!has_ray && queue_item(qin, first + __popc(idle & below), len, p)) {
                     float4 o4, d4;
-                    wf.load_ray(p, o4, d4);
+                    fetch_ray(wf, qin, p, o4, d4);
                     uwalk_begin(w, S, mk3(o4.x, o4.y, o4.z), mk3(d4.x, d4.y, d4.z));
                     q.rayO[lane] = make_float4(o4.x, o4.y, o4.z, w.slack);
                     q.rayD[lane] = make_float4(d4.x, d4.y, d4.z, 0.0f);
@@ -1159,7 +1180,11 @@ static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefro
 
 void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const QueueOut& hitq,
                      const DevParams* exit_prm, unsigned long long* ray_counter, unsigned long long* work) {
-    HitSink sink{hitq, 0, 0, 1.0f};
+    HitSink sink{hitq, 0, 0, 1.0f, 0, {0.0f, 0.0f, 0.0f}};
+    if (qin.gen.on == 2) {
+        sink.store_miss = 1;
+        for (int i = 0; i < 3; ++i) sink.miss_ori[i] = qin.gen.cam.ori[i];
+    }
     if (exit_prm) {
         sink.exit_mode = 1;
         sink.flat_face = exit_prm->flat_face;

@@ -17,11 +17,21 @@ struct CameraRays {
 
 // A queue of path slots, split into one private region of `cap` entries per CTA of the wavefront
 // grid (see kernels.cu). items == nullptr as input: the identity over n_identity slots.
+// Camera rays made where they are consumed (MCPT_OPT_FUSED_RAYGEN): the first traversal of a batch computes the ray of
+// slot p itself (and stores it, so that every later stage finds the ray sector as k_raygen would have left it).
+struct RayGen {
+    CameraRays cam;
+    int32_t width, height;
+    uint32_t npix;
+    int32_t on;   // 1: the ray is stored where it is made; 2: only the rays that hit nothing are stored (by deliver(): the
+                  // fake sky of k_accumulate reads their direction), which is enough when nothing else reads a primary ray back
+};
 struct QueueIn {
     const uint32_t* items;
     const uint32_t* counts;  // entries in each CTA's region
     uint32_t n_identity;
     uint32_t cap;
+    RayGen gen;              // on != 0 (identity queues only): slot p's ray is the camera ray of pixel p % npix
 };
 struct QueueOut {
     uint32_t* items;  // nullptr: no queue

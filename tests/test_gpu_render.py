@@ -386,3 +386,33 @@ def test_pooled_flat_walk_finds_the_same_records(kind, bounces, ior):
     for name in ("pooled, async ray copies", "lockstep", "tree"):
         assert np.array_equal(base, out[name][0]), name
         assert out[name][1]["rays"] == st["rays"] and out[name][1]["segments"] == st["segments"], name
+
+
+@pytest.mark.parametrize("kind,kw,mode,fast", [(1, {}, 0, 1), ("c2", {}, 0, 0), (5, {}, 0, 1), (8, {}, 0, 1), ("mesh", dict(n_meshes=3, tris_log2=9), 0, 1),
+                                               (3, {}, 1, 1), (6, {}, 2, 0)])
+def test_camera_rays_made_by_the_first_traversal(kind, kw, mode, fast):
+    """MCPT_OPT_FUSED_RAYGEN: the first traversal of a batch computes (and stores) the camera ray of every path it takes
+    instead of reading what k_raygen wrote -- the same arithmetic, so sums, ray and segment counts are the same bits, on
+    the flat, the tree and the unified walk, in the debug modes and with libm shading (which reads the ray origin back)."""
+    s, o = both(kind, **kw)
+    w, h = 200, 117                      # not a multiple of the tile
+    iv, ipv = capi.default_camera(w, h)
+    out = {}
+    for fused in (1, 0):
+        c = Context(0)
+        try:
+            c.set_option(capi.OPT_FUSED_RAYGEN, fused)
+            c.set_option(capi.OPT_FAST_MATH, fast)
+            c.set_option(capi.OPT_PASSES_PER_BATCH, 3)
+            c.upload_scene(s)
+            c.resize(w, h)
+            c.set_camera(iv, ipv)
+            c.set_params(nb_bounces=6, refract_ind=1.5, date=float(DATE), mode=mode)
+            c.render(0, 5)
+            out[fused] = (c.read_accum(), c.stats())
+        finally:
+            c.close()
+    assert out[1][0][..., :3].mean() > 0.005
+    assert np.array_equal(out[1][0], out[0][0])
+    assert out[1][1]["rays"] == out[0][1]["rays"] and out[1][1]["segments"] == out[0][1]["segments"]
+    assert out[1][1]["launches"] < out[0][1]["launches"]
