@@ -59,6 +59,8 @@ struct mcpt_ctx {
     float4* accum = nullptr;
     bool accum_owned = false;
     size_t accum_bytes = 0;
+    float4* cam_dirs = nullptr;   // camera direction of every pixel (MCPT_OPT_FUSED_RAYGEN), rebuilt by every mcpt_render
+    size_t cam_dirs_px = 0;
     void* resolve_tmp = nullptr;  // device staging for host-destination resolves
     size_t resolve_tmp_bytes = 0;
     char* trace_wf = nullptr;     // ray + hit sectors of mcpt_trace_rays through the production kernel (grow-only)
@@ -300,6 +302,7 @@ int mcpt_destroy(mcpt_ctx* c) {
     trim_cache(c);
     if (c->accum_owned && c->accum) cudaFree(c->accum);
     if (c->dev_stats) cudaFree(c->dev_stats);
+    if (c->cam_dirs) cudaFree(c->cam_dirs);
     if (c->resolve_tmp) cudaFree(c->resolve_tmp);
     if (c->trace_wf) cudaFree(c->trace_wf);
     for (auto& sp : c->spans) {

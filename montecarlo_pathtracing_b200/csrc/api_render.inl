@@ -200,6 +200,20 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
     const DevScene& S = c->scene;
     unsigned long long* work = c->opt_count_work ? c->dev_stats + 2 : nullptr;
 
+    if (c->opt_fused_raygen) {
+        // the camera direction of every pixel, once per call: the first traversal of every batch reads it (16 B per ray out
+        // of the L2) instead of evaluating the vertex shader's interpolation per path
+        if (c->cam_dirs_px < npix) {
+            if (c->cam_dirs) cudaFree(c->cam_dirs);
+            c->cam_dirs = nullptr;
+            c->cam_dirs_px = 0;
+            void* p = nullptr;
+            if (cudaMalloc(&p, size_t(npix) * sizeof(float4)) != cudaSuccess) return fail(c, MCPT_E_NOMEM, "camera direction table");
+            c->cam_dirs = static_cast<float4*>(p);
+            c->cam_dirs_px = npix;
+        }
+        launch_camera_table(lc, c->prm, c->cam, c->cam_dirs, npix);
+    }
     for (int b0 = 0; b0 < n_passes; b0 += ppb) {
         const int nb = std::min(ppb, n_passes - b0);
         const uint32_t slots = npix * uint32_t(nb);
@@ -230,7 +244,7 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
         const bool nee = mc && c->opt_nee && S.n_lights > 0;
         // nothing reads a primary ray back except the fake sky (rays that hit nothing) -- unless the shading uses libm (it
         // rebuilds E from the origin), a debug shader or next-event estimation runs: then every ray is stored
-        if (fused_raygen) in_identity.gen = RayGen{c->cam, c->prm.width, c->prm.height, npix, (mc && !nee && c->opt_fast_math) ? 2 : 1};
+        if (fused_raygen) in_identity.gen = RayGen{c->cam, c->cam_dirs, c->prm.width, c->prm.height, npix, 1.0f / float(npix), (mc && !nee && c->opt_fast_math) ? 2 : 1};
         const QueueIn in_next{q_next.items, q_next.counts, 0, cap}, in_hit{q_hit.items, q_hit.counts, 0, cap},
             in_int{q_int.items, q_int.counts, 0, cap};
         const QueueOut q_shadow{c->queue[3], c->counters + 3 * gmax, cap};

@@ -122,6 +122,19 @@ __global__ void __launch_bounds__(kBlock) k_raygen(DevParams prm, CameraRays cam
     }
 }
 
+__global__ void __launch_bounds__(kBlock) k_camera_table(DevParams prm, CameraRays cam, float4* __restrict__ dirs, uint32_t npix) {
+    for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
+        float4 o4, d4;
+        camera_ray(cam, prm.width, prm.height, pix, o4, d4);
+        dirs[pix] = d4;
+    }
+}
+
+void launch_camera_table(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, float4* dirs, uint32_t npix) {
+    k_camera_table<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(prm, cam, dirs, npix);
+    lc.count();
+}
+
 void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,
                    int n_passes, uint32_t npix) {
     k_raygen<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(prm, cam, wf, first_pass, n_passes, npix);
@@ -177,7 +190,13 @@ __device__ __forceinline__ bool queue_item(const QueueIn& q, uint32_t i, uint32_
 // and stored (k_raygen's arithmetic, so the same bits)
 __device__ __forceinline__ void fetch_ray(const Wavefront& wf, const QueueIn& q, uint32_t p, float4& o4, float4& d4) {
     if (q.gen.on) {
-        camera_ray(q.gen.cam, q.gen.width, q.gen.height, p % q.gen.npix, o4, d4);
+        // pixel = p mod npix with the pass index (< 64) estimated in fp32 and corrected by one either way
+        const uint32_t k = __float2uint_rz(__uint2float_rz(p) * q.gen.inv_npix);
+        uint32_t pix = p - k * q.gen.npix;
+        if (int32_t(pix) < 0) pix += q.gen.npix;
+        else if (pix >= q.gen.npix) pix -= q.gen.npix;
+        o4 = make_float4(q.gen.cam.ori[0], q.gen.cam.ori[1], q.gen.cam.ori[2], 0.0f);
+        d4 = __ldg(q.gen.dirs + pix);
         if (q.gen.on == 1) wf.store_ray(p, o4, d4);
     } else {
         wf.load_ray(p, o4, d4);

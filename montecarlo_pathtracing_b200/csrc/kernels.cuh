@@ -21,8 +21,11 @@ struct CameraRays {
 // slot p itself (and stores it, so that every later stage finds the ray sector as k_raygen would have left it).
 struct RayGen {
     CameraRays cam;
+    const float4* dirs;   // the camera direction of every pixel (launch_camera_table: npix entries, L2 resident, made once per
+                          // mcpt_render -- the same for every pass); the origin is cam.ori
     int32_t width, height;
     uint32_t npix;
+    float inv_npix;
     int32_t on;   // 1: the ray is stored where it is made; 2: only the rays that hit nothing are stored (by deliver(): the
                   // fake sky of k_accumulate reads their direction), which is enough when nothing else reads a primary ray back
 };
@@ -50,6 +53,8 @@ struct LaunchCfg {
     }
 };
 
+// the table RayGen::dirs points to (k_raygen's arithmetic per pixel)
+void launch_camera_table(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, float4* dirs, uint32_t npix);
 void launch_raygen(const LaunchCfg& lc, const DevParams& prm, const CameraRays& cam, Wavefront wf, int first_pass,
                    int n_passes, uint32_t npix);
 // hitq.items != null: rays that hit something are appended to hitq; the others are already settled
