@@ -242,8 +242,9 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
         QueueIn in_identity{nullptr, nullptr, slots, cap};
         const bool mc = (c->prm.mode == 0);
         const bool nee = mc && c->opt_nee && S.n_lights > 0;
-        // nothing reads a primary ray back except the fake sky (rays that hit nothing) -- unless the shading uses libm (it
-        // rebuilds E from the origin), a debug shader or next-event estimation runs: then every ray is stored
+        // nothing reads a primary ray back except the fake sky (paths that were never shaded: k_accumulate then takes the
+        // direction from the camera table) -- unless the shading uses libm (it rebuilds E from the origin), a debug shader or
+        // next-event estimation runs: then every ray is stored
         if (fused_raygen) in_identity.gen = RayGen{c->cam, c->cam_dirs, c->prm.width, c->prm.height, npix, 1.0f / float(npix), (mc && !nee && c->opt_fast_math) ? 2 : 1};
         const QueueIn in_next{q_next.items, q_next.counts, 0, cap}, in_hit{q_hit.items, q_hit.counts, 0, cap},
             in_int{q_int.items, q_int.counts, 0, cap};
@@ -292,7 +293,7 @@ int mcpt_render(mcpt_ctx* c, int first_pass, int n_passes) {
             if (nee)
                 launch_accumulate_nee(lc, c->wf, c->nee, c->accum, npix, nb, c->prm.batch);
             else
-                launch_accumulate(lc, c->wf, c->accum, npix, nb, c->prm.batch);
+                launch_accumulate(lc, c->wf, c->accum, npix, nb, c->prm.batch, in_identity.gen.on == 2 ? c->cam_dirs : nullptr);
         }
         c->paths_started += slots;
     }

@@ -230,8 +230,6 @@ struct HitSink {
     int exit_mode;
     int flat_face;
     float refract_ind;
-    int store_miss;       // camera rays made by this traversal (RayGen::on == 2): a ray that hits nothing is stored here
-    float miss_ori[3];
 };
 
 template <bool EXIT>
@@ -254,8 +252,6 @@ __device__ __forceinline__ void deliver(const DevScene& S, const Wavefront& wf, 
     if (hit || (valid && !sink.hitq.items)) {
         wf.store_hit(p, best.h.pl, best.h.prim, best.h.sub, D);
     }
-    if (sink.store_miss && valid && !hit)
-        wf.store_ray(p, make_float4(sink.miss_ori[0], sink.miss_ori[1], sink.miss_ori[2], 0.0f), make_float4(D.x, D.y, D.z, 0.0f));
     if (sink.hitq.items) warp_append(s_count, sink.hitq, hit, p);
 }
 
@@ -1199,11 +1195,7 @@ static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefro
 
 void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const QueueIn& qin, const QueueOut& hitq,
                      const DevParams* exit_prm, unsigned long long* ray_counter, unsigned long long* work) {
-    HitSink sink{hitq, 0, 0, 1.0f, 0, {0.0f, 0.0f, 0.0f}};
-    if (qin.gen.on == 2) {
-        sink.store_miss = 1;
-        for (int i = 0; i < 3; ++i) sink.miss_ori[i] = qin.gen.cam.ori[i];
-    }
+    HitSink sink{hitq, 0, 0, 1.0f};
     if (exit_prm) {
         sink.exit_mode = 1;
         sink.flat_face = exit_prm->flat_face;

@@ -26,8 +26,8 @@ struct RayGen {
     int32_t width, height;
     uint32_t npix;
     float inv_npix;
-    int32_t on;   // 1: the ray is stored where it is made; 2: only the rays that hit nothing are stored (by deliver(): the
-                  // fake sky of k_accumulate reads their direction), which is enough when nothing else reads a primary ray back
+    int32_t on;   // 1: the ray is stored where it is made; 2: it is not stored at all -- nothing reads a primary ray back except the
+                  // fake sky of k_accumulate for paths that were never shaded, and that takes the direction from `dirs`
 };
 struct QueueIn {
     const uint32_t* items;
@@ -72,7 +72,7 @@ void launch_shade_nee(const LaunchCfg& lc, const DevScene& S, const DevParams& p
 void launch_nee_resolve(const LaunchCfg& lc, Wavefront nee, const QueueIn& qin);
 void launch_accumulate_nee(const LaunchCfg& lc, Wavefront wf, Wavefront nee, float4* accum, uint32_t npix, int n_passes, uint32_t batch);
 void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& prm, Wavefront wf, const QueueIn& qin);
-void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes, uint32_t batch);
+void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes, uint32_t batch, const float4* cam_dirs);
 void launch_resolve(const LaunchCfg& lc, const float4* accum, int w, int h, float divisor, int subsampling, void* dst,
                     bool rgba8);
 void launch_trace(const LaunchCfg& lc, const DevScene& S, int64_t n, const float4* o, const float4* d, void* hits_out,

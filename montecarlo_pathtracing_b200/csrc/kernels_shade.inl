@@ -401,9 +401,13 @@ void launch_shade_exit(const LaunchCfg& lc, const DevScene& S, const DevParams& 
 // fake sky applies (tp/montecarlo.frag:118-119) with the path's total and attenuation -- the
 // initial 0 and 0.8 (:105-107) if it was never shaded in this batch.
 __global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __restrict__ accum, uint32_t npix,
-                                                        int n_passes, uint32_t batch) {
+                                                        int n_passes, uint32_t batch, const float4* __restrict__ cam_dirs) {
     for (uint32_t pix = blockIdx.x * blockDim.x + threadIdx.x; pix < npix; pix += gridDim.x * blockDim.x) {
         float4 a = accum[pix];
+        // a path that was never shaded still has its camera ray: with RayGen::on == 2 that ray was never stored, its
+        // direction is the pixel's entry of the camera table
+        float4 cam_d = make_float4(0.0f, 0.0f, 0.0f, 0.0f);
+        if (cam_dirs) cam_d = __ldg(cam_dirs + pix);
         // kAccUnroll passes at a time: their radiance sectors are requested together, then the directions of the ones that
         // escaped, and only then are they added -- in pass order (one pass per trip left 32 dependent round trips to DRAM
         // per pixel: 0.65 ms per 33 M paths)
@@ -415,7 +419,10 @@ __global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __r
                 if (k0 + j < n_passes) wf.load_rad(uint64_t(k0 + j) * npix + pix, a4[j], t4[j]);
 #pragma unroll
             for (int j = 0; j < kAccUnroll; ++j)
-                if (k0 + j < n_passes && __float_as_uint(a4[j].w) != 2u * batch + 1u) d4[j] = wf.load_ray_d(uint64_t(k0 + j) * npix + pix);
+                if (k0 + j < n_passes && __float_as_uint(a4[j].w) != 2u * batch + 1u) {
+                    if (cam_dirs && __float_as_uint(a4[j].w) != 2u * batch) d4[j] = cam_d;
+                    else d4[j] = wf.load_ray_d(uint64_t(k0 + j) * npix + pix);
+                }
 #pragma unroll
             for (int j = 0; j < kAccUnroll; ++j) {
                 if (k0 + j >= n_passes) break;
@@ -440,8 +447,8 @@ __global__ void __launch_bounds__(kBlock) k_accumulate(Wavefront wf, float4* __r
     }
 }
 
-void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes, uint32_t batch) {
-    k_accumulate<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(wf, accum, npix, n_passes, batch);
+void launch_accumulate(const LaunchCfg& lc, Wavefront wf, float4* accum, uint32_t npix, int n_passes, uint32_t batch, const float4* cam_dirs) {
+    k_accumulate<<<grid_for(lc, npix, 16), kBlock, 0, lc.stream>>>(wf, accum, npix, n_passes, batch, cam_dirs);
     lc.count();
 }
 
