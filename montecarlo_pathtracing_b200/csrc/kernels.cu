@@ -3,6 +3,7 @@
 // Compiled with -fmad=false (see vecmath.cuh). All kernels are grid-stride over a
 // device-resident work count, launched with a fixed grid that is a multiple of
 // the SM count, so a bounce never needs a host round trip to size its launches.
+#include <atomic>
 #include <cfloat>
 #include <cstdio>
 #include <cstring>
@@ -15,6 +16,20 @@
 namespace mcpt {
 
 constexpr int kBlock = 256;
+
+// Kernels that take more than 48 KB of dynamic shared memory need the attribute once per DEVICE (contexts of one process may
+// live on different GPUs): one bit per device ordinal, one word per kernel
+// (the kernel is a template argument: kernels of the same signature must not share the word).
+template <auto Kernel>
+static void allow_large_smem() {
+    static std::atomic<unsigned long long> done{0ull};
+    int dev = 0;
+    cudaGetDevice(&dev);
+    const unsigned long long bit = 1ull << (dev & 63);
+    if (done.load(std::memory_order_relaxed) & bit) return;
+    if (cudaFuncSetAttribute(Kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess)
+        done.fetch_or(bit, std::memory_order_relaxed);
+}
 
 static inline int grid_for(const LaunchCfg& lc, uint64_t n, int blocks_per_sm) {
     uint64_t want = (n + kBlock - 1) / kBlock;
@@ -1172,10 +1187,8 @@ static void launch_traverse_kind(const LaunchCfg& lc, const DevScene& S, Wavefro
         const size_t base = (size_t(S.smem_bytes) + 15) & ~size_t(15);
         const size_t smem_async = base + (kBlock / 32) * pool_bytes_per_warp(S.flat_max_type, true);
         const size_t smem_plain = base + (kBlock / 32) * pool_bytes_per_warp(S.flat_max_type, false);
-        static bool once = false;
-        if (!once)
-            once = cudaFuncSetAttribute(k_traverse_flat_pooled<COUNT, MINB, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess &&
-                   cudaFuncSetAttribute(k_traverse_flat_pooled<COUNT, MINB, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess;
+        allow_large_smem<k_traverse_flat_pooled<COUNT, MINB, false, false>>();
+        allow_large_smem<k_traverse_flat_pooled<COUNT, MINB, false, true>>();
         // the second pair of ray buffers only where MINB CTAs of it still fit one SM (228 KB, 1 KB reserved per CTA)
         if (S.flat_pool >= 2 && MINB * (smem_async + 1024 + 64) <= size_t(228) * 1024)
             k_traverse_flat_pooled<COUNT, MINB, false, true><<<grid, kBlock, smem_async, lc.stream>>>(S, wf, qin, sink, ray_counter, work);
@@ -1205,10 +1218,8 @@ void launch_traverse(const LaunchCfg& lc, const DevScene& S, Wavefront wf, const
         const size_t smem = ((size_t(S.smem_bytes) + 15) & ~size_t(15)) + (kBlock / 32) * kUPoolBytesPerWarp;
 #define MCPT_TRAVERSE_UP(COUNT, MINB)                                                                                                   \
     do {                                                                                                                                \
-        static bool once = false;                                                                                                       \
-        if (!once)                                                                                                                      \
-            once = cudaFuncSetAttribute(k_traverse_unified_pooled<COUNT, MINB, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess && \
-                   cudaFuncSetAttribute(k_traverse_unified_pooled<COUNT, MINB, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024) == cudaSuccess; \
+        allow_large_smem<k_traverse_unified_pooled<COUNT, MINB, true>>();                                                               \
+        allow_large_smem<k_traverse_unified_pooled<COUNT, MINB, false>>();                                                              \
         if (sink.exit_mode)                                                                                                             \
             k_traverse_unified_pooled<COUNT, MINB, true><<<lc.grid, kBlock, smem, lc.stream>>>(S, wf, qin, sink, ray_counter, work);    \
         else                                                                                                                            \
