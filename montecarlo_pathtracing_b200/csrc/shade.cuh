@@ -37,6 +37,8 @@ MCPT_DEV uint3 rng_seed(float tcx, float tcy, int numero_pass, float date) {
 // The xxhash32 state after n draws is seed0 + n * (11, 43, 67) (mod 2^32), and seed0 is a function
 // of the pixel, the pass and `date` only. So the wavefront stores the draw COUNT (4 bytes, in the
 // spare lane of the direction) instead of the 12-byte state, and shade rebuilds the state.
+// (Measured and dropped: screen_tc of every pixel from a table built next to the camera table instead of the two integer and two
+// IEEE divisions below -- the extra gather costs k_shade more than the arithmetic: 7.8 -> 8.25 ms per config-2 step.)
 MCPT_DEV uint3 path_seed(uint32_t p, uint32_t npix, int width, int height, int first_pass, float date, uint32_t n_draws) {
     const uint32_t k = p / npix;
     const uint32_t pix = p - k * npix;
